@@ -1,0 +1,179 @@
+// Shared declarations for the sm_100a kernels of the training hot path.
+// Path boundary: CudaRasterizer::Rasterizer::{forward,backward}
+//   (reference lib/diff-gaussian-rasterization/cuda_rasterizer/rasterizer.h:24-84) and
+//   Trainer::train (reference src/Trainer.cu:252-543).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <cstdint>
+#include <cstddef>
+
+#define GSB_TILE 16                 // tile edge in pixels: fixed by key/range parity (config.h:15-16)
+#define GSB_TILE_PIX (GSB_TILE * GSB_TILE)
+
+// One 48-byte record per splat and view: everything the render kernels gather per list entry.
+// Three float4 so a record moves as three 16-byte cp.async (LDGSTS) transfers.
+struct __align__(16) SplatRec {
+    float4 a;   // mean2D.x, mean2D.y, conic.x, conic.y
+    float4 b;   // conic.z, opacity, r, g
+    float4 c;   // b, depth, splat index (int bits), radius (int bits)
+};
+
+// Per-splat scratch written by the render backward (one vector red per float4) and consumed
+// (then cleared) by the preprocess backward.
+struct __align__(16) GradRec {
+    float4 a;   // dL/dmean2D.x, dL/dmean2D.y, dL/dconic.x, dL/dconic.y
+    float4 b;   // dL/dconic.w, dL/dopacity, dL/dr, dL/dg
+    float4 c;   // dL/db, unused x3
+};
+
+// Device-resident control block, cleared by one memset per view.
+struct GsbCtrl {
+    uint32_t num_rendered;          // R: total duplicates (device copy; host copy is optional)
+    uint32_t num_visible;           // splats with radius > 0
+    uint32_t overflow;              // 1 if R exceeded the binning capacity
+    uint32_t pad0;
+    uint32_t tickets[16];           // dynamic tile ids of the look-back kernels (one per launch)
+    uint32_t hist[8][256];          // digit histograms: [0..3] depth sort, [4..7] tile sort
+};
+
+#define GSB_CUDA_OK(expr)                                                              \
+    do {                                                                               \
+        cudaError_t _e = (expr);                                                       \
+        if (_e != cudaSuccess) return gsb_fail(_e, #expr, __FILE__, __LINE__);         \
+    } while (0)
+
+int gsb_fail(cudaError_t e, const char* what, const char* file, int line);
+int gsb_fail_msg(const char* msg);
+
+static inline int gsb_div_up(long long a, long long b) { return (int)((a + b - 1) / b); }
+
+// ------------------------------------------------------------------------------------------
+// Kernel launchers (defined in the .cu files of this directory).  All take a stream and never
+// synchronise; sizes that live on the device are passed as pointers into GsbCtrl.
+// ------------------------------------------------------------------------------------------
+
+struct PreprocessArgs {
+    int P, D, M;
+    const float* means3D;
+    const float* scales;
+    float scale_modifier;
+    const float* rotations;
+    const float* opacities;
+    const float* shs;
+    const float* cov3D_precomp;
+    const float* colors_precomp;
+    const float* viewmatrix;        // device, 16 floats column-major
+    const float* projmatrix;        // device, 16 floats column-major
+    const float* cam_pos;           // device, 3 floats
+    int W, H;
+    float tan_fovx, tan_fovy, focal_x, focal_y;
+    int grid_x, grid_y;
+    int prefiltered;
+    // outputs
+    int* radii;                     // [P]
+    int* radii_user;                // [P] or null (caller's optional array)
+    float* depths;                  // [P]
+    uint32_t* tiles_touched;        // [P]
+    SplatRec* recs;                 // [P]
+    float* cov3D;                   // [P][6]
+    uint8_t* clamped;               // [P] bit c set if channel c was clamped at 0
+    uint32_t* sort_keys;            // [P] depth bits (0xFFFFFFFF for culled splats)
+    uint32_t* sort_vals;            // [P] splat index
+};
+void launch_preprocess_fwd(const PreprocessArgs& a, cudaStream_t s);
+void launch_mark_visible(int P, const float* means3D, const float* viewmatrix, bool* present, cudaStream_t s);
+
+// binning.cu
+struct BinningArgs {
+    int P;
+    uint32_t r_cap;                 // capacity of the duplicate arrays
+    int grid_x, grid_y;
+    int tile_bits;                  // getHigherMsb(tiles)
+    const int* radii;
+    const uint32_t* tiles_touched;
+    const SplatRec* recs;
+    uint32_t* pkeys[2];             // [P] depth-sort ping-pong (pkeys[0] holds the input)
+    uint32_t* pvals[2];             // [P]
+    uint32_t* offsets;              // [P] exclusive offsets in depth order
+    uint32_t* rkeys[2];             // [r_cap] tile-id ping-pong
+    uint32_t* rvals[2];             // [r_cap] splat-id ping-pong
+    uint2* ranges;                  // [tiles], zeroed by the caller
+    unsigned long long* lookback;   // [lookback_tiles][256]
+    uint32_t lookback_tiles;
+    uint32_t* epoch;                // host counter, bumped per look-back launch
+    GsbCtrl* ctrl;
+    uint32_t* num_rendered_host;    // pinned host mirror of R, or null
+};
+// Returns the index (0/1) of the rvals/rkeys buffer holding the sorted list.
+int launch_binning(const BinningArgs& a, cudaStream_t s);
+// Second half of launch_binning when the caller has to size rkeys/rvals from R (compat API).
+void launch_binning_depth_and_scan(const BinningArgs& a, cudaStream_t s);
+int launch_binning_emit_and_sort(const BinningArgs& a, cudaStream_t s);
+
+// render_fwd.cu
+struct RenderFwdArgs {
+    int W, H, grid_x, grid_y;
+    const uint2* ranges;
+    const uint32_t* point_list;
+    const SplatRec* recs;
+    const float* bg;                // device, 3 floats
+    float* out_color;               // [3][H][W]
+    float* final_T;                 // [H*W]
+    uint32_t* n_contrib;            // [H*W]
+    uint32_t* tile_max;             // [tiles] max n_contrib in tile
+    int ppt;                        // pixels per thread: 1, 2 or 4
+};
+void launch_render_fwd(const RenderFwdArgs& a, cudaStream_t s);
+
+// render_bwd.cu
+struct RenderBwdArgs {
+    int W, H, grid_x, grid_y;
+    const uint2* ranges;
+    const uint32_t* point_list;
+    const SplatRec* recs;
+    const float* bg;
+    const float* final_T;
+    const uint32_t* n_contrib;
+    const uint32_t* tile_max;
+    const float* dL_dpix;           // [3][H][W], or null when the loss is fused:
+    const uint32_t* truth;          //   RGBA8 truth frame and
+    const float* rendered;          //   the forward's out_color (dL = truth/255 - rendered)
+    GradRec* grads;                 // [P], accumulated with vector reds
+    int ppt;
+};
+void launch_render_bwd(const RenderBwdArgs& a, cudaStream_t s);
+
+// preprocess_bwd.cu
+struct PreprocessBwdArgs {
+    int P, D, M;
+    const float* means3D;
+    const float* scales;
+    float scale_modifier;
+    const float* rotations;
+    const float* shs;
+    const float* cov3D;             // precomputed or the forward's
+    int cov3D_is_precomp;
+    int colors_precomp;             // nonzero: no SH backward
+    const float* viewmatrix;
+    const float* projmatrix;
+    const float* cam_pos;
+    float tan_fovx, tan_fovy, focal_x, focal_y;
+    const int* radii;
+    const uint8_t* clamped;
+    GradRec* grads;                 // consumed and cleared
+    // mode A (Rasterizer::backward): caller arrays, reference semantics
+    float* dL_dmean2D;              // [P][3] +=
+    float* dL_dconic;               // [P][4] +=
+    float* dL_dopacity;             // [P]    +=
+    float* dL_dcolor;               // [P][3] +=
+    float* dL_dmean3D;              // [P][3] overwritten for visible splats
+    float* dL_dcov3D;               // [P][6]
+    float* dL_dsh;                  // [P][M][3]
+    float* dL_dscale;               // [P][3]
+    float* dL_drot;                 // [P][4]
+    // mode B (Trainer): running means, layout [var P | loc 3P | sh 3MP | scale 3P | opacity P | rot 4P]
+    float* avg;                     // null selects mode A
+    float samples;                  // S = 2 * number of cameras
+};
+void launch_preprocess_bwd(const PreprocessBwdArgs& a, cudaStream_t s);

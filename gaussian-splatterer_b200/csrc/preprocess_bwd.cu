@@ -1,0 +1,284 @@
+// Backward of the per-splat preprocess, one fused kernel:
+//   conic gradient -> 2D covariance -> 3D covariance + mean   (computeCov2DCUDA,
+//       reference cuda_rasterizer/backward.cu:144-274)
+//   screen-space mean gradient -> 3D mean, SH backward, covariance -> scale / rotation
+//       (preprocessCUDA backward :346-396, computeColorFromSH :20-139, computeCov3D :278-341)
+// and, in Trainer mode, the running-mean accumulation of accumulateGradients
+// (reference src/Trainer.cu:47-77) so the 23 per-view gradient floats never round-trip HBM.
+// It consumes the packed GradRec scratch written by the render backward and clears it, which
+// replaces the nine per-view cudaMemsets of src/Trainer.cu:366-375.
+//
+// Quirks kept: the quaternion is used unnormalised and its gradient is not projected
+// (backward.cu:281,340); clamped SH channels get zero colour gradient; the x/z, y/z clamp zeroes
+// the matching mean gradient term.
+
+#include "common.cuh"
+
+namespace {
+
+__device__ const float kC0 = 0.28209479177387814f;
+__device__ const float kC1 = 0.4886025119029199f;
+__device__ const float kC2[5] = {1.0925484305920792f, -1.0925484305920792f, 0.31539156525252005f,
+                                 -1.0925484305920792f, 0.5462742152960396f};
+__device__ const float kC3[7] = {-0.5900435899266435f, 2.890611442640554f, -0.4570457994644658f,
+                                 0.3731763325901154f, -0.4570457994644658f, 1.445305721320277f,
+                                 -0.5900435899266435f};
+
+struct V3 { float x, y, z; };
+__device__ __forceinline__ V3 ld3(const float* p) { return {p[0], p[1], p[2]}; }
+__device__ __forceinline__ V3 operator*(float s, V3 v) { return {s * v.x, s * v.y, s * v.z}; }
+__device__ __forceinline__ V3 operator+(V3 a, V3 b) { return {a.x + b.x, a.y + b.y, a.z + b.z}; }
+__device__ __forceinline__ float dot(V3 a, V3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+
+// Writes dL/dsh (M x 3) through `emit(coeff, value)` and returns dL/dmean from the view direction.
+template <typename Emit>
+__device__ V3 sh_backward(int deg, float px, float py, float pz, const float* cam, const float* sh, V3 dRGB, Emit emit) {
+    const V3 d0 = {px - cam[0], py - cam[1], pz - cam[2]};
+    const float len = sqrtf(d0.x * d0.x + d0.y * d0.y + d0.z * d0.z);
+    const float x = d0.x / len, y = d0.y / len, z = d0.z / len;
+    V3 dx = {0, 0, 0}, dy = {0, 0, 0}, dz = {0, 0, 0};
+    emit(0, kC0 * dRGB);
+    if (deg > 0) {
+        emit(1, (-kC1 * y) * dRGB);
+        emit(2, (kC1 * z) * dRGB);
+        emit(3, (-kC1 * x) * dRGB);
+        dx = (-kC1) * ld3(sh + 9);
+        dy = (-kC1) * ld3(sh + 3);
+        dz = kC1 * ld3(sh + 6);
+        if (deg > 1) {
+            const float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
+            emit(4, (kC2[0] * xy) * dRGB);
+            emit(5, (kC2[1] * yz) * dRGB);
+            emit(6, (kC2[2] * (2.f * zz - xx - yy)) * dRGB);
+            emit(7, (kC2[3] * xz) * dRGB);
+            emit(8, (kC2[4] * (xx - yy)) * dRGB);
+            const V3 s4 = ld3(sh + 12), s5 = ld3(sh + 15), s6 = ld3(sh + 18), s7 = ld3(sh + 21), s8 = ld3(sh + 24);
+            dx = dx + (kC2[0] * y) * s4 + (kC2[2] * 2.f * -x) * s6 + (kC2[3] * z) * s7 + (kC2[4] * 2.f * x) * s8;
+            dy = dy + (kC2[0] * x) * s4 + (kC2[1] * z) * s5 + (kC2[2] * 2.f * -y) * s6 + (kC2[4] * 2.f * -y) * s8;
+            dz = dz + (kC2[1] * y) * s5 + (kC2[2] * 2.f * 2.f * z) * s6 + (kC2[3] * x) * s7;
+            if (deg > 2) {
+                emit(9, (kC3[0] * y * (3.f * xx - yy)) * dRGB);
+                emit(10, (kC3[1] * xy * z) * dRGB);
+                emit(11, (kC3[2] * y * (4.f * zz - xx - yy)) * dRGB);
+                emit(12, (kC3[3] * z * (2.f * zz - 3.f * xx - 3.f * yy)) * dRGB);
+                emit(13, (kC3[4] * x * (4.f * zz - xx - yy)) * dRGB);
+                emit(14, (kC3[5] * z * (xx - yy)) * dRGB);
+                emit(15, (kC3[6] * x * (xx - 3.f * yy)) * dRGB);
+                const V3 s9 = ld3(sh + 27), s10 = ld3(sh + 30), s11 = ld3(sh + 33), s12 = ld3(sh + 36),
+                         s13 = ld3(sh + 39), s14 = ld3(sh + 42), s15 = ld3(sh + 45);
+                dx = dx + (kC3[0] * 3.f * 2.f * xy) * s9 + (kC3[1] * yz) * s10 + (kC3[2] * -2.f * xy) * s11 +
+                     (kC3[3] * -3.f * 2.f * xz) * s12 + (kC3[4] * (-3.f * xx + 4.f * zz - yy)) * s13 +
+                     (kC3[5] * 2.f * xz) * s14 + (kC3[6] * 3.f * (xx - yy)) * s15;
+                dy = dy + (kC3[0] * 3.f * (xx - yy)) * s9 + (kC3[1] * xz) * s10 +
+                     (kC3[2] * (-3.f * yy + 4.f * zz - xx)) * s11 + (kC3[3] * -3.f * 2.f * yz) * s12 +
+                     (kC3[4] * -2.f * xy) * s13 + (kC3[5] * -2.f * yz) * s14 + (kC3[6] * -3.f * 2.f * xy) * s15;
+                dz = dz + (kC3[1] * xy) * s10 + (kC3[2] * 4.f * 2.f * yz) * s11 +
+                     (kC3[3] * 3.f * (2.f * zz - xx - yy)) * s12 + (kC3[4] * 4.f * 2.f * xz) * s13 +
+                     (kC3[5] * (xx - yy)) * s14;
+            }
+        }
+    }
+    // through dir = d0 / |d0|  (dnormvdv, auxiliary.h:108-119)
+    const V3 dd = {dot(dx, dRGB), dot(dy, dRGB), dot(dz, dRGB)};
+    const float sum2 = d0.x * d0.x + d0.y * d0.y + d0.z * d0.z;
+    const float inv32 = 1.0f / sqrtf(sum2 * sum2 * sum2);
+    V3 g;
+    g.x = ((sum2 - d0.x * d0.x) * dd.x - d0.y * d0.x * dd.y - d0.z * d0.x * dd.z) * inv32;
+    g.y = (-d0.x * d0.y * dd.x + (sum2 - d0.y * d0.y) * dd.y - d0.z * d0.y * dd.z) * inv32;
+    g.z = (-d0.x * d0.z * dd.x - d0.y * d0.z * dd.y + (sum2 - d0.z * d0.z) * dd.z) * inv32;
+    return g;
+}
+
+__global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreprocessBwdArgs a) {
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= a.P || !(a.radii[idx] > 0)) return;
+
+    // take and clear the per-view scratch
+    GradRec g = a.grads[idx];
+    {
+        const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+        a.grads[idx].a = z; a.grads[idx].b = z; a.grads[idx].c = z;
+    }
+    float gm2x = g.a.x, gm2y = g.a.y;
+    float gcx = g.a.z, gcy = g.a.w, gcw = g.b.x;
+    float gop = g.b.y;
+    V3 gcol = {g.b.z, g.b.w, g.c.x};
+    const bool modeA = (a.avg == nullptr);
+    if (modeA) {
+        // Rasterizer::backward accumulates into caller arrays (atomicAdd semantics) and the
+        // per-splat stage then reads the totals.
+        gm2x = (a.dL_dmean2D[3 * idx] += gm2x);
+        gm2y = (a.dL_dmean2D[3 * idx + 1] += gm2y);
+        gcx = (a.dL_dconic[4 * idx] += gcx);
+        gcy = (a.dL_dconic[4 * idx + 1] += gcy);
+        gcw = (a.dL_dconic[4 * idx + 3] += gcw);
+        gop = (a.dL_dopacity[idx] += gop);
+        gcol.x = (a.dL_dcolor[3 * idx] += gcol.x);
+        gcol.y = (a.dL_dcolor[3 * idx + 1] += gcol.y);
+        gcol.z = (a.dL_dcolor[3 * idx + 2] += gcol.z);
+    }
+
+    const float mx = a.means3D[3 * idx], my = a.means3D[3 * idx + 1], mz = a.means3D[3 * idx + 2];
+    const float* V = a.viewmatrix;
+    const float* Pm = a.projmatrix;
+    const float v0 = __ldg(V + 0), v1 = __ldg(V + 1), v2 = __ldg(V + 2);
+    const float v4 = __ldg(V + 4), v5 = __ldg(V + 5), v6 = __ldg(V + 6);
+    const float v8 = __ldg(V + 8), v9 = __ldg(V + 9), v10 = __ldg(V + 10);
+
+    // ---- conic -> cov2D -> cov3D and the covariance path of the mean ----
+    float c3[6];
+#pragma unroll
+    for (int k = 0; k < 6; k++) c3[k] = a.cov3D[6 * idx + k];
+    float tx = v0 * mx + v4 * my + v8 * mz + __ldg(V + 12);
+    float ty = v1 * mx + v5 * my + v9 * mz + __ldg(V + 13);
+    const float tz = v2 * mx + v6 * my + v10 * mz + __ldg(V + 14);
+    const float limx = 1.3f * a.tan_fovx, limy = 1.3f * a.tan_fovy;
+    const float txtz = tx / tz, tytz = ty / tz;
+    tx = fminf(limx, fmaxf(-limx, txtz)) * tz;
+    ty = fminf(limy, fmaxf(-limy, tytz)) * tz;
+    const float x_grad_mul = (txtz < -limx || txtz > limx) ? 0.f : 1.f;
+    const float y_grad_mul = (tytz < -limy || tytz > limy) ? 0.f : 1.f;
+    const float hx = a.focal_x, hy = a.focal_y;
+    const float J00 = hx / tz, J02 = -(hx * tx) / (tz * tz), J11 = hy / tz, J12 = -(hy * ty) / (tz * tz);
+    const float a0 = v0 * J00 + v2 * J02, a1 = v4 * J00 + v6 * J02, a2 = v8 * J00 + v10 * J02;   // T col 0
+    const float b0 = v1 * J11 + v2 * J12, b1 = v5 * J11 + v6 * J12, b2 = v9 * J11 + v10 * J12;   // T col 1
+    const float ua0 = a0 * c3[0] + a1 * c3[1] + a2 * c3[2];
+    const float ua1 = a0 * c3[1] + a1 * c3[3] + a2 * c3[4];
+    const float ua2 = a0 * c3[2] + a1 * c3[4] + a2 * c3[5];
+    const float ub0 = b0 * c3[0] + b1 * c3[1] + b2 * c3[2];
+    const float ub1 = b0 * c3[1] + b1 * c3[3] + b2 * c3[4];
+    const float ub2 = b0 * c3[2] + b1 * c3[4] + b2 * c3[5];
+    const float ca = a0 * ua0 + a1 * ua1 + a2 * ua2 + 0.3f;
+    const float cb = a0 * ub0 + a1 * ub1 + a2 * ub2;
+    const float cc = b0 * ub0 + b1 * ub1 + b2 * ub2 + 0.3f;
+    const float denom = ca * cc - cb * cb;
+    const float denom2inv = 1.0f / ((denom * denom) + 0.0000001f);
+    float dLa = 0.f, dLb = 0.f, dLc = 0.f;
+    float dcov[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    if (denom2inv != 0.f) {
+        dLa = denom2inv * (-cc * cc * gcx + 2.f * cb * cc * gcy + (denom - ca * cc) * gcw);
+        dLc = denom2inv * (-ca * ca * gcw + 2.f * ca * cb * gcy + (denom - ca * cc) * gcx);
+        dLb = denom2inv * 2.f * (cb * cc * gcx - (denom + 2.f * cb * cb) * gcy + ca * cb * gcw);
+        dcov[0] = a0 * a0 * dLa + a0 * b0 * dLb + b0 * b0 * dLc;
+        dcov[3] = a1 * a1 * dLa + a1 * b1 * dLb + b1 * b1 * dLc;
+        dcov[5] = a2 * a2 * dLa + a2 * b2 * dLb + b2 * b2 * dLc;
+        dcov[1] = 2.f * a0 * a1 * dLa + (a0 * b1 + a1 * b0) * dLb + 2.f * b0 * b1 * dLc;
+        dcov[2] = 2.f * a0 * a2 * dLa + (a0 * b2 + a2 * b0) * dLb + 2.f * b0 * b2 * dLc;
+        dcov[4] = 2.f * a2 * a1 * dLa + (a1 * b2 + a2 * b1) * dLb + 2.f * b1 * b2 * dLc;
+    }
+    const float dT00 = 2.f * ua0 * dLa + ub0 * dLb, dT01 = 2.f * ua1 * dLa + ub1 * dLb, dT02 = 2.f * ua2 * dLa + ub2 * dLb;
+    const float dT10 = 2.f * ub0 * dLc + ua0 * dLb, dT11 = 2.f * ub1 * dLc + ua1 * dLb, dT12 = 2.f * ub2 * dLc + ua2 * dLb;
+    const float dJ00 = v0 * dT00 + v4 * dT01 + v8 * dT02;
+    const float dJ02 = v2 * dT00 + v6 * dT01 + v10 * dT02;
+    const float dJ11 = v1 * dT10 + v5 * dT11 + v9 * dT12;
+    const float dJ12 = v2 * dT10 + v6 * dT11 + v10 * dT12;
+    const float itz = 1.f / tz, itz2 = itz * itz, itz3 = itz2 * itz;
+    const float dtx = x_grad_mul * -hx * itz2 * dJ02;
+    const float dty = y_grad_mul * -hy * itz2 * dJ12;
+    const float dtz = -hx * itz2 * dJ00 - hy * itz2 * dJ11 + (2.f * hx * tx) * itz3 * dJ02 + (2.f * hy * ty) * itz3 * dJ12;
+    V3 gmean = {v0 * dtx + v1 * dty + v2 * dtz, v4 * dtx + v5 * dty + v6 * dtz, v8 * dtx + v9 * dty + v10 * dtz};
+
+    // ---- screen-space mean gradient through the perspective divide ----
+    {
+        const float p0 = __ldg(Pm + 0), p1 = __ldg(Pm + 1), p3 = __ldg(Pm + 3);
+        const float p4 = __ldg(Pm + 4), p5 = __ldg(Pm + 5), p7 = __ldg(Pm + 7);
+        const float p8 = __ldg(Pm + 8), p9 = __ldg(Pm + 9), p11 = __ldg(Pm + 11);
+        const float hw = p3 * mx + p7 * my + p11 * mz + __ldg(Pm + 15);
+        const float m_w = 1.0f / (hw + 0.0000001f);
+        const float mul1 = (p0 * mx + p4 * my + p8 * mz + __ldg(Pm + 12)) * m_w * m_w;
+        const float mul2 = (p1 * mx + p5 * my + p9 * mz + __ldg(Pm + 13)) * m_w * m_w;
+        gmean.x += (p0 * m_w - p3 * mul1) * gm2x + (p1 * m_w - p3 * mul2) * gm2y;
+        gmean.y += (p4 * m_w - p7 * mul1) * gm2x + (p5 * m_w - p7 * mul2) * gm2y;
+        gmean.z += (p8 * m_w - p11 * mul1) * gm2x + (p9 * m_w - p11 * mul2) * gm2y;
+    }
+
+    const float S = a.samples;
+    const size_t P = (size_t)a.P;
+    const int M = a.M;
+    float* avg_loc = modeA ? nullptr : a.avg + P;
+    float* avg_sh = modeA ? nullptr : a.avg + 4 * P;
+    float* avg_scale = modeA ? nullptr : a.avg + 4 * P + 3 * (size_t)M * P;
+    float* avg_op = modeA ? nullptr : avg_scale + 3 * P;
+    float* avg_rot = modeA ? nullptr : avg_op + P;
+
+    // ---- SH backward ----
+    if (!a.colors_precomp) {
+        const uint8_t cl = a.clamped[idx];
+        const V3 dRGB = {(cl & 1) ? 0.f : gcol.x, (cl & 2) ? 0.f : gcol.y, (cl & 4) ? 0.f : gcol.z};
+        const float* sh = a.shs + (size_t)idx * M * 3;
+        V3 gdir;
+        if (modeA) {
+            float* out = a.dL_dsh + (size_t)idx * M * 3;
+            gdir = sh_backward(a.D, mx, my, mz, a.cam_pos, sh, dRGB, [&](int c, V3 v) {
+                out[3 * c] = v.x; out[3 * c + 1] = v.y; out[3 * c + 2] = v.z;
+            });
+        } else {
+            float* out = avg_sh + (size_t)idx * M * 3;
+            gdir = sh_backward(a.D, mx, my, mz, a.cam_pos, sh, dRGB, [&](int c, V3 v) {
+                out[3 * c] += v.x / S; out[3 * c + 1] += v.y / S; out[3 * c + 2] += v.z / S;
+            });
+        }
+        gmean = gmean + gdir;
+    }
+
+    if (modeA) {
+        a.dL_dmean3D[3 * idx] = gmean.x; a.dL_dmean3D[3 * idx + 1] = gmean.y; a.dL_dmean3D[3 * idx + 2] = gmean.z;
+#pragma unroll
+        for (int k = 0; k < 6; k++) a.dL_dcov3D[6 * idx + k] = dcov[k];
+    } else {
+        a.avg[idx] += sqrtf(gmean.x * gmean.x + gmean.y * gmean.y + gmean.z * gmean.z) / S;
+        avg_loc[3 * idx] += gmean.x / S; avg_loc[3 * idx + 1] += gmean.y / S; avg_loc[3 * idx + 2] += gmean.z / S;
+        avg_op[idx] += gop / S;
+    }
+
+    // ---- cov3D -> scale, rotation ----
+    if (!a.cov3D_is_precomp) {
+        const float r = a.rotations[4 * idx], x = a.rotations[4 * idx + 1], y = a.rotations[4 * idx + 2], z = a.rotations[4 * idx + 3];
+        const float s[3] = {a.scale_modifier * a.scales[3 * idx], a.scale_modifier * a.scales[3 * idx + 1],
+                            a.scale_modifier * a.scales[3 * idx + 2]};
+        // Rg[c][r]: columns of the reference's R literal
+        const float Rg[3][3] = {{1.f - 2.f * (y * y + z * z), 2.f * (x * y - r * z), 2.f * (x * z + r * y)},
+                                {2.f * (x * y + r * z), 1.f - 2.f * (x * x + z * z), 2.f * (y * z - r * x)},
+                                {2.f * (x * z - r * y), 2.f * (y * z + r * x), 1.f - 2.f * (x * x + y * y)}};
+        const float Dg[3][3] = {{dcov[0], 0.5f * dcov[1], 0.5f * dcov[2]},
+                                {0.5f * dcov[1], dcov[3], 0.5f * dcov[4]},
+                                {0.5f * dcov[2], 0.5f * dcov[4], dcov[5]}};
+        // dMt[c][r] = 2 * sum_k (s_c Rg[k][c]) * Dg[r][k]
+        float dMt[3][3];
+#pragma unroll
+        for (int c = 0; c < 3; c++)
+#pragma unroll
+            for (int rr = 0; rr < 3; rr++)
+                dMt[c][rr] = 2.0f * (s[c] * Rg[0][c] * Dg[rr][0] + s[c] * Rg[1][c] * Dg[rr][1] + s[c] * Rg[2][c] * Dg[rr][2]);
+        float gs[3];
+#pragma unroll
+        for (int c = 0; c < 3; c++) gs[c] = Rg[0][c] * dMt[c][0] + Rg[1][c] * dMt[c][1] + Rg[2][c] * dMt[c][2];
+#pragma unroll
+        for (int c = 0; c < 3; c++)
+#pragma unroll
+            for (int rr = 0; rr < 3; rr++) dMt[c][rr] *= s[c];
+        float gq[4];
+        gq[0] = 2 * z * (dMt[0][1] - dMt[1][0]) + 2 * y * (dMt[2][0] - dMt[0][2]) + 2 * x * (dMt[1][2] - dMt[2][1]);
+        gq[1] = 2 * y * (dMt[1][0] + dMt[0][1]) + 2 * z * (dMt[2][0] + dMt[0][2]) + 2 * r * (dMt[1][2] - dMt[2][1]) - 4 * x * (dMt[2][2] + dMt[1][1]);
+        gq[2] = 2 * x * (dMt[1][0] + dMt[0][1]) + 2 * r * (dMt[2][0] - dMt[0][2]) + 2 * z * (dMt[1][2] + dMt[2][1]) - 4 * y * (dMt[2][2] + dMt[0][0]);
+        gq[3] = 2 * r * (dMt[0][1] - dMt[1][0]) + 2 * x * (dMt[2][0] + dMt[0][2]) + 2 * y * (dMt[1][2] + dMt[2][1]) - 4 * z * (dMt[1][1] + dMt[0][0]);
+        if (modeA) {
+#pragma unroll
+            for (int c = 0; c < 3; c++) a.dL_dscale[3 * idx + c] = gs[c];
+#pragma unroll
+            for (int c = 0; c < 4; c++) a.dL_drot[4 * idx + c] = gq[c];
+        } else {
+#pragma unroll
+            for (int c = 0; c < 3; c++) avg_scale[3 * idx + c] += gs[c] / S;
+#pragma unroll
+            for (int c = 0; c < 4; c++) avg_rot[4 * idx + c] += gq[c] / S;
+        }
+    }
+}
+
+}  // namespace
+
+void launch_preprocess_bwd(const PreprocessBwdArgs& a, cudaStream_t s) {
+    if (a.P <= 0) return;
+    preprocess_bwd_kernel<<<gsb_div_up(a.P, 256), 256, 0, s>>>(a);
+}

@@ -1,0 +1,271 @@
+// C ABI of the rasterizer level: gsb_rasterizer_forward / backward / mark_visible.
+// Orchestration counterpart of CudaRasterizer::Rasterizer::{forward,backward,markVisible}
+// (reference cuda_rasterizer/rasterizer_impl.cu:141-153,198-434); the workspace carving below
+// plays the role of Geometry/Binning/ImageState::fromChunk (:155-194) with this library's own
+// private layout inside the three caller-allocated blobs.
+
+#include "workspace.cuh"
+#include "trainer_kernels.cuh"
+#include "../../include/gsb.h"
+
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+
+namespace {
+thread_local char g_err[512] = "";
+int g_fwd_ppt = 2, g_bwd_ppt = 2;
+}  // namespace
+
+int gsb_fail(cudaError_t e, const char* what, const char* file, int line) {
+    snprintf(g_err, sizeof(g_err), "CUDA error %d (%s) in %s at %s:%d", (int)e, cudaGetErrorString(e), what, file, line);
+    return GSB_ERR_CUDA;
+}
+int gsb_fail_msg(const char* msg) {
+    snprintf(g_err, sizeof(g_err), "%s", msg);
+    return GSB_ERR_ARG;
+}
+
+// getHigherMsb (rasterizer_impl.cu:35-50): smallest b with n < 2^b ... as the reference computes it.
+int gsb_tile_bits(uint32_t n) {
+    uint32_t msb = sizeof(n) * 4, step = msb;
+    while (step > 1) {
+        step /= 2;
+        if (n >> msb) msb += step; else msb -= step;
+    }
+    if (n >> msb) msb++;
+    return (int)msb;
+}
+
+namespace {
+
+__global__ void sorted_keys_kernel(const uint32_t* tiles, const uint32_t* list, const float* depths, uint32_t R,
+                                   uint64_t* out) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= R) return;
+    out[i] = ((uint64_t)tiles[i] << 32) | (uint64_t)__float_as_uint(depths[list[i]]);
+}
+
+__global__ void fill_background_kernel(float* out, const float* bg, int n) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    out[i] = bg[0]; out[i + n] = bg[1]; out[i + 2 * (size_t)n] = bg[2];
+}
+
+int check(cudaStream_t s, bool debug) {
+    if (debug) {
+        GSB_CUDA_OK(cudaStreamSynchronize(s));
+    }
+    GSB_CUDA_OK(cudaGetLastError());
+    return GSB_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* gsb_last_error(void) { return g_err; }
+int gsb_version(void) { return 100; }
+
+void gsb_set_render_ppt(int fwd_ppt, int bwd_ppt) {
+    if (fwd_ppt == 1 || fwd_ppt == 2 || fwd_ppt == 4) g_fwd_ppt = fwd_ppt;
+    if (bwd_ppt == 1 || bwd_ppt == 2 || bwd_ppt == 4) g_bwd_ppt = bwd_ppt;
+}
+
+int gsb_rasterizer_forward(gsb_alloc_fn geometry_alloc, void* geometry_user, gsb_alloc_fn binning_alloc,
+                           void* binning_user, gsb_alloc_fn image_alloc, void* image_user, int P, int D, int M,
+                           const float* background, int width, int height, const float* means3D, const float* shs,
+                           const float* colors_precomp, const float* opacities, const float* scales,
+                           float scale_modifier, const float* rotations, const float* cov3D_precomp,
+                           const float* viewmatrix, const float* projmatrix, const float* cam_pos, float tan_fovx,
+                           float tan_fovy, int prefiltered, float* out_color, int* radii, int debug, void* stream,
+                           int* num_rendered) {
+    cudaStream_t s = (cudaStream_t)stream;
+    if (num_rendered) *num_rendered = 0;
+    if (P < 0 || width <= 0 || height <= 0 || !geometry_alloc || !binning_alloc || !image_alloc)
+        return gsb_fail_msg("gsb_rasterizer_forward: invalid argument");
+    if (colors_precomp == nullptr && shs == nullptr)
+        return gsb_fail_msg("gsb_rasterizer_forward: neither shs nor colors_precomp given");
+    const bool dbg = debug != 0;
+    const int grid_x = (width + GSB_TILE - 1) / GSB_TILE, grid_y = (height + GSB_TILE - 1) / GSB_TILE;
+    const int tiles = grid_x * grid_y;
+
+    GeomWs g;
+    char* gptr = geometry_alloc(GeomWs::required((size_t)P), geometry_user);
+    if (!gptr) { gsb_fail_msg("geometry allocator returned NULL"); return GSB_ERR_ALLOC; }
+    g.carve(gptr, (size_t)P);
+    ImageWs im;
+    char* iptr = image_alloc(ImageWs::required((size_t)width * height, (size_t)tiles), image_user);
+    if (!iptr) { gsb_fail_msg("image allocator returned NULL"); return GSB_ERR_ALLOC; }
+    im.carve(iptr, (size_t)width * height, (size_t)tiles);
+
+    GSB_CUDA_OK(cudaMemsetAsync(g.ctrl, 0, sizeof(GsbCtrl), s));
+    GSB_CUDA_OK(cudaMemsetAsync(g.lookback, 0, GeomWs::lookback_tiles((size_t)P) * 256 * sizeof(unsigned long long), s));
+    GSB_CUDA_OK(cudaMemsetAsync(im.ranges, 0, (size_t)tiles * sizeof(uint2), s));
+
+    PreprocessArgs pa;
+    pa.P = P; pa.D = D; pa.M = M;
+    pa.means3D = means3D; pa.scales = scales; pa.scale_modifier = scale_modifier; pa.rotations = rotations;
+    pa.opacities = opacities; pa.shs = shs; pa.cov3D_precomp = cov3D_precomp; pa.colors_precomp = colors_precomp;
+    pa.viewmatrix = viewmatrix; pa.projmatrix = projmatrix; pa.cam_pos = cam_pos;
+    pa.W = width; pa.H = height; pa.tan_fovx = tan_fovx; pa.tan_fovy = tan_fovy;
+    pa.focal_y = height / (2.0f * tan_fovy);
+    pa.focal_x = width / (2.0f * tan_fovx);
+    pa.grid_x = grid_x; pa.grid_y = grid_y; pa.prefiltered = prefiltered;
+    pa.radii = g.radii; pa.radii_user = radii; pa.depths = g.depths; pa.tiles_touched = g.tiles_touched;
+    pa.recs = g.recs; pa.cov3D = g.cov3D; pa.clamped = g.clamped; pa.sort_keys = g.pkeys[0]; pa.sort_vals = g.pvals[0];
+    launch_preprocess_fwd(pa, s);
+    if (int e = check(s, dbg)) return e;
+
+    uint32_t epoch = 0;
+    BinningArgs ba;
+    ba.P = P; ba.r_cap = 0xFFFFFFFFu; ba.grid_x = grid_x; ba.grid_y = grid_y; ba.tile_bits = gsb_tile_bits((uint32_t)tiles);
+    ba.radii = g.radii; ba.tiles_touched = g.tiles_touched; ba.recs = g.recs;
+    ba.pkeys[0] = g.pkeys[0]; ba.pkeys[1] = g.pkeys[1]; ba.pvals[0] = g.pvals[0]; ba.pvals[1] = g.pvals[1];
+    ba.offsets = g.offsets; ba.rkeys[0] = ba.rkeys[1] = ba.rvals[0] = ba.rvals[1] = nullptr;
+    ba.ranges = im.ranges; ba.lookback = g.lookback; ba.lookback_tiles = (uint32_t)GeomWs::lookback_tiles((size_t)P);
+    ba.epoch = &epoch; ba.ctrl = g.ctrl; ba.num_rendered_host = nullptr;
+    launch_binning_depth_and_scan(ba, s);
+    if (int e = check(s, dbg)) return e;
+
+    // The one forced device->host crossing of this API (rasterizer_impl.cu:281): R sizes the
+    // binning workspace the caller allocates.
+    uint32_t R = 0;
+    if (P > 0) {
+        GSB_CUDA_OK(cudaMemcpyAsync(&R, &g.ctrl->num_rendered, sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+        GSB_CUDA_OK(cudaStreamSynchronize(s));
+    }
+    if (R > 0x7FFFFFFFu) return gsb_fail_msg("gsb_rasterizer_forward: duplicate count exceeds int range");
+    BinWs b;
+    char* bptr = binning_alloc(BinWs::required((size_t)R), binning_user);
+    if (!bptr) { gsb_fail_msg("binning allocator returned NULL"); return GSB_ERR_ALLOC; }
+    b.carve(bptr, (size_t)R);
+    int fin = 0;
+    if (R > 0) {
+        GSB_CUDA_OK(cudaMemsetAsync(b.lookback, 0, BinWs::lookback_tiles((size_t)R) * 256 * sizeof(unsigned long long), s));
+        ba.r_cap = R;
+        ba.rkeys[0] = b.rkeys[0]; ba.rkeys[1] = b.rkeys[1]; ba.rvals[0] = b.rvals[0]; ba.rvals[1] = b.rvals[1];
+        ba.lookback = b.lookback; ba.lookback_tiles = (uint32_t)BinWs::lookback_tiles((size_t)R);
+        fin = launch_binning_emit_and_sort(ba, s);
+        if (int e = check(s, dbg)) return e;
+    }
+
+    RenderFwdArgs ra;
+    ra.W = width; ra.H = height; ra.grid_x = grid_x; ra.grid_y = grid_y;
+    ra.ranges = im.ranges; ra.point_list = b.rvals[fin]; ra.recs = g.recs; ra.bg = background;
+    ra.out_color = out_color; ra.final_T = im.final_T; ra.n_contrib = im.n_contrib; ra.tile_max = im.tile_max;
+    ra.ppt = g_fwd_ppt;
+    launch_render_fwd(ra, s);
+    if (int e = check(s, dbg)) return e;
+    if (num_rendered) *num_rendered = (int)R;
+    return GSB_OK;
+}
+
+int gsb_rasterizer_backward(int P, int D, int M, int R, const float* background, int width, int height,
+                            const float* means3D, const float* shs, const float* colors_precomp, const float* scales,
+                            float scale_modifier, const float* rotations, const float* cov3D_precomp,
+                            const float* viewmatrix, const float* projmatrix, const float* campos, float tan_fovx,
+                            float tan_fovy, const int* radii, char* geom_buffer, char* binning_buffer, char* image_buffer,
+                            const float* dL_dpix, float* dL_dmean2D, float* dL_dconic, float* dL_dopacity,
+                            float* dL_dcolor, float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscale,
+                            float* dL_drot, int debug, void* stream) {
+    cudaStream_t s = (cudaStream_t)stream;
+    if (P <= 0) return GSB_OK;
+    if (!geom_buffer || !image_buffer || !dL_dpix) return gsb_fail_msg("gsb_rasterizer_backward: invalid argument");
+    const bool dbg = debug != 0;
+    const int grid_x = (width + GSB_TILE - 1) / GSB_TILE, grid_y = (height + GSB_TILE - 1) / GSB_TILE;
+    const int tiles = grid_x * grid_y;
+    GeomWs g; g.carve(geom_buffer, (size_t)P);
+    ImageWs im; im.carve(image_buffer, (size_t)width * height, (size_t)tiles);
+    BinWs b; b.carve(binning_buffer, (size_t)(R > 0 ? R : 0));
+    const int npass = (gsb_tile_bits((uint32_t)tiles) + 7) / 8;
+    const int fin = (npass > 0 ? npass : 1) & 1;
+    if (radii == nullptr) radii = g.radii;
+
+    GSB_CUDA_OK(cudaMemsetAsync(g.grads, 0, (size_t)P * sizeof(GradRec), s));
+    if (R > 0) {
+        RenderBwdArgs rb;
+        rb.W = width; rb.H = height; rb.grid_x = grid_x; rb.grid_y = grid_y;
+        rb.ranges = im.ranges; rb.point_list = b.rvals[fin]; rb.recs = g.recs; rb.bg = background;
+        rb.final_T = im.final_T; rb.n_contrib = im.n_contrib; rb.tile_max = im.tile_max;
+        rb.dL_dpix = dL_dpix; rb.truth = nullptr; rb.rendered = nullptr; rb.grads = g.grads; rb.ppt = g_bwd_ppt;
+        launch_render_bwd(rb, s);
+        if (int e = check(s, dbg)) return e;
+    }
+    PreprocessBwdArgs pb;
+    memset(&pb, 0, sizeof(pb));
+    pb.P = P; pb.D = D; pb.M = M;
+    pb.means3D = means3D; pb.scales = scales; pb.scale_modifier = scale_modifier; pb.rotations = rotations; pb.shs = shs;
+    pb.cov3D = cov3D_precomp ? cov3D_precomp : g.cov3D;
+    pb.cov3D_is_precomp = (scales == nullptr) ? 1 : 0;
+    pb.colors_precomp = (shs == nullptr) ? 1 : 0;
+    pb.viewmatrix = viewmatrix; pb.projmatrix = projmatrix; pb.cam_pos = campos;
+    pb.tan_fovx = tan_fovx; pb.tan_fovy = tan_fovy;
+    pb.focal_y = height / (2.0f * tan_fovy);
+    pb.focal_x = width / (2.0f * tan_fovx);
+    pb.radii = radii; pb.clamped = g.clamped; pb.grads = g.grads;
+    pb.dL_dmean2D = dL_dmean2D; pb.dL_dconic = dL_dconic; pb.dL_dopacity = dL_dopacity; pb.dL_dcolor = dL_dcolor;
+    pb.dL_dmean3D = dL_dmean3D; pb.dL_dcov3D = dL_dcov3D; pb.dL_dsh = dL_dsh; pb.dL_dscale = dL_dscale; pb.dL_drot = dL_drot;
+    pb.avg = nullptr; pb.samples = 1.f;
+    launch_preprocess_bwd(pb, s);
+    return check(s, dbg);
+}
+
+int gsb_rasterizer_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix,
+                                unsigned char* present, void* stream) {
+    (void)projmatrix;   // the reference's test only uses the view-space depth (auxiliary.h:152-154)
+    launch_mark_visible(P, means3D, viewmatrix, reinterpret_cast<bool*>(present), (cudaStream_t)stream);
+    GSB_CUDA_OK(cudaGetLastError());
+    return GSB_OK;
+}
+
+int gsb_rasterizer_state(int P, int width, int height, int R, char* geom_buffer, char* binning_buffer,
+                         char* image_buffer, gsb_state_view* out) {
+    if (!out || !geom_buffer || !image_buffer) return gsb_fail_msg("gsb_rasterizer_state: invalid argument");
+    const int grid_x = (width + GSB_TILE - 1) / GSB_TILE, grid_y = (height + GSB_TILE - 1) / GSB_TILE;
+    const int tiles = grid_x * grid_y;
+    GeomWs g; g.carve(geom_buffer, (size_t)P);
+    ImageWs im; im.carve(image_buffer, (size_t)width * height, (size_t)tiles);
+    const int npass = (gsb_tile_bits((uint32_t)tiles) + 7) / 8;
+    const int fin = (npass > 0 ? npass : 1) & 1;
+    memset(out, 0, sizeof(*out));
+    out->radii = g.radii; out->depths = g.depths; out->tiles_touched = g.tiles_touched;
+    out->recs = reinterpret_cast<const float*>(g.recs); out->cov3D = g.cov3D; out->clamped = g.clamped;
+    out->depth_order = g.pvals[0];
+    if (binning_buffer && R > 0) {
+        BinWs b; b.carve(binning_buffer, (size_t)R);
+        out->point_list = b.rvals[fin]; out->point_list_tiles = b.rkeys[fin];
+    }
+    out->ranges = reinterpret_cast<const uint32_t*>(im.ranges); out->n_contrib = im.n_contrib; out->final_T = im.final_T;
+    out->tile_max = im.tile_max; out->counters = &g.ctrl->num_rendered;
+    return GSB_OK;
+}
+
+int gsb_rasterizer_sorted_keys(int P, int width, int height, int R, char* geom_buffer, char* binning_buffer,
+                               uint64_t* dev_keys_out, void* stream) {
+    if (R <= 0) return GSB_OK;
+    const int grid_x = (width + GSB_TILE - 1) / GSB_TILE, grid_y = (height + GSB_TILE - 1) / GSB_TILE;
+    const int npass = (gsb_tile_bits((uint32_t)(grid_x * grid_y)) + 7) / 8;
+    const int fin = (npass > 0 ? npass : 1) & 1;
+    GeomWs g; g.carve(geom_buffer, (size_t)P);
+    BinWs b; b.carve(binning_buffer, (size_t)R);
+    sorted_keys_kernel<<<gsb_div_up(R, 256), 256, 0, (cudaStream_t)stream>>>(b.rkeys[fin], b.rvals[fin], g.depths, (uint32_t)R,
+                                                                           dev_keys_out);
+    GSB_CUDA_OK(cudaGetLastError());
+    return GSB_OK;
+}
+
+int gsb_image_float_to_int(const float* dev_src, uint32_t* dev_fb, int w, int h, void* stream) {
+    launch_image_float_to_int(dev_src, dev_fb, w, h, (cudaStream_t)stream);
+    GSB_CUDA_OK(cudaGetLastError());
+    return GSB_OK;
+}
+
+int gsb_image_int_to_loss(const uint32_t* dev_truth, const float* dev_rasterized, float* dev_loss, int w, int h,
+                          void* stream) {
+    launch_image_int_to_loss(dev_truth, dev_rasterized, dev_loss, w, h, (cudaStream_t)stream);
+    GSB_CUDA_OK(cudaGetLastError());
+    return GSB_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,489 @@
+// C ABI of the trainer level: gsb_trainer_*.  Host orchestration counterpart of Trainer::train /
+// Trainer::render (reference src/Trainer.cu:148-216,252-543).
+//
+// Differences in mechanism (not in results):
+//   * workspaces live in grow-only arenas: no cudaMalloc / cudaFree per view (T:335-337,422-424)
+//   * camera constants are uploaded once per set_truths, not four blocking copies per view (T:317-326)
+//   * no host synchronisation inside an iteration: R stays on the device, the binning arena is sized
+//     from a high-water mark and an overflow (detected at the end of the iteration through a pinned
+//     host mirror of every view's R) grows the arena and re-runs the iteration before any parameter
+//     was touched
+//   * loss, per-view gradient buffers, their nine memsets and accumulateGradients are fused into the
+//     render-backward prologue and the preprocess-backward epilogue
+//   * densify runs on the GPU (classify + scan + scatter) instead of a D2H / CPU / H2D round trip.
+
+#include "workspace.cuh"
+#include "trainer_kernels.cuh"
+#include "../../include/gsb.h"
+
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+#include <vector>
+
+struct gsb_trainer {
+    int W = 0, H = 0, grid_x = 0, grid_y = 0, tiles = 0, tile_bits = 0;
+    cudaStream_t stream = nullptr;
+
+    // bound model (canonical storage: the caller's ModelSplatsDevice arrays)
+    int count = 0, capacity = 0, D = 0, M = 0;
+    float *loc = nullptr, *shs = nullptr, *scales = nullptr, *opac = nullptr, *rot = nullptr;
+
+    // truths
+    std::vector<const uint32_t*> truthW, truthB;
+    std::vector<gsb_camera> cams;
+    gsb_camera* d_cams = nullptr;
+    size_t d_cams_cap = 0;
+    gsb_camera* d_pcam = nullptr;     // camera slot of Trainer::render
+    int total_cameras = 0;
+    float* d_bg = nullptr;            // white rgb, black rgb
+
+    // arenas
+    char* geom = nullptr; size_t geom_P = 0; GeomWs g;
+    char* bin = nullptr; uint32_t r_cap = 0; BinWs b;
+    char* img = nullptr; ImageWs im;
+    float* rendered = nullptr;        // [3][H][W]
+    // preview arena (Trainer::render at another resolution)
+    char* pimg = nullptr; size_t pimg_bytes = 0; float* pcolor = nullptr; size_t pcolor_floats = 0;
+
+    float* avg_own = nullptr; size_t avg_own_floats = 0;
+    float* avg_ext = nullptr;
+    uint32_t epoch = 0;
+    uint32_t* h_R = nullptr; size_t h_R_cap = 0;   // pinned mirrors of every view's R
+
+    // densify scratch
+    uint8_t* flags = nullptr; uint32_t *keep_idx = nullptr, *aux_idx = nullptr, *totals = nullptr, *dens_ticket = nullptr;
+    unsigned long long* dens_lb = nullptr; size_t dens_P = 0;
+    bool plan_valid = false;
+    gsb_project_params plan_params;
+    uint32_t n_keep = 0, n_split_done = 0, n_clone_done = 0;
+
+    gsb_allreduce_fn allreduce = nullptr; void* allreduce_user = nullptr;
+    bool loss_on = false; double* d_loss = nullptr;
+    int fwd_ppt = 2, bwd_ppt = 2;
+    gsb_trainer_stats stats;
+};
+
+namespace {
+
+float* avg_ptr(gsb_trainer* t) { return t->avg_ext ? t->avg_ext : t->avg_own; }
+size_t grad_floats(const gsb_trainer* t) { return (size_t)t->count * (12 + 3 * (size_t)t->M); }
+
+int ensure_geom(gsb_trainer* t, size_t P) {
+    if (t->geom && P <= t->geom_P) { t->g.carve(t->geom, t->geom_P); return GSB_OK; }
+    if (t->geom) GSB_CUDA_OK(cudaFree(t->geom));
+    const size_t cap = P + P / 8 + 1024;
+    const size_t bytes = GeomWs::required(cap);
+    GSB_CUDA_OK(cudaMalloc(&t->geom, bytes));
+    GSB_CUDA_OK(cudaMemsetAsync(t->geom, 0, bytes, t->stream));   // look-back words and grad scratch start at zero
+    t->geom_P = cap;
+    t->g.carve(t->geom, cap);
+    return GSB_OK;
+}
+
+int ensure_bin(gsb_trainer* t, uint32_t r_cap) {
+    if (t->bin && r_cap <= t->r_cap) return GSB_OK;
+    if (t->bin) GSB_CUDA_OK(cudaFree(t->bin));
+    const size_t bytes = BinWs::required(r_cap);
+    GSB_CUDA_OK(cudaMalloc(&t->bin, bytes));
+    GSB_CUDA_OK(cudaMemsetAsync(t->bin, 0, bytes, t->stream));
+    t->r_cap = r_cap;
+    t->b.carve(t->bin, r_cap);
+    return GSB_OK;
+}
+
+int ensure_avg(gsb_trainer* t) {
+    const size_t n = grad_floats(t);
+    if (t->avg_ext || n <= t->avg_own_floats) return GSB_OK;
+    if (t->avg_own) GSB_CUDA_OK(cudaFree(t->avg_own));
+    GSB_CUDA_OK(cudaMalloc(&t->avg_own, (n + n / 8 + 256) * sizeof(float)));
+    t->avg_own_floats = n + n / 8 + 256;
+    return GSB_OK;
+}
+
+// forward half of one view pass; returns the number of kernels launched
+int forward_pass(gsb_trainer* t, const float* view, const float* projview, const float* campos, float tanx, float tany,
+                 float scale_modifier, const float* bg, int W, int H, ImageWs& im, float* out_color, uint32_t* h_R) {
+    cudaStream_t s = t->stream;
+    const int grid_x = (W + GSB_TILE - 1) / GSB_TILE, grid_y = (H + GSB_TILE - 1) / GSB_TILE;
+    const int tiles = grid_x * grid_y;
+    const int P = t->count;
+    GSB_CUDA_OK(cudaMemsetAsync(t->g.ctrl, 0, sizeof(GsbCtrl), s));
+    GSB_CUDA_OK(cudaMemsetAsync(im.ranges, 0, (size_t)tiles * sizeof(uint2), s));
+
+    PreprocessArgs pa;
+    pa.P = P; pa.D = t->D; pa.M = t->M;
+    pa.means3D = t->loc; pa.scales = t->scales; pa.scale_modifier = scale_modifier; pa.rotations = t->rot;
+    pa.opacities = t->opac; pa.shs = t->shs; pa.cov3D_precomp = nullptr; pa.colors_precomp = nullptr;
+    pa.viewmatrix = view; pa.projmatrix = projview; pa.cam_pos = campos;
+    pa.W = W; pa.H = H; pa.tan_fovx = tanx; pa.tan_fovy = tany;
+    pa.focal_y = H / (2.0f * tany);
+    pa.focal_x = W / (2.0f * tanx);
+    pa.grid_x = grid_x; pa.grid_y = grid_y; pa.prefiltered = 0;
+    pa.radii = t->g.radii; pa.radii_user = nullptr; pa.depths = t->g.depths; pa.tiles_touched = t->g.tiles_touched;
+    pa.recs = t->g.recs; pa.cov3D = t->g.cov3D; pa.clamped = t->g.clamped;
+    pa.sort_keys = t->g.pkeys[0]; pa.sort_vals = t->g.pvals[0];
+    launch_preprocess_fwd(pa, s);
+
+    BinningArgs ba;
+    ba.P = P; ba.r_cap = t->r_cap; ba.grid_x = grid_x; ba.grid_y = grid_y; ba.tile_bits = gsb_tile_bits((uint32_t)tiles);
+    ba.radii = t->g.radii; ba.tiles_touched = t->g.tiles_touched; ba.recs = t->g.recs;
+    ba.pkeys[0] = t->g.pkeys[0]; ba.pkeys[1] = t->g.pkeys[1]; ba.pvals[0] = t->g.pvals[0]; ba.pvals[1] = t->g.pvals[1];
+    ba.offsets = t->g.offsets;
+    ba.rkeys[0] = t->b.rkeys[0]; ba.rkeys[1] = t->b.rkeys[1]; ba.rvals[0] = t->b.rvals[0]; ba.rvals[1] = t->b.rvals[1];
+    ba.ranges = im.ranges; ba.epoch = &t->epoch; ba.ctrl = t->g.ctrl; ba.num_rendered_host = h_R;
+    ba.lookback = t->g.lookback; ba.lookback_tiles = (uint32_t)GeomWs::lookback_tiles(t->geom_P);
+    launch_binning_depth_and_scan(ba, s);
+    ba.lookback = t->b.lookback; ba.lookback_tiles = (uint32_t)BinWs::lookback_tiles(t->r_cap);
+    const int fin = launch_binning_emit_and_sort(ba, s);
+    const int npass = std::max(1, (ba.tile_bits + 7) / 8);
+
+    RenderFwdArgs ra;
+    ra.W = W; ra.H = H; ra.grid_x = grid_x; ra.grid_y = grid_y;
+    ra.ranges = im.ranges; ra.point_list = t->b.rvals[fin]; ra.recs = t->g.recs; ra.bg = bg;
+    ra.out_color = out_color; ra.final_T = im.final_T; ra.n_contrib = im.n_contrib; ra.tile_max = im.tile_max;
+    ra.ppt = t->fwd_ppt;
+    launch_render_fwd(ra, s);
+    t->stats.kernel_launches += 1 + 1 + 4 + 1 + 1 + 1 + npass + 1 + 1;
+    GSB_CUDA_OK(cudaGetLastError());
+    return fin + 100;   // >= 100: success, low digit = final buffer
+}
+
+}  // namespace
+
+extern "C" {
+
+int gsb_trainer_create(gsb_trainer** out, int width, int height, void* stream) {
+    if (!out || width <= 0 || height <= 0) return gsb_fail_msg("gsb_trainer_create: invalid argument");
+    int ndev = 0;
+    GSB_CUDA_OK(cudaGetDeviceCount(&ndev));
+    if (ndev == 0) return gsb_fail_msg("gsb_trainer_create: no CUDA device (this library has no CPU path)");
+    gsb_trainer* t = new gsb_trainer();
+    memset(&t->stats, 0, sizeof(t->stats));
+    t->W = width; t->H = height;
+    t->grid_x = (width + GSB_TILE - 1) / GSB_TILE; t->grid_y = (height + GSB_TILE - 1) / GSB_TILE;
+    t->tiles = t->grid_x * t->grid_y;
+    t->tile_bits = gsb_tile_bits((uint32_t)t->tiles);
+    t->stream = (cudaStream_t)stream;
+    const float bg[6] = {1.f, 1.f, 1.f, 0.f, 0.f, 0.f};
+    GSB_CUDA_OK(cudaMalloc(&t->d_bg, sizeof(bg)));
+    GSB_CUDA_OK(cudaMemcpy(t->d_bg, bg, sizeof(bg), cudaMemcpyHostToDevice));
+    const size_t N = (size_t)width * height;
+    GSB_CUDA_OK(cudaMalloc(&t->img, ImageWs::required(N, (size_t)t->tiles)));
+    t->im.carve(t->img, N, (size_t)t->tiles);
+    GSB_CUDA_OK(cudaMalloc(&t->rendered, 3 * N * sizeof(float)));
+    GSB_CUDA_OK(cudaMalloc(&t->d_loss, sizeof(double)));
+    GSB_CUDA_OK(cudaMemset(t->d_loss, 0, sizeof(double)));
+    GSB_CUDA_OK(cudaMalloc(&t->totals, 4 * sizeof(uint32_t)));
+    GSB_CUDA_OK(cudaMalloc(&t->dens_ticket, sizeof(uint32_t)));
+    GSB_CUDA_OK(cudaMalloc(&t->d_pcam, sizeof(gsb_camera)));
+    *out = t;
+    return GSB_OK;
+}
+
+int gsb_trainer_destroy(gsb_trainer* t) {
+    if (!t) return GSB_OK;
+    cudaStreamSynchronize(t->stream);
+    cudaFree(t->d_cams); cudaFree(t->d_pcam); cudaFree(t->d_bg); cudaFree(t->geom); cudaFree(t->bin); cudaFree(t->img); cudaFree(t->rendered);
+    cudaFree(t->pimg); cudaFree(t->pcolor); cudaFree(t->avg_own); cudaFree(t->d_loss);
+    cudaFree(t->flags); cudaFree(t->keep_idx); cudaFree(t->aux_idx); cudaFree(t->totals); cudaFree(t->dens_ticket);
+    cudaFree(t->dens_lb);
+    if (t->h_R) cudaFreeHost(t->h_R);
+    delete t;
+    return GSB_OK;
+}
+
+int gsb_trainer_bind_model(gsb_trainer* t, int count, int capacity, int shDegree, int shCoeffs, float* devLocations,
+                           float* devShs, float* devScales, float* devOpacities, float* devRotations) {
+    if (!t || count < 0 || shCoeffs <= 0) return gsb_fail_msg("gsb_trainer_bind_model: invalid argument");
+    t->count = count; t->capacity = capacity; t->D = shDegree; t->M = shCoeffs;
+    t->loc = devLocations; t->shs = devShs; t->scales = devScales; t->opac = devOpacities; t->rot = devRotations;
+    t->plan_valid = false;
+    return GSB_OK;
+}
+
+int gsb_trainer_set_truths(gsb_trainer* t, int n, const uint32_t* const* devW, const uint32_t* const* devB,
+                           const gsb_camera* cameras, int total_cameras) {
+    if (!t || n < 0 || (n > 0 && (!devW || !devB || !cameras))) return gsb_fail_msg("gsb_trainer_set_truths: invalid argument");
+    t->truthW.assign(devW, devW + n);
+    t->truthB.assign(devB, devB + n);
+    t->cams.assign(cameras, cameras + n);
+    t->total_cameras = total_cameras > 0 ? total_cameras : n;
+    if ((size_t)n > t->d_cams_cap) {
+        if (t->d_cams) GSB_CUDA_OK(cudaFree(t->d_cams));
+        GSB_CUDA_OK(cudaMalloc(&t->d_cams, (size_t)n * sizeof(gsb_camera)));
+        t->d_cams_cap = (size_t)n;
+    }
+    if (n > 0) {
+        GSB_CUDA_OK(cudaMemcpyAsync(t->d_cams, cameras, (size_t)n * sizeof(gsb_camera), cudaMemcpyHostToDevice, t->stream));
+        GSB_CUDA_OK(cudaStreamSynchronize(t->stream));   // `cameras` may be a temporary
+    }
+    if ((size_t)2 * n > t->h_R_cap) {
+        if (t->h_R) GSB_CUDA_OK(cudaFreeHost(t->h_R));
+        GSB_CUDA_OK(cudaHostAlloc(&t->h_R, (size_t)2 * n * sizeof(uint32_t), cudaHostAllocMapped));
+        t->h_R_cap = (size_t)2 * n;
+    }
+    return GSB_OK;
+}
+
+int gsb_trainer_set_grad_buffer(gsb_trainer* t, float* dev_avg) {
+    if (!t) return gsb_fail_msg("gsb_trainer_set_grad_buffer: null trainer");
+    t->avg_ext = dev_avg;
+    return GSB_OK;
+}
+size_t gsb_trainer_grad_floats(const gsb_trainer* t) { return t ? grad_floats(t) : 0; }
+float* gsb_trainer_grad_buffer(gsb_trainer* t) { return t ? avg_ptr(t) : nullptr; }
+
+int gsb_trainer_set_allreduce(gsb_trainer* t, gsb_allreduce_fn fn, void* user) {
+    if (!t) return gsb_fail_msg("gsb_trainer_set_allreduce: null trainer");
+    t->allreduce = fn; t->allreduce_user = user;
+    return GSB_OK;
+}
+
+int gsb_trainer_set_options(gsb_trainer* t, int fwd_ppt, int bwd_ppt) {
+    if (!t) return gsb_fail_msg("gsb_trainer_set_options: null trainer");
+    if (fwd_ppt == 1 || fwd_ppt == 2 || fwd_ppt == 4) t->fwd_ppt = fwd_ppt;
+    if (bwd_ppt == 1 || bwd_ppt == 2 || bwd_ppt == 4) t->bwd_ppt = bwd_ppt;
+    return GSB_OK;
+}
+
+int gsb_trainer_enable_loss(gsb_trainer* t, int on) {
+    if (!t) return gsb_fail_msg("gsb_trainer_enable_loss: null trainer");
+    t->loss_on = on != 0;
+    return GSB_OK;
+}
+
+int gsb_trainer_get_stats(gsb_trainer* t, gsb_trainer_stats* out) {
+    if (!t || !out) return gsb_fail_msg("gsb_trainer_get_stats: invalid argument");
+    *out = t->stats;
+    return GSB_OK;
+}
+
+int gsb_trainer_accumulate(gsb_trainer* t) {
+    if (!t) return gsb_fail_msg("gsb_trainer_accumulate: null trainer");
+    if (t->truthW.empty()) {
+        gsb_fail_msg("Can't run training iteration, no truth data available!");   // src/Trainer.cu:253
+        return GSB_ERR_STATE;
+    }
+    if (t->count <= 0 || !t->loc) { gsb_fail_msg("gsb_trainer_accumulate: no model bound"); return GSB_ERR_STATE; }
+    cudaStream_t s = t->stream;
+    const int n = (int)t->truthW.size();
+    const int P = t->count;
+    if (int e = ensure_geom(t, (size_t)P)) return e;
+    if (int e = ensure_avg(t)) return e;
+    if (t->r_cap == 0) {
+        if (int e = ensure_bin(t, (uint32_t)std::min<size_t>(0x7FFFFFF0u, std::max<size_t>((size_t)1 << 20, (size_t)P * 6)))) return e;
+    }
+    float* avg = avg_ptr(t);
+    const float S = 2.0f * (float)t->total_cameras;
+    t->stats.retries = 0;
+
+    for (int attempt = 0; attempt < 4; attempt++) {
+        GSB_CUDA_OK(cudaMemsetAsync(avg, 0, grad_floats(t) * sizeof(float), s));
+        if (t->loss_on) GSB_CUDA_OK(cudaMemsetAsync(t->d_loss, 0, sizeof(double), s));
+        for (int i = 0; i < 2 * n; i++) {
+            const bool white = i < n;
+            const int cam = i % n;
+            const uint32_t* truth = white ? t->truthW[cam] : t->truthB[cam];
+            const gsb_camera* dc = t->d_cams + cam;
+            const float* bg = t->d_bg + (white ? 0 : 3);
+            const int r = forward_pass(t, dc->view, dc->projview, dc->location, t->cams[cam].tan_fovx, t->cams[cam].tan_fovy,
+                                       1.0f, bg, t->W, t->H, t->im, t->rendered, t->h_R + i);
+            if (r < 100) return r;
+            const int fin = r - 100;
+            if (t->loss_on) {
+                launch_sum_sq_residual(truth, t->rendered, t->W, t->H, t->d_loss, s);
+                t->stats.kernel_launches++;
+            }
+            RenderBwdArgs rb;
+            rb.W = t->W; rb.H = t->H; rb.grid_x = t->grid_x; rb.grid_y = t->grid_y;
+            rb.ranges = t->im.ranges; rb.point_list = t->b.rvals[fin]; rb.recs = t->g.recs; rb.bg = bg;
+            rb.final_T = t->im.final_T; rb.n_contrib = t->im.n_contrib; rb.tile_max = t->im.tile_max;
+            rb.dL_dpix = nullptr; rb.truth = truth; rb.rendered = t->rendered; rb.grads = t->g.grads; rb.ppt = t->bwd_ppt;
+            launch_render_bwd(rb, s);
+
+            PreprocessBwdArgs pb;
+            memset(&pb, 0, sizeof(pb));
+            pb.P = P; pb.D = t->D; pb.M = t->M;
+            pb.means3D = t->loc; pb.scales = t->scales; pb.scale_modifier = 1.0f; pb.rotations = t->rot; pb.shs = t->shs;
+            pb.cov3D = t->g.cov3D; pb.cov3D_is_precomp = 0; pb.colors_precomp = 0;
+            pb.viewmatrix = dc->view; pb.projmatrix = dc->projview; pb.cam_pos = dc->location;
+            pb.tan_fovx = t->cams[cam].tan_fovx; pb.tan_fovy = t->cams[cam].tan_fovy;
+            pb.focal_y = t->H / (2.0f * pb.tan_fovy);
+            pb.focal_x = t->W / (2.0f * pb.tan_fovx);
+            pb.radii = t->g.radii; pb.clamped = t->g.clamped; pb.grads = t->g.grads;
+            pb.avg = avg; pb.samples = S;
+            launch_preprocess_bwd(pb, s);
+            t->stats.kernel_launches += 2;
+        }
+        GSB_CUDA_OK(cudaGetLastError());
+        // one synchronisation per iteration: learn every view's R, detect arena overflow
+        GSB_CUDA_OK(cudaStreamSynchronize(s));
+        uint32_t maxR = 0;
+        long long total = 0;
+        for (int i = 0; i < 2 * n; i++) { maxR = std::max(maxR, t->h_R[i]); total += t->h_R[i]; }
+        t->stats.rendered_total = total;
+        t->stats.views = 2 * n;
+        if (maxR <= t->r_cap) {
+            if (t->loss_on) GSB_CUDA_OK(cudaMemcpy(&t->stats.sum_sq_residual, t->d_loss, sizeof(double), cudaMemcpyDeviceToHost));
+            return GSB_OK;
+        }
+        // Some view did not fit: its gradients are incomplete.  Nothing but the running means and the
+        // (self-clearing) scratch was written, so grow the arena and redo the iteration.
+        t->stats.retries++;
+        GSB_CUDA_OK(cudaMemsetAsync(t->g.grads, 0, (size_t)t->geom_P * sizeof(GradRec), s));
+        if (int e = ensure_bin(t, (uint32_t)std::min<size_t>(0x7FFFFFF0u, (size_t)maxR + maxR / 4 + 4096))) return e;
+    }
+    gsb_fail_msg("gsb_trainer_accumulate: binning arena kept overflowing");
+    return GSB_ERR_STATE;
+}
+
+int gsb_trainer_apply(gsb_trainer* t, const gsb_project_params* p) {
+    if (!t || !p) return gsb_fail_msg("gsb_trainer_apply: invalid argument");
+    ApplyArgs a;
+    a.locations = t->loc; a.shs = t->shs; a.scales = t->scales; a.opacities = t->opac; a.rotations = t->rot;
+    a.avg = avg_ptr(t);
+    a.lrLocation = p->lrLocation; a.lrSh = p->lrSh; a.lrScale = p->lrScale; a.lrOpacity = p->lrOpacity;
+    a.lrRotation = p->lrRotation; a.maxScale = p->paramScaleMax; a.M = t->M; a.count = t->count;
+    launch_apply_gradients(a, t->stream);
+    t->stats.kernel_launches++;
+    GSB_CUDA_OK(cudaGetLastError());
+    return GSB_OK;
+}
+
+int gsb_trainer_densify_plan(gsb_trainer* t, const gsb_project_params* p, int* new_count) {
+    if (!t || !p || !new_count) return gsb_fail_msg("gsb_trainer_densify_plan: invalid argument");
+    cudaStream_t s = t->stream;
+    const size_t P = (size_t)t->count;
+    if (P > t->dens_P) {
+        cudaFree(t->flags); cudaFree(t->keep_idx); cudaFree(t->aux_idx); cudaFree(t->dens_lb);
+        const size_t cap = P + P / 4 + 1024;
+        GSB_CUDA_OK(cudaMalloc(&t->flags, cap));
+        GSB_CUDA_OK(cudaMalloc(&t->keep_idx, cap * sizeof(uint32_t)));
+        GSB_CUDA_OK(cudaMalloc(&t->aux_idx, cap * sizeof(uint32_t)));
+        const size_t lbw = ((cap + 1023) / 1024 + 1) * 4;
+        GSB_CUDA_OK(cudaMalloc(&t->dens_lb, lbw * sizeof(unsigned long long)));
+        GSB_CUDA_OK(cudaMemsetAsync(t->dens_lb, 0, lbw * sizeof(unsigned long long), s));
+        t->dens_P = cap;
+    }
+    GSB_CUDA_OK(cudaMemsetAsync(t->dens_ticket, 0, sizeof(uint32_t), s));
+    GSB_CUDA_OK(cudaMemsetAsync(t->totals, 0, 4 * sizeof(uint32_t), s));
+    DensifyArgs a;
+    a.locations = t->loc; a.shs = t->shs; a.scales = t->scales; a.opacities = t->opac; a.rotations = t->rot;
+    a.avg = avg_ptr(t); a.M = t->M; a.count = t->count;
+    a.cullOpacity = p->paramCullOpacity; a.cullSize = p->paramCullSize; a.densifyVariance = p->paramDensifyVariance;
+    a.splitSize = p->paramSplitSize; a.splitDistance = p->paramSplitDistance; a.splitScale = p->paramSplitScale;
+    a.cloneDistance = p->paramCloneDistance;
+    a.flags = t->flags; a.keep_idx = t->keep_idx; a.aux_idx = t->aux_idx; a.totals = t->totals;
+    a.lookback = t->dens_lb; a.epoch = ++t->epoch; a.ticket = t->dens_ticket;
+    launch_densify_classify_scan(a, s);
+    t->stats.kernel_launches++;
+    uint32_t tot[3] = {0, 0, 0};
+    GSB_CUDA_OK(cudaMemcpyAsync(tot, t->totals, sizeof(tot), cudaMemcpyDeviceToHost, s));
+    GSB_CUDA_OK(cudaStreamSynchronize(s));
+    // The reference appends while count < capacity, counting before the cull compaction
+    // (src/Trainer.cu:460,500): splits first, then clones.
+    const long long room = std::max(0LL, (long long)t->capacity - (long long)t->count);
+    t->n_keep = tot[0];
+    t->n_split_done = (uint32_t)std::min<long long>(tot[1], room);
+    t->n_clone_done = (uint32_t)std::min<long long>(tot[2], room - t->n_split_done);
+    t->plan_params = *p;
+    t->plan_valid = true;
+    *new_count = (int)(t->n_keep + t->n_split_done + t->n_clone_done);
+    return GSB_OK;
+}
+
+int gsb_trainer_densify_commit(gsb_trainer* t, float* devLocations, float* devShs, float* devScales, float* devOpacities,
+                               float* devRotations) {
+    if (!t || !t->plan_valid) { gsb_fail_msg("gsb_trainer_densify_commit: no plan"); return GSB_ERR_STATE; }
+    const gsb_project_params* p = &t->plan_params;
+    DensifyArgs a;
+    a.locations = t->loc; a.shs = t->shs; a.scales = t->scales; a.opacities = t->opac; a.rotations = t->rot;
+    a.avg = avg_ptr(t); a.M = t->M; a.count = t->count;
+    a.cullOpacity = p->paramCullOpacity; a.cullSize = p->paramCullSize; a.densifyVariance = p->paramDensifyVariance;
+    a.splitSize = p->paramSplitSize; a.splitDistance = p->paramSplitDistance; a.splitScale = p->paramSplitScale;
+    a.cloneDistance = p->paramCloneDistance;
+    a.flags = t->flags; a.keep_idx = t->keep_idx; a.aux_idx = t->aux_idx; a.totals = t->totals;
+    a.lookback = t->dens_lb; a.epoch = t->epoch; a.ticket = t->dens_ticket;
+    DensifyOut o;
+    o.locations = devLocations; o.shs = devShs; o.scales = devScales; o.opacities = devOpacities; o.rotations = devRotations;
+    o.n_keep = t->n_keep; o.n_split_done = t->n_split_done; o.n_clone_done = t->n_clone_done;
+    launch_densify_scatter(a, o, t->stream);
+    t->stats.kernel_launches++;
+    GSB_CUDA_OK(cudaGetLastError());
+    GSB_CUDA_OK(cudaStreamSynchronize(t->stream));   // the caller frees the old arrays next
+    t->count = (int)(t->n_keep + t->n_split_done + t->n_clone_done);
+    t->loc = devLocations; t->shs = devShs; t->scales = devScales; t->opac = devOpacities; t->rot = devRotations;
+    t->plan_valid = false;
+    return GSB_OK;
+}
+
+int gsb_trainer_train(gsb_trainer* t, const gsb_project_params* p, int densify, int* new_count) {
+    if (!t || !p) return gsb_fail_msg("gsb_trainer_train: invalid argument");
+    if (int e = gsb_trainer_accumulate(t)) return e;
+    if (t->allreduce) {
+        if (int e = t->allreduce(avg_ptr(t), grad_floats(t), t->stream, t->allreduce_user)) {
+            gsb_fail_msg("gsb_trainer_train: all-reduce hook failed");
+            return e;
+        }
+    }
+    if (int e = gsb_trainer_apply(t, p)) return e;
+    if (densify) {
+        if (!new_count) return gsb_fail_msg("gsb_trainer_train: densify needs new_count");
+        return gsb_trainer_densify_plan(t, p, new_count);
+    }
+    return GSB_OK;
+}
+
+int gsb_trainer_render(gsb_trainer* t, uint32_t* dev_frame_buffer, int width, int height, float splat_scale,
+                       const gsb_camera* camera) {
+    if (!t || !dev_frame_buffer || !camera || width <= 0 || height <= 0) return gsb_fail_msg("gsb_trainer_render: invalid argument");
+    cudaStream_t s = t->stream;
+    const size_t N = (size_t)width * height;
+    const int tiles = ((width + GSB_TILE - 1) / GSB_TILE) * ((height + GSB_TILE - 1) / GSB_TILE);
+    if (int e = ensure_geom(t, (size_t)std::max(t->count, 1))) return e;
+    if (t->r_cap == 0) {
+        if (int e = ensure_bin(t, (uint32_t)std::max<size_t>((size_t)1 << 20, (size_t)t->count * 6))) return e;
+    }
+    // preview arena: the training image workspace is reused when the size matches (T:159-167)
+    ImageWs im;
+    float* color;
+    if (width == t->W && height == t->H) {
+        im = t->im; color = t->rendered;
+    } else {
+        const size_t need = ImageWs::required(N, (size_t)tiles);
+        if (need > t->pimg_bytes) {
+            cudaFree(t->pimg);
+            GSB_CUDA_OK(cudaMalloc(&t->pimg, need));
+            t->pimg_bytes = need;
+        }
+        if (3 * N > t->pcolor_floats) {
+            cudaFree(t->pcolor);
+            GSB_CUDA_OK(cudaMalloc(&t->pcolor, 3 * N * sizeof(float)));
+            t->pcolor_floats = 3 * N;
+        }
+        im.carve(t->pimg, N, (size_t)tiles);
+        color = t->pcolor;
+    }
+    gsb_camera* dc = t->d_pcam;
+    GSB_CUDA_OK(cudaMemcpyAsync(dc, camera, sizeof(gsb_camera), cudaMemcpyHostToDevice, s));
+    for (int attempt = 0; attempt < 4; attempt++) {
+        uint32_t* hR = nullptr;
+        if (!t->h_R) {
+            GSB_CUDA_OK(cudaHostAlloc(&t->h_R, 2 * sizeof(uint32_t), cudaHostAllocMapped));
+            t->h_R_cap = 2;
+        }
+        hR = t->h_R;
+        const int r = forward_pass(t, dc->view, dc->projview, dc->location, camera->tan_fovx, camera->tan_fovy, splat_scale,
+                                   t->d_bg + 3, width, height, im, color, hR);
+        if (r < 100) return r;
+        launch_image_float_to_int(color, dev_frame_buffer, width, height, s);
+        t->stats.kernel_launches++;
+        GSB_CUDA_OK(cudaStreamSynchronize(s));   // the reference ends render() with a device sync (T:215)
+        if (t->count == 0 || hR[0] <= t->r_cap) break;
+        if (int e = ensure_bin(t, (uint32_t)std::min<size_t>(0x7FFFFFF0u, (size_t)hR[0] + hR[0] / 4 + 4096))) return e;
+    }
+    return GSB_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,196 @@
+/* gsb.h -- C ABI of the B200-native Gaussian-Splatterer training hot path (libgsb200.so).
+ *
+ * Plain pointers and sizes only; every pointer named dev* / documented "device" is CUDA device
+ * memory of the current device.  All functions return 0 on success or a non-zero error code and
+ * leave a message retrievable with gsb_last_error().  Nothing here falls back to the CPU: without
+ * a CUDA device every compute entry point fails.
+ *
+ * Each entry point names the reference interface it replaces (paths relative to the reference
+ * repository osreboot/Gaussian-Splatterer @ 5ca294e):
+ *   R  = lib/diff-gaussian-rasterization/cuda_rasterizer/rasterizer.h
+ *   RI = lib/diff-gaussian-rasterization/cuda_rasterizer/rasterizer_impl.cu
+ *   T  = src/Trainer.cu, TH = src/Trainer.cuh, P = src/Project.h
+ * The C++ headers in include/compat/ wrap this ABI in the reference's own class signatures.
+ */
+#ifndef GSB_H_INCLUDED
+#define GSB_H_INCLUDED
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GSB_OK 0
+#define GSB_ERR_CUDA 1        /* a CUDA call failed (message holds cudaGetErrorString) */
+#define GSB_ERR_ARG 2         /* invalid argument */
+#define GSB_ERR_STATE 3       /* call order / missing data (e.g. train() without truth frames) */
+#define GSB_ERR_ALLOC 4       /* a caller-supplied allocator returned NULL */
+
+const char* gsb_last_error(void);
+int gsb_version(void);
+
+/* Workspace allocator: the callee asks for `bytes`, the caller returns device memory it owns.
+ * Replaces the three std::function<char*(size_t)> arguments of Rasterizer::forward (R:34-36). */
+typedef char* (*gsb_alloc_fn)(size_t bytes, void* user);
+
+/* ---- rasterizer level ------------------------------------------------------------------- */
+
+/* Rasterizer::forward (R:33-56, RI:198-336).  Same arguments in the same order; the three
+ * std::function allocators become (fn, user) pairs, bool becomes int, the return value moves to
+ * *num_rendered and `stream` (a cudaStream_t, NULL = legacy default stream) is added.
+ * One host synchronisation is unavoidable: the binning workspace is sized from R (RI:281-285). */
+int gsb_rasterizer_forward(gsb_alloc_fn geometry_alloc, void* geometry_user,
+                           gsb_alloc_fn binning_alloc, void* binning_user,
+                           gsb_alloc_fn image_alloc, void* image_user,
+                           int P, int D, int M,
+                           const float* background, int width, int height,
+                           const float* means3D, const float* shs, const float* colors_precomp,
+                           const float* opacities, const float* scales, float scale_modifier,
+                           const float* rotations, const float* cov3D_precomp,
+                           const float* viewmatrix, const float* projmatrix, const float* cam_pos,
+                           float tan_fovx, float tan_fovy, int prefiltered,
+                           float* out_color, int* radii, int debug, void* stream,
+                           int* num_rendered);
+
+/* Rasterizer::backward (R:58-83, RI:340-434).  Gradient outputs follow the reference exactly:
+ * dL_dmean2D / dL_dconic / dL_dopacity / dL_dcolor are accumulated into (caller pre-zeroes them,
+ * T:365-375); dL_dmean3D / dL_dcov3D / dL_dsh / dL_dscale / dL_drot are overwritten for visible
+ * splats only. */
+int gsb_rasterizer_backward(int P, int D, int M, int R,
+                            const float* background, int width, int height,
+                            const float* means3D, const float* shs, const float* colors_precomp,
+                            const float* scales, float scale_modifier, const float* rotations,
+                            const float* cov3D_precomp, const float* viewmatrix,
+                            const float* projmatrix, const float* campos,
+                            float tan_fovx, float tan_fovy, const int* radii,
+                            char* geom_buffer, char* binning_buffer, char* image_buffer,
+                            const float* dL_dpix,
+                            float* dL_dmean2D, float* dL_dconic, float* dL_dopacity,
+                            float* dL_dcolor, float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh,
+                            float* dL_dscale, float* dL_drot, int debug, void* stream);
+
+/* Rasterizer::markVisible (R:24-29, RI:141-153). */
+int gsb_rasterizer_mark_visible(int P, const float* means3D, const float* viewmatrix,
+                                const float* projmatrix, unsigned char* present, void* stream);
+
+/* Pixels-per-thread of the render kernels (1, 2 or 4); tuning knob, results do not depend on it. */
+void gsb_set_render_ppt(int fwd_ppt, int bwd_ppt);
+
+/* Read-only view into the private workspace layout after gsb_rasterizer_forward, for parity tests
+ * (counterpart of Geometry/Binning/ImageState::fromChunk, RI:155-194).  Device pointers. */
+typedef struct gsb_state_view {
+    const int* radii;                 /* [P] */
+    const float* depths;              /* [P] (valid where radii > 0) */
+    const uint32_t* tiles_touched;    /* [P] */
+    const float* recs;                /* [P][12]: x y conic.x conic.y | conic.z opacity r g | b depth idx radius */
+    const float* cov3D;               /* [P][6] */
+    const unsigned char* clamped;     /* [P] bit c = channel c clamped */
+    const uint32_t* depth_order;      /* [P] splat ids sorted by depth bits (culled last) */
+    const uint32_t* point_list;       /* [R] splat ids sorted by (tile, depth) */
+    const uint32_t* point_list_tiles; /* [R] tile id of each sorted entry */
+    const uint32_t* ranges;           /* [tiles][2] */
+    const uint32_t* n_contrib;        /* [H*W] */
+    const float* final_T;             /* [H*W] */
+    const uint32_t* tile_max;         /* [tiles] */
+    const uint32_t* counters;         /* [3]: R, visible, overflow */
+} gsb_state_view;
+int gsb_rasterizer_state(int P, int width, int height, int R, char* geom_buffer,
+                         char* binning_buffer, char* image_buffer, gsb_state_view* out);
+/* Materialise the reference's 64-bit sort keys (tile << 32 | depth bits, RI:102-104) of the
+ * sorted list into dev_keys_out[R]. */
+int gsb_rasterizer_sorted_keys(int P, int width, int height, int R, char* geom_buffer,
+                               char* binning_buffer, uint64_t* dev_keys_out, void* stream);
+
+/* ---- trainer level ---------------------------------------------------------------------- */
+
+/* The Project fields Trainer::train reads (P:26-39), in declaration order. */
+typedef struct gsb_project_params {
+    float lrLocation, lrSh, lrScale, lrOpacity, lrRotation;
+    float paramScaleMax;
+    float paramCullOpacity, paramCullSize, paramDensifyVariance;
+    float paramSplitSize, paramSplitDistance, paramSplitScale, paramCloneDistance;
+} gsb_project_params;
+
+/* What train() derives from a Camera per view (T:321-326,355-356): view = -lookAt,
+ * projview = perspective * view (both column-major), camera location, tan(fov/2). */
+typedef struct gsb_camera {
+    float view[16];
+    float projview[16];
+    float location[3];
+    float tan_fovx, tan_fovy;
+} gsb_camera;
+
+typedef struct gsb_trainer gsb_trainer;
+
+/* Trainer::Trainer / ~Trainer (T:103-146).  Resolution is a runtime parameter here (the
+ * reference fixes 1024x1024 at compile time, src/Config.h:13-14). */
+int gsb_trainer_create(gsb_trainer** out, int width, int height, void* stream);
+int gsb_trainer_destroy(gsb_trainer* t);
+
+/* Bind the five ModelSplatsDevice arrays (src/ModelSplatsDevice.h:8-19).  They stay the canonical
+ * parameter storage, owned by the caller; call again whenever `model` is replaced. */
+int gsb_trainer_bind_model(gsb_trainer* t, int count, int capacity, int shDegree, int shCoeffs,
+                           float* devLocations, float* devShs, float* devScales,
+                           float* devOpacities, float* devRotations);
+
+/* truthFrameBuffersW / truthFrameBuffersB / truthCameras (TH:52-54): n device RGBA8 frames per
+ * background, owned by the caller.  `total_cameras` is the camera count over ALL ranks (S = 2 *
+ * total_cameras scales the running means, T:419); pass n on a single GPU. */
+int gsb_trainer_set_truths(gsb_trainer* t, int n, const uint32_t* const* devW,
+                           const uint32_t* const* devB, const gsb_camera* cameras,
+                           int total_cameras);
+
+/* Optional caller-owned buffer for the 24*count running means
+ * [var | loc 3 | sh 3*shCoeffs | scale 3 | opacity | rot 4] so the caller can all-reduce it. */
+int gsb_trainer_set_grad_buffer(gsb_trainer* t, float* dev_avg);
+size_t gsb_trainer_grad_floats(const gsb_trainer* t);
+float* gsb_trainer_grad_buffer(gsb_trainer* t);
+
+/* Exchange step between accumulate and apply on multi-GPU runs: sum `count` floats at `dev`
+ * across ranks, in place, ordered after `stream`. */
+typedef int (*gsb_allreduce_fn)(float* dev, size_t count, void* stream, void* user);
+int gsb_trainer_set_allreduce(gsb_trainer* t, gsb_allreduce_fn fn, void* user);
+
+/* Trainer::train (T:252-543) split at the point where ranks exchange gradients:
+ *   accumulate = zero the means, then forward + loss + backward + accumulate of every local view
+ *   apply      = applyGradients (T:428-431)
+ *   train      = accumulate, all-reduce hook (if set), apply, optional densify plan
+ * With densify != 0 train() stops after gsb_trainer_densify_plan; the caller allocates arrays for
+ * *new_count splats and finishes with gsb_trainer_densify_commit (the reference reallocates the
+ * model the same way, T:540-541). */
+int gsb_trainer_accumulate(gsb_trainer* t);
+int gsb_trainer_apply(gsb_trainer* t, const gsb_project_params* p);
+int gsb_trainer_train(gsb_trainer* t, const gsb_project_params* p, int densify, int* new_count);
+int gsb_trainer_densify_plan(gsb_trainer* t, const gsb_project_params* p, int* new_count);
+int gsb_trainer_densify_commit(gsb_trainer* t, float* devLocations, float* devShs, float* devScales,
+                               float* devOpacities, float* devRotations);
+
+/* Trainer::render (T:148-216): black background, splatScale as scale_modifier, RGBA8 out. */
+int gsb_trainer_render(gsb_trainer* t, uint32_t* dev_frame_buffer, int width, int height,
+                       float splat_scale, const gsb_camera* camera);
+
+/* Monitoring / measurement (no reference counterpart). */
+typedef struct gsb_trainer_stats {
+    long long rendered_total;      /* sum of R over the view passes of the last accumulate */
+    long long visible_total;       /* sum of visible splats */
+    int views;                     /* view passes of the last accumulate */
+    int retries;                   /* accumulate re-runs caused by binning-capacity growth */
+    long long kernel_launches;     /* kernels launched by this trainer since creation */
+    double sum_sq_residual;        /* sum over views of sum(residual^2), if enabled */
+} gsb_trainer_stats;
+int gsb_trainer_get_stats(gsb_trainer* t, gsb_trainer_stats* out);
+int gsb_trainer_enable_loss(gsb_trainer* t, int on);
+/* Fuse the white and black pass of a camera (shared preprocess / sort / blend). 0 = off. */
+int gsb_trainer_set_options(gsb_trainer* t, int fwd_ppt, int bwd_ppt);
+
+/* Image helpers: imageFloatToInt / imageIntToLoss (T:19-44). */
+int gsb_image_float_to_int(const float* dev_src, uint32_t* dev_fb, int w, int h, void* stream);
+int gsb_image_int_to_loss(const uint32_t* dev_truth, const float* dev_rasterized, float* dev_loss,
+                          int w, int h, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GSB_H_INCLUDED */
