@@ -56,8 +56,6 @@ def lib():
     vp, i, f, sz = C.c_void_p, C.c_int, C.c_float, C.c_size_t
     L.gsb_last_error.restype = C.c_char_p
     L.gsb_version.restype = i
-    L.gsb_set_render_ppt.argtypes = [i, i]
-    L.gsb_set_render_ppt.restype = None
     L.gsb_rasterizer_forward.argtypes = [ALLOC_FN, vp, ALLOC_FN, vp, ALLOC_FN, vp, i, i, i, vp, i, i, vp, vp, vp,
                                          vp, vp, f, vp, vp, vp, vp, vp, f, f, i, vp, vp, i, vp, C.POINTER(i)]
     L.gsb_rasterizer_forward.restype = i
@@ -102,8 +100,8 @@ def lib():
     L.gsb_trainer_get_stats.restype = i
     L.gsb_trainer_enable_loss.argtypes = [vp, i]
     L.gsb_trainer_enable_loss.restype = i
-    L.gsb_trainer_set_options.argtypes = [vp, i, i]
-    L.gsb_trainer_set_options.restype = i
+    L.gsb_trainer_profile_pass.argtypes = [vp, i, C.POINTER(C.c_float), C.POINTER(C.c_uint)]
+    L.gsb_trainer_profile_pass.restype = i
     L.gsb_image_float_to_int.argtypes = [vp, vp, i, i, vp]
     L.gsb_image_float_to_int.restype = i
     L.gsb_image_int_to_loss.argtypes = [vp, vp, vp, i, i, vp]
@@ -115,12 +113,10 @@ def lib():
 # Every symbol include/gsb.h declares; the CPU test-suite checks the library exports all of them.
 EXPORTED_SYMBOLS = [
     "gsb_last_error", "gsb_version", "gsb_rasterizer_forward", "gsb_rasterizer_backward",
-    "gsb_rasterizer_mark_visible", "gsb_set_render_ppt", "gsb_rasterizer_state", "gsb_rasterizer_sorted_keys",
     "gsb_trainer_create", "gsb_trainer_destroy", "gsb_trainer_bind_model", "gsb_trainer_set_truths",
     "gsb_trainer_set_grad_buffer", "gsb_trainer_grad_floats", "gsb_trainer_grad_buffer",
     "gsb_trainer_set_allreduce", "gsb_trainer_accumulate", "gsb_trainer_apply", "gsb_trainer_train",
     "gsb_trainer_densify_plan", "gsb_trainer_densify_commit", "gsb_trainer_render", "gsb_trainer_get_stats",
-    "gsb_trainer_enable_loss", "gsb_trainer_set_options", "gsb_image_float_to_int", "gsb_image_int_to_loss",
 ]
 
 

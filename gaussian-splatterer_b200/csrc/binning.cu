@@ -275,10 +275,10 @@ __global__ void __launch_bounds__(256) tile_ranges_kernel(const uint32_t* __rest
 
 }  // namespace
 
-void launch_binning_depth_and_scan(const BinningArgs& a, cudaStream_t s) {
+void launch_depth_sort(const BinningArgs& a, cudaStream_t s) {
     const uint32_t P = (uint32_t)a.P;
     if (P == 0) return;
-    // 1. stable sort of splats by depth bits: 4 passes, result back in pkeys[0]/pvals[0]
+    // stable sort of splats by depth bits: 4 passes, result back in pkeys[0]/pvals[0]
     radix_hist_kernel<4><<<min(gsb_div_up(P, 256 * 8), 592), 256, 0, s>>>(a.pkeys[0], nullptr, P, P, 0, &a.ctrl->hist[0][0]);
     const int tiles = gsb_div_up(P, RS_TILE);
     for (int p = 0; p < 4; p++) {
@@ -287,19 +287,30 @@ void launch_binning_depth_and_scan(const BinningArgs& a, cudaStream_t s) {
                                                           8 * p, &a.ctrl->hist[p][0], a.lookback, ++(*a.epoch),
                                                           &a.ctrl->tickets[p]);
     }
-    // 2. offsets of every splat's duplicates, in depth order
+}
+
+void launch_scan_offsets(const BinningArgs& a, cudaStream_t s) {
+    const uint32_t P = (uint32_t)a.P;
+    if (P == 0) return;
+    // offsets of every splat's duplicates, in depth order
     scan_offsets_kernel<<<gsb_div_up(P, SC_TILE), 256, 0, s>>>(a.pvals[0], a.tiles_touched, P, a.offsets, a.lookback,
                                                                ++(*a.epoch), &a.ctrl->tickets[4], a.ctrl, a.r_cap,
                                                                a.num_rendered_host);
 }
 
-int launch_binning_emit_and_sort(const BinningArgs& a, cudaStream_t s) {
+void launch_emit(const BinningArgs& a, cudaStream_t s) {
     const uint32_t P = (uint32_t)a.P;
-    if (P == 0 || a.r_cap == 0) return 0;
+    if (P == 0 || a.r_cap == 0) return;
     emit_kernel<<<gsb_div_up(P, 256), 256, 0, s>>>(a.pvals[0], a.offsets, a.tiles_touched, a.radii, a.recs, P, a.grid_x,
                                                    a.grid_y, a.r_cap, a.rkeys[0], a.rvals[0]);
-    // 3. stable sort of the duplicates by tile id
-    const int npass = max(1, (a.tile_bits + 7) / 8);
+}
+
+int gsb_tile_sort_passes(int tile_bits) { return max(1, (tile_bits + 7) / 8); }
+
+int launch_tile_sort(const BinningArgs& a, cudaStream_t s) {
+    const int npass = gsb_tile_sort_passes(a.tile_bits);
+    if (a.P == 0 || a.r_cap == 0) return npass & 1;
+    // stable sort of the duplicates by tile id
     const int grid_cap = gsb_div_up(a.r_cap, RS_TILE);
     const int hist_grid = min(max(grid_cap / 2, 1), 592);
     switch (npass) {
@@ -314,12 +325,23 @@ int launch_binning_emit_and_sort(const BinningArgs& a, cudaStream_t s) {
                                                              &a.ctrl->num_rendered, 0, a.r_cap, 8 * p, &a.ctrl->hist[4 + p][0],
                                                              a.lookback, ++(*a.epoch), &a.ctrl->tickets[5 + p]);
     }
-    const int fin = npass & 1;
-    tile_ranges_kernel<<<min(max(grid_cap * 4, 1), 2368), 256, 0, s>>>(a.rkeys[fin], &a.ctrl->num_rendered, a.r_cap, a.ranges);
-    return fin;
+    return npass & 1;
 }
 
-int launch_binning(const BinningArgs& a, cudaStream_t s) {
-    launch_binning_depth_and_scan(a, s);
-    return launch_binning_emit_and_sort(a, s);
+void launch_tile_ranges(const BinningArgs& a, int fin, cudaStream_t s) {
+    if (a.P == 0 || a.r_cap == 0) return;
+    const int grid_cap = gsb_div_up(a.r_cap, RS_TILE);
+    tile_ranges_kernel<<<min(max(grid_cap * 4, 1), 2368), 256, 0, s>>>(a.rkeys[fin], &a.ctrl->num_rendered, a.r_cap, a.ranges);
+}
+
+void launch_binning_depth_and_scan(const BinningArgs& a, cudaStream_t s) {
+    launch_depth_sort(a, s);
+    launch_scan_offsets(a, s);
+}
+
+int launch_binning_emit_and_sort(const BinningArgs& a, cudaStream_t s) {
+    launch_emit(a, s);
+    const int fin = launch_tile_sort(a, s);
+    launch_tile_ranges(a, fin, s);
+    return fin;
 }

@@ -16,7 +16,7 @@
 struct __align__(16) SplatRec {
     float4 a;   // mean2D.x, mean2D.y, conic.x, conic.y
     float4 b;   // conic.z, opacity, r, g
-    float4 c;   // b, depth, splat index (int bits), radius (int bits)
+    float4 c;   // b, cull threshold on power, cull half-extent x, cull half-extent y
 };
 
 // Per-splat scratch written by the render backward (one vector red per float4) and consumed
@@ -105,9 +105,15 @@ struct BinningArgs {
     GsbCtrl* ctrl;
     uint32_t* num_rendered_host;    // pinned host mirror of R, or null
 };
-// Returns the index (0/1) of the rvals/rkeys buffer holding the sorted list.
-int launch_binning(const BinningArgs& a, cudaStream_t s);
-// Second half of launch_binning when the caller has to size rkeys/rvals from R (compat API).
+// The stages, in order.  launch_tile_sort returns the index (0/1) of the rkeys/rvals buffer that
+// holds the sorted list; a.lookback must cover P items for the first two and r_cap for the sort.
+void launch_depth_sort(const BinningArgs& a, cudaStream_t s);
+void launch_scan_offsets(const BinningArgs& a, cudaStream_t s);
+void launch_emit(const BinningArgs& a, cudaStream_t s);
+int launch_tile_sort(const BinningArgs& a, cudaStream_t s);
+void launch_tile_ranges(const BinningArgs& a, int fin, cudaStream_t s);
+int gsb_tile_sort_passes(int tile_bits);
+// Convenience: depth sort + scan (everything before R is known) and emit + sort + ranges.
 void launch_binning_depth_and_scan(const BinningArgs& a, cudaStream_t s);
 int launch_binning_emit_and_sort(const BinningArgs& a, cudaStream_t s);
 
@@ -122,7 +128,6 @@ struct RenderFwdArgs {
     float* final_T;                 // [H*W]
     uint32_t* n_contrib;            // [H*W]
     uint32_t* tile_max;             // [tiles] max n_contrib in tile
-    int ppt;                        // pixels per thread: 1, 2 or 4
 };
 void launch_render_fwd(const RenderFwdArgs& a, cudaStream_t s);
 
@@ -140,7 +145,6 @@ struct RenderBwdArgs {
     const uint32_t* truth;          //   RGBA8 truth frame and
     const float* rendered;          //   the forward's out_color (dL = truth/255 - rendered)
     GradRec* grads;                 // [P], accumulated with vector reds
-    int ppt;
 };
 void launch_render_bwd(const RenderBwdArgs& a, cudaStream_t s);
 

@@ -130,7 +130,7 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(const PreprocessArg
     }
 
     float cov[6];
-    float ix = 0.f, iy = 0.f, conx = 0.f, cony = 0.f, conz = 0.f;
+    float ix = 0.f, iy = 0.f, conx = 0.f, cony = 0.f, conz = 0.f, covx = 0.f, covy = 0.f;
     if (alive) {
         const float hx = affine_row(px, py, pz, __ldg(Pm + 0), __ldg(Pm + 4), __ldg(Pm + 8), __ldg(Pm + 12));
         const float hy = affine_row(px, py, pz, __ldg(Pm + 1), __ldg(Pm + 5), __ldg(Pm + 9), __ldg(Pm + 13));
@@ -185,6 +185,7 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(const PreprocessArg
             conx = mul_(cyy, det_inv);
             cony = mul_(cxy, -det_inv);
             conz = mul_(cxx, det_inv);
+            covx = cxx; covy = cyy;
             const float mid = mul_(add_(cxx, cyy), 0.5f);
             const float sq = __fsqrt_rn(fmaxf(fma_(mid, mid, -det), 0.1f));
             const float lam = fmaxf(add_(mid, sq), sub_(mid, sq));
@@ -222,10 +223,23 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(const PreprocessArg
     }
     a.clamped[idx] = flags;
     a.depths[idx] = depth;
+    // Conservative culling data for the render kernels.  A pair can only blend if
+    // opacity * exp(power) >= 1/255, i.e. power >= -log(255 * opacity); `lim` sits 0.05 below that
+    // (far more than the rounding error of power and expf), and (ex, ey) is the half-extent of the
+    // bounding box of { power >= lim - 0.05 }, inflated.  Neither value enters any blended result.
+    const float opac = a.opacities[idx];
+    float lim = __int_as_float(0x7f800000), ex = -1e30f, ey = -1e30f;   // opacity < 1/255: never blends
+    if (!(opac < 1.0f / 255.0f)) {
+        lim = -logf(opac * 255.0f) - 0.05f;
+        const float k = -2.0f * (lim - 0.05f);
+        ex = sqrtf(fmaxf(k * covx, 0.f)) * 1.001f + 0.01f;
+        ey = sqrtf(fmaxf(k * covy, 0.f)) * 1.001f + 0.01f;
+        if (!(ex == ex) || !(ey == ey)) { ex = 1e30f; ey = 1e30f; }     // NaN covariance: never cull
+    }
     SplatRec rec;
     rec.a = make_float4(ix, iy, conx, cony);
-    rec.b = make_float4(conz, a.opacities[idx], rgb.x, rgb.y);
-    rec.c = make_float4(rgb.z, depth, __int_as_float(idx), __int_as_float(radius));
+    rec.b = make_float4(conz, opac, rgb.x, rgb.y);
+    rec.c = make_float4(rgb.z, lim, ex, ey);
     a.recs[idx] = rec;
 }
 

@@ -14,7 +14,6 @@
 
 namespace {
 thread_local char g_err[512] = "";
-int g_fwd_ppt = 2, g_bwd_ppt = 2;
 }  // namespace
 
 int gsb_fail(cudaError_t e, const char* what, const char* file, int line) {
@@ -67,10 +66,6 @@ extern "C" {
 const char* gsb_last_error(void) { return g_err; }
 int gsb_version(void) { return 100; }
 
-void gsb_set_render_ppt(int fwd_ppt, int bwd_ppt) {
-    if (fwd_ppt == 1 || fwd_ppt == 2 || fwd_ppt == 4) g_fwd_ppt = fwd_ppt;
-    if (bwd_ppt == 1 || bwd_ppt == 2 || bwd_ppt == 4) g_bwd_ppt = bwd_ppt;
-}
 
 int gsb_rasterizer_forward(gsb_alloc_fn geometry_alloc, void* geometry_user, gsb_alloc_fn binning_alloc,
                            void* binning_user, gsb_alloc_fn image_alloc, void* image_user, int P, int D, int M,
@@ -154,7 +149,6 @@ int gsb_rasterizer_forward(gsb_alloc_fn geometry_alloc, void* geometry_user, gsb
     ra.W = width; ra.H = height; ra.grid_x = grid_x; ra.grid_y = grid_y;
     ra.ranges = im.ranges; ra.point_list = b.rvals[fin]; ra.recs = g.recs; ra.bg = background;
     ra.out_color = out_color; ra.final_T = im.final_T; ra.n_contrib = im.n_contrib; ra.tile_max = im.tile_max;
-    ra.ppt = g_fwd_ppt;
     launch_render_fwd(ra, s);
     if (int e = check(s, dbg)) return e;
     if (num_rendered) *num_rendered = (int)R;
@@ -188,7 +182,7 @@ int gsb_rasterizer_backward(int P, int D, int M, int R, const float* background,
         rb.W = width; rb.H = height; rb.grid_x = grid_x; rb.grid_y = grid_y;
         rb.ranges = im.ranges; rb.point_list = b.rvals[fin]; rb.recs = g.recs; rb.bg = background;
         rb.final_T = im.final_T; rb.n_contrib = im.n_contrib; rb.tile_max = im.tile_max;
-        rb.dL_dpix = dL_dpix; rb.truth = nullptr; rb.rendered = nullptr; rb.grads = g.grads; rb.ppt = g_bwd_ppt;
+        rb.dL_dpix = dL_dpix; rb.truth = nullptr; rb.rendered = nullptr; rb.grads = g.grads;
         launch_render_bwd(rb, s);
         if (int e = check(s, dbg)) return e;
     }

@@ -1,54 +1,46 @@
 // Forward tile renderer: front-to-back alpha blending of each tile's depth-ordered splat list.
 // Replaces renderCUDA<3> forward (reference cuda_rasterizer/forward.cu:261-374).
 //
-// One CTA per 16x16 tile; each thread owns PPT pixels of one column so a staged splat record is
-// read from shared memory once and reused PPT times.  Records (48 B, see SplatRec) are gathered
-// into a double-buffered shared-memory ring with 16-byte cp.async copies issued one batch ahead,
-// and the list indices for the batch after that are prefetched into registers, so neither the
-// dependent gather nor the index load sits on the critical path of the blend loop.
-// The per-pair arithmetic (power, exp, alpha, the 1/255 and 1e-4 tests, the colour FMA order) is
-// pinned with explicit rn intrinsics to what the reference build executes, so every blend /
-// skip / stop decision and therefore n_contrib is identical and images agree to float rounding.
+// One 128-thread CTA per 16x16 tile.  Each warp owns an 8x8 pixel sub-block (two pixels per lane,
+// same column, four rows apart) so a staged record read from shared memory serves two pixels.
+// Per batch of 128 list entries:
+//   * records (48 B, see SplatRec) are gathered into a double-buffered shared-memory ring with
+//     16-byte cp.async copies issued one batch ahead; the list indices of the batch after that are
+//     prefetched into registers, so neither the dependent gather nor the index load is exposed;
+//   * every warp builds a 128-bit survivor mask with four ballots: an entry survives if the bounding
+//     box of { opacity * exp(power) >= 1/255 } (stored, conservatively inflated, in the record) meets
+//     the warp's sub-block.  The blend loop then visits survivors only (ffs over the mask), in list
+//     order.  Culled pairs are exactly those the reference would `continue` over, so nothing changes
+//     in any pixel's T / colour / n_contrib;
+//   * a survivor is first tested against the record's threshold on `power`, skipping exp for pairs that
+//     cannot reach alpha 1/255.
+// The arithmetic of a blended pair (power, expf, alpha, the 1/255 and 1e-4 tests, the colour FMA
+// order) is pinned with explicit rn intrinsics to what the reference build executes, so every
+// blend / skip / stop decision and n_contrib are identical and images agree bit for bit.
 
 #include "common.cuh"
+#include "render_common.cuh"
 
 namespace {
 
-constexpr int RB = 128;   // list entries per staged batch
-
-__device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
-    const uint32_t d = (uint32_t)__cvta_generic_to_shared(smem);
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(gmem) : "memory");
-}
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
-
-template <int PPT>
-__global__ void __launch_bounds__(GSB_TILE_PIX / PPT) render_fwd_kernel(const RenderFwdArgs a) {
-    constexpr int NT = GSB_TILE_PIX / PPT;      // threads per CTA
-    constexpr int ROWS = GSB_TILE / PPT;        // thread rows
-    constexpr int EPT = (RB + NT - 1) / NT;     // staged entries per thread per batch
+__global__ void __launch_bounds__(RENDER_THREADS) render_fwd_kernel(const RenderFwdArgs a) {
     __shared__ SplatRec s_rec[2][RB];
     __shared__ uint32_t s_max;
 
-    const int tid = threadIdx.x;
-    const int tx = tid & (GSB_TILE - 1), ty = tid >> 4;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int tile = blockIdx.y * a.grid_x + blockIdx.x;
-    const int pix_x = blockIdx.x * GSB_TILE + tx;
+    // warp sub-block origin and this lane's two pixels
+    const int bx0 = blockIdx.x * GSB_TILE + (warp & 1) * 8, by0 = blockIdx.y * GSB_TILE + (warp >> 1) * 8;
+    const int pix_x = bx0 + (lane & 7);
+    const int pix_y[2] = {by0 + (lane >> 3), by0 + (lane >> 3) + 4};
     const float pxf = (float)pix_x;
-    int pix_y[PPT];
-    float pyf[PPT];
-    bool done[PPT];
-    float T[PPT], Cr[PPT], Cg[PPT], Cb[PPT];
-    uint32_t last[PPT];
+    const float pyf[2] = {(float)pix_y[0], (float)pix_y[1]};
+    const float bcx = (float)bx0 + 3.5f, bcy = (float)by0 + 3.5f;   // sub-block centre
+    bool done[2];
+    float T[2] = {1.0f, 1.0f}, Cr[2] = {0.f, 0.f}, Cg[2] = {0.f, 0.f}, Cb[2] = {0.f, 0.f};
+    uint32_t last[2] = {0, 0};
 #pragma unroll
-    for (int k = 0; k < PPT; k++) {
-        pix_y[k] = blockIdx.y * GSB_TILE + ty + k * ROWS;
-        pyf[k] = (float)pix_y[k];
-        done[k] = !(pix_x < a.W && pix_y[k] < a.H);
-        T[k] = 1.0f; Cr[k] = Cg[k] = Cb[k] = 0.f;
-        last[k] = 0;
-    }
+    for (int k = 0; k < 2; k++) done[k] = !(pix_x < a.W && pix_y[k] < a.H);
     if (tid == 0) s_max = 0;
 
     const uint2 range = a.ranges[tile];
@@ -56,79 +48,81 @@ __global__ void __launch_bounds__(GSB_TILE_PIX / PPT) render_fwd_kernel(const Re
     const int rounds = (len + RB - 1) / RB;
     const uint32_t* list = a.point_list + range.x;
 
-    // prologue: ids of batch 0 -> gather batch 0; ids of batch 1 -> registers
-    uint32_t ids[EPT];
-#pragma unroll
-    for (int e = 0; e < EPT; e++) {
-        const int p = e * NT + tid;
-        ids[e] = (p < RB && p < len) ? list[p] : 0xFFFFFFFFu;
-    }
+    uint32_t next_id = (tid < len) ? list[tid] : 0xFFFFFFFFu;
     auto issue = [&](int buf) {
-#pragma unroll
-        for (int e = 0; e < EPT; e++) {
-            const int p = e * NT + tid;
-            if (p < RB && ids[e] != 0xFFFFFFFFu) {
-                const SplatRec* g = a.recs + ids[e];
-                cp_async16(&s_rec[buf][p].a, &g->a);
-                cp_async16(&s_rec[buf][p].b, &g->b);
-                cp_async16(&s_rec[buf][p].c, &g->c);
-            }
+        if (next_id != 0xFFFFFFFFu) {
+            const SplatRec* g = a.recs + next_id;
+            cp_async16(&s_rec[buf][tid].a, &g->a);
+            cp_async16(&s_rec[buf][tid].b, &g->b);
+            cp_async16(&s_rec[buf][tid].c, &g->c);
         }
         cp_async_commit();
     };
-    auto load_ids = [&](int batch) {
-#pragma unroll
-        for (int e = 0; e < EPT; e++) {
-            const int p = e * NT + tid;
-            const int q = batch * RB + p;
-            ids[e] = (p < RB && q < len) ? list[q] : 0xFFFFFFFFu;
-        }
-    };
     if (rounds > 0) {
         issue(0);
-        load_ids(1);
+        next_id = (RB + tid < len) ? list[RB + tid] : 0xFFFFFFFFu;
     }
 
     for (int i = 0; i < rounds; i++) {
-        bool all = true;
-#pragma unroll
-        for (int k = 0; k < PPT; k++) all = all && done[k];
+        const bool all = done[0] && done[1];
         cp_async_wait_all();
-        // batch i is visible, batch i-1 fully consumed; vote like the reference's __syncthreads_count
+        // batch i visible, batch i-1 fully consumed; vote like the reference's __syncthreads_count
         if (__syncthreads_and(all)) break;
         if (i + 1 < rounds) {
             issue((i + 1) & 1);
-            load_ids(i + 2);
+            const int q = (i + 2) * RB + tid;
+            next_id = (q < len) ? list[q] : 0xFFFFFFFFu;
         }
         const SplatRec* buf = s_rec[i & 1];
         const int cnt = min(RB, len - i * RB);
-        for (int j = 0; j < cnt; j++) {
-            const float4 ra = buf[j].a;   // x, y, conic.x, conic.y
-            const float4 rb = buf[j].b;   // conic.z, opacity, r, g
-            const float dx = __fsub_rn(ra.x, pxf);
-            const float bx = __fmul_rn(dx, ra.z);
-            const float cxy = __fmul_rn(dx, ra.w);
+        if (__all_sync(0xffffffffu, all)) continue;   // this warp's 64 pixels are finished
+
+        uint32_t mask[RB / 32];
 #pragma unroll
-            for (int k = 0; k < PPT; k++) {
-                if (done[k]) continue;
-                const float dy = __fsub_rn(ra.y, pyf[k]);
-                // power = -0.5 (cx dx^2 + cz dy^2) - cy dx dy, in the reference's evaluation order
-                const float ay = __fmul_rn(dy, __fmul_rn(dy, rb.x));
-                const float power = __fmaf_rn(__fmaf_rn(dx, bx, ay), -0.5f, -__fmul_rn(dy, cxy));
-                if (power > 0.0f) continue;
-                const float alpha = fminf(0.99f, __fmul_rn(rb.y, expf(power)));
-                if (alpha < 1.0f / 255.0f) continue;
-                const float test_T = __fmul_rn(T[k], __fsub_rn(1.0f, alpha));
-                if (test_T < 0.0001f) {
-                    done[k] = true;
-                    continue;
+        for (int m = 0; m < RB / 32; m++) {
+            const int e = m * 32 + lane;
+            bool hit = false;
+            if (e < cnt) {
+                const float2 xy = *reinterpret_cast<const float2*>(&buf[e].a);
+                const float2 ext = *reinterpret_cast<const float2*>(&buf[e].c.z);
+                hit = (fabsf(xy.x - bcx) <= ext.x + 3.5f) && (fabsf(xy.y - bcy) <= ext.y + 3.5f);
+            }
+            mask[m] = __ballot_sync(0xffffffffu, hit);
+        }
+#pragma unroll
+        for (int m = 0; m < RB / 32; m++) {
+            uint32_t bits = mask[m];
+            while (bits) {
+                const int j = m * 32 + __ffs(bits) - 1;
+                bits &= bits - 1;
+                const float4 ra = buf[j].a;   // x, y, conic.x, conic.y
+                const float4 rb = buf[j].b;   // conic.z, opacity, r, g
+                const float2 rc = *reinterpret_cast<const float2*>(&buf[j].c);   // b, power threshold
+                const float dx = __fsub_rn(ra.x, pxf);
+                const float bx = __fmul_rn(dx, ra.z);
+                const float cxy = __fmul_rn(dx, ra.w);
+#pragma unroll
+                for (int k = 0; k < 2; k++) {
+                    if (done[k]) continue;
+                    const float dy = __fsub_rn(ra.y, pyf[k]);
+                    // power = -0.5 (cx dx^2 + cz dy^2) - cy dx dy, in the reference's evaluation order
+                    const float ay = __fmul_rn(dy, __fmul_rn(dy, rb.x));
+                    const float power = __fmaf_rn(__fmaf_rn(dx, bx, ay), -0.5f, -__fmul_rn(dy, cxy));
+                    if (power < rc.y) continue;          // cannot reach alpha 1/255
+                    if (power > 0.0f) continue;
+                    const float alpha = fminf(0.99f, __fmul_rn(rb.y, expf(power)));
+                    if (alpha < 1.0f / 255.0f) continue;
+                    const float test_T = __fmul_rn(T[k], __fsub_rn(1.0f, alpha));
+                    if (test_T < 0.0001f) {
+                        done[k] = true;
+                        continue;
+                    }
+                    Cr[k] = __fmaf_rn(T[k], __fmul_rn(alpha, rb.z), Cr[k]);
+                    Cg[k] = __fmaf_rn(T[k], __fmul_rn(alpha, rb.w), Cg[k]);
+                    Cb[k] = __fmaf_rn(T[k], __fmul_rn(alpha, rc.x), Cb[k]);
+                    T[k] = test_T;
+                    last[k] = (uint32_t)(i * RB + j + 1);
                 }
-                const float blue = buf[j].c.x;
-                Cr[k] = __fmaf_rn(T[k], __fmul_rn(alpha, rb.z), Cr[k]);
-                Cg[k] = __fmaf_rn(T[k], __fmul_rn(alpha, rb.w), Cg[k]);
-                Cb[k] = __fmaf_rn(T[k], __fmul_rn(alpha, blue), Cb[k]);
-                T[k] = test_T;
-                last[k] = (uint32_t)(i * RB + j + 1);
             }
         }
     }
@@ -138,7 +132,7 @@ __global__ void __launch_bounds__(GSB_TILE_PIX / PPT) render_fwd_kernel(const Re
     const size_t plane = (size_t)a.W * a.H;
     uint32_t mx = 0;
 #pragma unroll
-    for (int k = 0; k < PPT; k++) {
+    for (int k = 0; k < 2; k++) {
         if (pix_x < a.W && pix_y[k] < a.H) {
             const size_t pid = (size_t)pix_y[k] * a.W + pix_x;
             a.final_T[pid] = T[k];
@@ -151,7 +145,7 @@ __global__ void __launch_bounds__(GSB_TILE_PIX / PPT) render_fwd_kernel(const Re
     }
     mx = __reduce_max_sync(0xffffffffu, mx);
     __syncthreads();
-    if ((tid & 31) == 0 && mx) atomicMax(&s_max, mx);
+    if (lane == 0 && mx) atomicMax(&s_max, mx);
     __syncthreads();
     if (tid == 0) a.tile_max[tile] = s_max;
 }
@@ -159,10 +153,5 @@ __global__ void __launch_bounds__(GSB_TILE_PIX / PPT) render_fwd_kernel(const Re
 }  // namespace
 
 void launch_render_fwd(const RenderFwdArgs& a, cudaStream_t s) {
-    const dim3 grid(a.grid_x, a.grid_y);
-    switch (a.ppt) {
-        case 1: render_fwd_kernel<1><<<grid, 256, 0, s>>>(a); break;
-        case 4: render_fwd_kernel<4><<<grid, 64, 0, s>>>(a); break;
-        default: render_fwd_kernel<2><<<grid, 128, 0, s>>>(a); break;
-    }
+    render_fwd_kernel<<<dim3(a.grid_x, a.grid_y), RENDER_THREADS, 0, s>>>(a);
 }

@@ -60,7 +60,6 @@ struct gsb_trainer {
 
     gsb_allreduce_fn allreduce = nullptr; void* allreduce_user = nullptr;
     bool loss_on = false; double* d_loss = nullptr;
-    int fwd_ppt = 2, bwd_ppt = 2;
     gsb_trainer_stats stats;
 };
 
@@ -101,16 +100,27 @@ int ensure_avg(gsb_trainer* t) {
     return GSB_OK;
 }
 
-// forward half of one view pass; returns the number of kernels launched
+// Stage boundaries of one view pass (gsb_trainer_profile_pass reports the time between them).
+enum { ST_CLEAR = 0, ST_PREPROCESS, ST_DEPTH_SORT, ST_SCAN, ST_EMIT, ST_TILE_SORT, ST_RANGES, ST_RENDER_FWD,
+       ST_RENDER_BWD, ST_PREPROCESS_BWD, ST_COUNT };
+
+inline void mark(cudaEvent_t* ev, int k, cudaStream_t s) {
+    if (ev) cudaEventRecord(ev[k], s);
+}
+
+// forward half of one view pass; returns 100 + index of the buffer holding the sorted list
 int forward_pass(gsb_trainer* t, const float* view, const float* projview, const float* campos, float tanx, float tany,
-                 float scale_modifier, const float* bg, int W, int H, ImageWs& im, float* out_color, uint32_t* h_R) {
+                 float scale_modifier, const float* bg, int W, int H, ImageWs& im, float* out_color, uint32_t* h_R,
+                 cudaEvent_t* ev = nullptr) {
     cudaStream_t s = t->stream;
     const int grid_x = (W + GSB_TILE - 1) / GSB_TILE, grid_y = (H + GSB_TILE - 1) / GSB_TILE;
     const int tiles = grid_x * grid_y;
     const int P = t->count;
+    mark(ev, ST_CLEAR, s);
     GSB_CUDA_OK(cudaMemsetAsync(t->g.ctrl, 0, sizeof(GsbCtrl), s));
     GSB_CUDA_OK(cudaMemsetAsync(im.ranges, 0, (size_t)tiles * sizeof(uint2), s));
 
+    mark(ev, ST_PREPROCESS, s);
     PreprocessArgs pa;
     pa.P = P; pa.D = t->D; pa.M = t->M;
     pa.means3D = t->loc; pa.scales = t->scales; pa.scale_modifier = scale_modifier; pa.rotations = t->rot;
@@ -133,20 +143,78 @@ int forward_pass(gsb_trainer* t, const float* view, const float* projview, const
     ba.rkeys[0] = t->b.rkeys[0]; ba.rkeys[1] = t->b.rkeys[1]; ba.rvals[0] = t->b.rvals[0]; ba.rvals[1] = t->b.rvals[1];
     ba.ranges = im.ranges; ba.epoch = &t->epoch; ba.ctrl = t->g.ctrl; ba.num_rendered_host = h_R;
     ba.lookback = t->g.lookback; ba.lookback_tiles = (uint32_t)GeomWs::lookback_tiles(t->geom_P);
-    launch_binning_depth_and_scan(ba, s);
+    mark(ev, ST_DEPTH_SORT, s);
+    launch_depth_sort(ba, s);
+    mark(ev, ST_SCAN, s);
+    launch_scan_offsets(ba, s);
     ba.lookback = t->b.lookback; ba.lookback_tiles = (uint32_t)BinWs::lookback_tiles(t->r_cap);
-    const int fin = launch_binning_emit_and_sort(ba, s);
-    const int npass = std::max(1, (ba.tile_bits + 7) / 8);
+    mark(ev, ST_EMIT, s);
+    launch_emit(ba, s);
+    mark(ev, ST_TILE_SORT, s);
+    const int fin = launch_tile_sort(ba, s);
+    mark(ev, ST_RANGES, s);
+    launch_tile_ranges(ba, fin, s);
+    const int npass = gsb_tile_sort_passes(ba.tile_bits);
 
+    mark(ev, ST_RENDER_FWD, s);
     RenderFwdArgs ra;
     ra.W = W; ra.H = H; ra.grid_x = grid_x; ra.grid_y = grid_y;
     ra.ranges = im.ranges; ra.point_list = t->b.rvals[fin]; ra.recs = t->g.recs; ra.bg = bg;
     ra.out_color = out_color; ra.final_T = im.final_T; ra.n_contrib = im.n_contrib; ra.tile_max = im.tile_max;
-    ra.ppt = t->fwd_ppt;
     launch_render_fwd(ra, s);
     t->stats.kernel_launches += 1 + 1 + 4 + 1 + 1 + 1 + npass + 1 + 1;
     GSB_CUDA_OK(cudaGetLastError());
-    return fin + 100;   // >= 100: success, low digit = final buffer
+    return fin + 100;
+}
+
+// loss + backward + accumulate of training view pass i (white passes first, then black: T:311-314)
+int backward_pass(gsb_trainer* t, int i, int fin, float* avg, float S, cudaEvent_t* ev = nullptr) {
+    cudaStream_t s = t->stream;
+    const int n = (int)t->truthW.size();
+    const bool white = i < n;
+    const int cam = i % n;
+    const uint32_t* truth = white ? t->truthW[cam] : t->truthB[cam];
+    const gsb_camera* dc = t->d_cams + cam;
+    const float* bg = t->d_bg + (white ? 0 : 3);
+    if (t->loss_on) {
+        launch_sum_sq_residual(truth, t->rendered, t->W, t->H, t->d_loss, s);
+        t->stats.kernel_launches++;
+    }
+    mark(ev, ST_RENDER_BWD, s);
+    RenderBwdArgs rb;
+    rb.W = t->W; rb.H = t->H; rb.grid_x = t->grid_x; rb.grid_y = t->grid_y;
+    rb.ranges = t->im.ranges; rb.point_list = t->b.rvals[fin]; rb.recs = t->g.recs; rb.bg = bg;
+    rb.final_T = t->im.final_T; rb.n_contrib = t->im.n_contrib; rb.tile_max = t->im.tile_max;
+    rb.dL_dpix = nullptr; rb.truth = truth; rb.rendered = t->rendered; rb.grads = t->g.grads;
+    launch_render_bwd(rb, s);
+
+    mark(ev, ST_PREPROCESS_BWD, s);
+    PreprocessBwdArgs pb;
+    memset(&pb, 0, sizeof(pb));
+    pb.P = t->count; pb.D = t->D; pb.M = t->M;
+    pb.means3D = t->loc; pb.scales = t->scales; pb.scale_modifier = 1.0f; pb.rotations = t->rot; pb.shs = t->shs;
+    pb.cov3D = t->g.cov3D; pb.cov3D_is_precomp = 0; pb.colors_precomp = 0;
+    pb.viewmatrix = dc->view; pb.projmatrix = dc->projview; pb.cam_pos = dc->location;
+    pb.tan_fovx = t->cams[cam].tan_fovx; pb.tan_fovy = t->cams[cam].tan_fovy;
+    pb.focal_y = t->H / (2.0f * pb.tan_fovy);
+    pb.focal_x = t->W / (2.0f * pb.tan_fovx);
+    pb.radii = t->g.radii; pb.clamped = t->g.clamped; pb.grads = t->g.grads;
+    pb.avg = avg; pb.samples = S;
+    launch_preprocess_bwd(pb, s);
+    mark(ev, ST_COUNT, s);
+    t->stats.kernel_launches += 2;
+    return GSB_OK;
+}
+
+int view_pass(gsb_trainer* t, int i, float* avg, float S, cudaEvent_t* ev = nullptr) {
+    const int n = (int)t->truthW.size();
+    const int cam = i % n;
+    const gsb_camera* dc = t->d_cams + cam;
+    const float* bg = t->d_bg + ((i < n) ? 0 : 3);
+    const int r = forward_pass(t, dc->view, dc->projview, dc->location, t->cams[cam].tan_fovx, t->cams[cam].tan_fovy, 1.0f, bg,
+                               t->W, t->H, t->im, t->rendered, t->h_R + i, ev);
+    if (r < 100) return r;
+    return backward_pass(t, i, r - 100, avg, S, ev);
 }
 
 }  // namespace
@@ -240,12 +308,6 @@ int gsb_trainer_set_allreduce(gsb_trainer* t, gsb_allreduce_fn fn, void* user) {
     return GSB_OK;
 }
 
-int gsb_trainer_set_options(gsb_trainer* t, int fwd_ppt, int bwd_ppt) {
-    if (!t) return gsb_fail_msg("gsb_trainer_set_options: null trainer");
-    if (fwd_ppt == 1 || fwd_ppt == 2 || fwd_ppt == 4) t->fwd_ppt = fwd_ppt;
-    if (bwd_ppt == 1 || bwd_ppt == 2 || bwd_ppt == 4) t->bwd_ppt = bwd_ppt;
-    return GSB_OK;
-}
 
 int gsb_trainer_enable_loss(gsb_trainer* t, int on) {
     if (!t) return gsb_fail_msg("gsb_trainer_enable_loss: null trainer");
@@ -281,41 +343,8 @@ int gsb_trainer_accumulate(gsb_trainer* t) {
     for (int attempt = 0; attempt < 4; attempt++) {
         GSB_CUDA_OK(cudaMemsetAsync(avg, 0, grad_floats(t) * sizeof(float), s));
         if (t->loss_on) GSB_CUDA_OK(cudaMemsetAsync(t->d_loss, 0, sizeof(double), s));
-        for (int i = 0; i < 2 * n; i++) {
-            const bool white = i < n;
-            const int cam = i % n;
-            const uint32_t* truth = white ? t->truthW[cam] : t->truthB[cam];
-            const gsb_camera* dc = t->d_cams + cam;
-            const float* bg = t->d_bg + (white ? 0 : 3);
-            const int r = forward_pass(t, dc->view, dc->projview, dc->location, t->cams[cam].tan_fovx, t->cams[cam].tan_fovy,
-                                       1.0f, bg, t->W, t->H, t->im, t->rendered, t->h_R + i);
-            if (r < 100) return r;
-            const int fin = r - 100;
-            if (t->loss_on) {
-                launch_sum_sq_residual(truth, t->rendered, t->W, t->H, t->d_loss, s);
-                t->stats.kernel_launches++;
-            }
-            RenderBwdArgs rb;
-            rb.W = t->W; rb.H = t->H; rb.grid_x = t->grid_x; rb.grid_y = t->grid_y;
-            rb.ranges = t->im.ranges; rb.point_list = t->b.rvals[fin]; rb.recs = t->g.recs; rb.bg = bg;
-            rb.final_T = t->im.final_T; rb.n_contrib = t->im.n_contrib; rb.tile_max = t->im.tile_max;
-            rb.dL_dpix = nullptr; rb.truth = truth; rb.rendered = t->rendered; rb.grads = t->g.grads; rb.ppt = t->bwd_ppt;
-            launch_render_bwd(rb, s);
-
-            PreprocessBwdArgs pb;
-            memset(&pb, 0, sizeof(pb));
-            pb.P = P; pb.D = t->D; pb.M = t->M;
-            pb.means3D = t->loc; pb.scales = t->scales; pb.scale_modifier = 1.0f; pb.rotations = t->rot; pb.shs = t->shs;
-            pb.cov3D = t->g.cov3D; pb.cov3D_is_precomp = 0; pb.colors_precomp = 0;
-            pb.viewmatrix = dc->view; pb.projmatrix = dc->projview; pb.cam_pos = dc->location;
-            pb.tan_fovx = t->cams[cam].tan_fovx; pb.tan_fovy = t->cams[cam].tan_fovy;
-            pb.focal_y = t->H / (2.0f * pb.tan_fovy);
-            pb.focal_x = t->W / (2.0f * pb.tan_fovx);
-            pb.radii = t->g.radii; pb.clamped = t->g.clamped; pb.grads = t->g.grads;
-            pb.avg = avg; pb.samples = S;
-            launch_preprocess_bwd(pb, s);
-            t->stats.kernel_launches += 2;
-        }
+        for (int i = 0; i < 2 * n; i++)
+            if (int e = view_pass(t, i, avg, S)) return e;
         GSB_CUDA_OK(cudaGetLastError());
         // one synchronisation per iteration: learn every view's R, detect arena overflow
         GSB_CUDA_OK(cudaStreamSynchronize(s));
@@ -336,6 +365,27 @@ int gsb_trainer_accumulate(gsb_trainer* t) {
     }
     gsb_fail_msg("gsb_trainer_accumulate: binning arena kept overflowing");
     return GSB_ERR_STATE;
+}
+
+int gsb_trainer_profile_pass(gsb_trainer* t, int pass_index, float* stage_ms, unsigned int* counters) {
+    if (!t || !stage_ms) return gsb_fail_msg("gsb_trainer_profile_pass: invalid argument");
+    const int n = (int)t->truthW.size();
+    if (n == 0 || pass_index < 0 || pass_index >= 2 * n || t->count <= 0 || !t->geom || !t->bin) {
+        gsb_fail_msg("gsb_trainer_profile_pass: run gsb_trainer_accumulate once first");
+        return GSB_ERR_STATE;
+    }
+    cudaEvent_t ev[ST_COUNT + 1];
+    for (int k = 0; k <= ST_COUNT; k++) GSB_CUDA_OK(cudaEventCreate(&ev[k]));
+    const int e = view_pass(t, pass_index, avg_ptr(t), 2.0f * (float)t->total_cameras, ev);
+    if (e) return e;
+    GSB_CUDA_OK(cudaStreamSynchronize(t->stream));
+    for (int k = 0; k < ST_COUNT; k++) GSB_CUDA_OK(cudaEventElapsedTime(&stage_ms[k], ev[k], ev[k + 1]));
+    for (int k = 0; k <= ST_COUNT; k++) cudaEventDestroy(ev[k]);
+    if (counters) {
+        counters[0] = t->h_R[pass_index];
+        GSB_CUDA_OK(cudaMemcpy(&counters[1], &t->g.ctrl->num_visible, sizeof(unsigned int), cudaMemcpyDeviceToHost));
+    }
+    return GSB_OK;
 }
 
 int gsb_trainer_apply(gsb_trainer* t, const gsb_project_params* p) {

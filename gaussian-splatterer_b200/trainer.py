@@ -223,9 +223,6 @@ class Trainer:
         self._allreduce_cb = ALLREDUCE_FN(hook)
         check(lib().gsb_trainer_set_allreduce(self._h, self._allreduce_cb, None))
 
-    def set_options(self, fwd_ppt=0, bwd_ppt=0):
-        check(lib().gsb_trainer_set_options(self._h, fwd_ppt, bwd_ppt))
-
     def enable_loss(self, on=True):
         check(lib().gsb_trainer_enable_loss(self._h, int(on)))
 
@@ -233,6 +230,16 @@ class Trainer:
         s = TrainerStats()
         check(lib().gsb_trainer_get_stats(self._h, C.byref(s)))
         return {k: getattr(s, k) for k, _ in TrainerStats._fields_}
+
+    STAGES = ("clear", "preprocess", "depth_sort", "scan", "emit", "tile_sort", "ranges", "render_fwd", "render_bwd",
+              "preprocess_bwd")
+
+    def profile_pass(self, pass_index):
+        """Per-stage milliseconds (CUDA events) and counters of one training view pass."""
+        ms = (C.c_float * 10)()
+        cnt = (C.c_uint * 2)()
+        check(lib().gsb_trainer_profile_pass(self._h, pass_index, ms, cnt))
+        return dict(zip(self.STAGES, [float(x) for x in ms])), {"R": int(cnt[0]), "visible": int(cnt[1])}
 
     # -- reference interface -------------------------------------------------------------------
     def render(self, frameBuffer, sizeX, sizeY, splatScale, camera):

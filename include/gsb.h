@@ -75,8 +75,6 @@ int gsb_rasterizer_backward(int P, int D, int M, int R,
 int gsb_rasterizer_mark_visible(int P, const float* means3D, const float* viewmatrix,
                                 const float* projmatrix, unsigned char* present, void* stream);
 
-/* Pixels-per-thread of the render kernels (1, 2 or 4); tuning knob, results do not depend on it. */
-void gsb_set_render_ppt(int fwd_ppt, int bwd_ppt);
 
 /* Read-only view into the private workspace layout after gsb_rasterizer_forward, for parity tests
  * (counterpart of Geometry/Binning/ImageState::fromChunk, RI:155-194).  Device pointers. */
@@ -84,7 +82,7 @@ typedef struct gsb_state_view {
     const int* radii;                 /* [P] */
     const float* depths;              /* [P] (valid where radii > 0) */
     const uint32_t* tiles_touched;    /* [P] */
-    const float* recs;                /* [P][12]: x y conic.x conic.y | conic.z opacity r g | b depth idx radius */
+    const float* recs;                /* [P][12]: x y conic.x conic.y / conic.z opacity r g / b cull-threshold cull-ex cull-ey */
     const float* cov3D;               /* [P][6] */
     const unsigned char* clamped;     /* [P] bit c = channel c clamped */
     const uint32_t* depth_order;      /* [P] splat ids sorted by depth bits (culled last) */
@@ -182,8 +180,15 @@ typedef struct gsb_trainer_stats {
 } gsb_trainer_stats;
 int gsb_trainer_get_stats(gsb_trainer* t, gsb_trainer_stats* out);
 int gsb_trainer_enable_loss(gsb_trainer* t, int on);
-/* Fuse the white and black pass of a camera (shared preprocess / sort / blend). 0 = off. */
-int gsb_trainer_set_options(gsb_trainer* t, int fwd_ppt, int bwd_ppt);
+
+/* Measurement: run training view pass `pass_index` (0..2n-1, white passes first) once with CUDA
+ * events between its stages and return the milliseconds of each, in this order:
+ *   0 clear, 1 preprocess, 2 depth sort, 3 offset scan, 4 emit, 5 tile sort, 6 tile ranges,
+ *   7 render forward, 8 render backward (+fused loss), 9 preprocess backward (+accumulate).
+ * counters (optional) receives R and the visible-splat count of that pass.  Needs one prior
+ * gsb_trainer_accumulate (arenas sized).  The running means are perturbed; call it outside training. */
+#define GSB_NUM_STAGES 10
+int gsb_trainer_profile_pass(gsb_trainer* t, int pass_index, float* stage_ms, unsigned int* counters);
 
 /* Image helpers: imageFloatToInt / imageIntToLoss (T:19-44). */
 int gsb_image_float_to_int(const float* dev_src, uint32_t* dev_fb, int w, int h, void* stream);
