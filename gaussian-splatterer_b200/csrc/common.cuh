@@ -21,9 +21,10 @@ struct __align__(16) SplatRec {
 
 // Per-splat scratch written by the render backward (one vector red per float4) and consumed
 // (then cleared) by the preprocess backward.
+// With h = G * dL/dalpha and d = mean2D - pixel, summed over all blended (pixel, splat) pairs:
 struct __align__(16) GradRec {
-    float4 a;   // dL/dmean2D.x, dL/dmean2D.y, dL/dconic.x, dL/dconic.y
-    float4 b;   // dL/dconic.w, dL/dopacity, dL/dr, dL/dg
+    float4 a;   // H0 = sum h, Hx = sum h dx, Hy = sum h dy, Hxx = sum h dx dx
+    float4 b;   // Hxy = sum h dx dy, Hyy = sum h dy dy, dL/dr, dL/dg
     float4 c;   // dL/db, unused x3
 };
 
@@ -166,6 +167,8 @@ struct PreprocessBwdArgs {
     const int* radii;
     const uint8_t* clamped;
     GradRec* grads;                 // consumed and cleared
+    const SplatRec* recs;           // the forward's records (conic, opacity)
+    int W, H;
     // mode A (Rasterizer::backward): caller arrays, reference semantics
     float* dL_dmean2D;              // [P][3] +=
     float* dL_dconic;               // [P][4] +=

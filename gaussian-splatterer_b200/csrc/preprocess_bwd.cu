@@ -99,9 +99,20 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreprocessBwd
         const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
         a.grads[idx].a = z; a.grads[idx].b = z; a.grads[idx].c = z;
     }
-    float gm2x = g.a.x, gm2y = g.a.y;
-    float gcx = g.a.z, gcy = g.a.w, gcw = g.b.x;
-    float gop = g.b.y;
+    // The render backward accumulates the moments H0, Hx, Hy, Hxx, Hxy, Hyy of h = G dL/dalpha (see
+    // GradRec); the gradients of backward.cu:536-554 are linear in them with per-splat coefficients.
+    float gm2x, gm2y, gcx, gcy, gcw, gop;
+    {
+        const SplatRec& r = a.recs[idx];
+        const float conx = r.a.z, cony = r.a.w, conz = r.b.x, opac = r.b.y;
+        const float H0 = g.a.x, Hx = g.a.y, Hy = g.a.z, Hxx = g.a.w, Hxy = g.b.x, Hyy = g.b.y;
+        gop = H0;
+        gm2x = -(0.5f * a.W) * opac * (conx * Hx + cony * Hy);
+        gm2y = -(0.5f * a.H) * opac * (conz * Hy + cony * Hx);
+        gcx = -0.5f * opac * Hxx;
+        gcy = -0.5f * opac * Hxy;
+        gcw = -0.5f * opac * Hyy;
+    }
     V3 gcol = {g.b.z, g.b.w, g.c.x};
     const bool modeA = (a.avg == nullptr);
     if (modeA) {

@@ -197,7 +197,7 @@ int gsb_rasterizer_backward(int P, int D, int M, int R, const float* background,
     pb.tan_fovx = tan_fovx; pb.tan_fovy = tan_fovy;
     pb.focal_y = height / (2.0f * tan_fovy);
     pb.focal_x = width / (2.0f * tan_fovx);
-    pb.radii = radii; pb.clamped = g.clamped; pb.grads = g.grads;
+    pb.radii = radii; pb.clamped = g.clamped; pb.grads = g.grads; pb.recs = g.recs; pb.W = width; pb.H = height;
     pb.dL_dmean2D = dL_dmean2D; pb.dL_dconic = dL_dconic; pb.dL_dopacity = dL_dopacity; pb.dL_dcolor = dL_dcolor;
     pb.dL_dmean3D = dL_dmean3D; pb.dL_dcov3D = dL_dcov3D; pb.dL_dsh = dL_dsh; pb.dL_dscale = dL_dscale; pb.dL_drot = dL_drot;
     pb.avg = nullptr; pb.samples = 1.f;

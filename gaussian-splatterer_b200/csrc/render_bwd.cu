@@ -1,41 +1,39 @@
-// Backward tile renderer: per-pixel gradients of the alpha blend, reduced per (tile, splat) before
+// Backward tile renderer: per-pixel gradients of the alpha blend, reduced per (warp, splat) before
 // they touch global memory.  Replaces renderCUDA<3> backward (reference
 // cuda_rasterizer/backward.cu:399-557), which issues 9 global atomicAdds per blended
 // (pixel, splat) pair, and -- when the loss is fused -- imageIntToLoss (src/Trainer.cu:33-44).
 //
 // Same tiling, staging and survivor masks as the forward (render_fwd.cu), walked back to front and
 // starting at the tile's largest n_contrib instead of the end of the list; a warp additionally drops
-// entries beyond the largest n_contrib of its own 64 pixels.  For every surviving list entry the 9
-// partial gradients are
-//   1. summed over the lane's two pixels in registers,
-//   2. reduced across the warp with a reduce-scatter butterfly (14 shuffles for 9 values instead of
-//      45) -- skipped when no lane of the warp blended the entry,
-//   3. parked in a per-warp shared-memory slot,
-// and after each batch one thread per entry adds the warps' slots and issues three reductions
-// (red.global.add.v4.f32 x2 + one scalar) into the packed GradRec scratch: 3 L2 transactions per
-// (tile, splat) instead of 9 per (pixel, splat).
+// entries beyond the largest n_contrib of its own 64 pixels.
+//
+// What is accumulated per (pixel, splat) pair is not the reference's nine gradients but the nine
+// sums they are linear in: with h = G * dL/dalpha and d = mean2D - pixel,
+//     H0 = sum h, Hx = sum h dx, Hy = sum h dy, Hxx = sum h dx dx, Hxy = sum h dx dy, Hyy = sum h dy dy
+// and the three colour sums.  dL/dopacity = H0, dL/dmean2D = -(W/2, H/2) * opacity * (conic * (Hx,Hy)),
+// dL/dconic = -opacity/2 * (Hxx, Hxy, Hyy): per-splat constants, applied once per splat by the
+// preprocess backward (preprocess_bwd.cu) instead of once per pair here.
+//
+// For every surviving list entry the nine partial sums are added over the lane's two pixels in
+// registers, reduced across the warp with a reduce-scatter butterfly (14 shuffles for 9 values
+// instead of 45; skipped when no lane blended the entry) and the nine lanes that end up holding a
+// total issue one red.global.add each into the packed GradRec scratch (two RED instructions per
+// warp and entry).  On the measured scenes 1.2 warps blend a given (tile, splat) duplicate, so a
+// further cross-warp stage would save almost nothing.
 
 #include "common.cuh"
 #include "render_common.cuh"
 
 namespace {
 
-__device__ __forceinline__ void red_add_v4(float4* addr, float4 v) {
-    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)
-                 : "memory");
-}
-
 struct BwdSmem {
     SplatRec rec[2][RB];
     uint32_t id[2][RB];
-    float acc[RENDER_WARPS][RB][12];
-    uint32_t mask[RENDER_WARPS][RB / 32];
 };
 
 template <bool FUSED_LOSS>
-__global__ void __launch_bounds__(RENDER_THREADS) render_bwd_kernel(const RenderBwdArgs a) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    BwdSmem& sm = *reinterpret_cast<BwdSmem*>(smem_raw);
+__global__ void __launch_bounds__(RENDER_THREADS, 6) render_bwd_kernel(const RenderBwdArgs a) {
+    __shared__ BwdSmem sm;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int tile = blockIdx.y * a.grid_x + blockIdx.x;
@@ -51,7 +49,6 @@ __global__ void __launch_bounds__(RENDER_THREADS) render_bwd_kernel(const Render
     const float bcx = (float)bx0 + 3.5f, bcy = (float)by0 + 3.5f;
     const float bg0 = __ldg(a.bg), bg1 = __ldg(a.bg + 1), bg2 = __ldg(a.bg + 2);
     const size_t plane = (size_t)a.W * a.H;
-    const float ddelx_dx = 0.5f * a.W, ddely_dy = 0.5f * a.H;
 
     float pyf[2], T[2], Tfin[2], bgdot[2], last_alpha[2];
     float dLr[2], dLg[2], dLb[2], lcr[2], lcg[2], lcb[2], arr[2], arg[2], arb[2];
@@ -107,16 +104,18 @@ __global__ void __launch_bounds__(RENDER_THREADS) render_bwd_kernel(const Render
 
     for (int i = 0; i < rounds; i++) {
         cp_async_wait_all();
-        __syncthreads();   // batch i visible; reduction of batch i-1 finished (acc / mask reusable)
+        __syncthreads();   // batch i visible, batch i-1 fully consumed
         if (i + 1 < rounds) {
             issue((i + 1) & 1);
             next_id = fetch_id(i + 2);
         }
         const SplatRec* buf = sm.rec[i & 1];
+        const uint32_t* ids = sm.id[i & 1];
         const int cnt = min(RB, start - i * RB);
         const int idx0 = start - 1 - i * RB;          // list position of entry 0 of this batch
+        if (idx0 - (cnt - 1) >= warp_max) continue;   // nothing in this batch reaches this warp's pixels
 
-        uint32_t mask[RB / 32], touched[RB / 32];
+        uint32_t mask[RB / 32];
 #pragma unroll
         for (int m = 0; m < RB / 32; m++) {
             const int e = m * 32 + lane;
@@ -127,14 +126,12 @@ __global__ void __launch_bounds__(RENDER_THREADS) render_bwd_kernel(const Render
                 hit = (fabsf(xy.x - bcx) <= ext.x + 3.5f) && (fabsf(xy.y - bcy) <= ext.y + 3.5f);
             }
             mask[m] = __ballot_sync(0xffffffffu, hit);
-            touched[m] = 0;
         }
 #pragma unroll
         for (int m = 0; m < RB / 32; m++) {
             uint32_t bits = mask[m];
             while (bits) {
-                const int b = __ffs(bits) - 1;
-                const int j = m * 32 + b;
+                const int j = m * 32 + __ffs(bits) - 1;
                 bits &= bits - 1;
                 const int idx = idx0 - j;
                 const float4 ra = buf[j].a;   // x, y, conic.x, conic.y
@@ -159,34 +156,31 @@ __global__ void __launch_bounds__(RENDER_THREADS) render_bwd_kernel(const Render
                     const float alpha = fminf(0.99f, __fmul_rn(rb.y, G));
                     if (alpha < 1.0f / 255.0f) continue;
                     hit = true;
-                    const float om = 1.f - alpha;
-                    T[k] = T[k] / om;
+                    const float inv = __fdividef(1.0f, 1.f - alpha);
+                    T[k] *= inv;
                     const float w = alpha * T[k];
                     // colour behind this splat, reconstructed back to front
-                    arr[k] = last_alpha[k] * lcr[k] + (1.f - last_alpha[k]) * arr[k];
-                    arg[k] = last_alpha[k] * lcg[k] + (1.f - last_alpha[k]) * arg[k];
-                    arb[k] = last_alpha[k] * lcb[k] + (1.f - last_alpha[k]) * arb[k];
+                    arr[k] = fmaf(last_alpha[k], lcr[k] - arr[k], arr[k]);
+                    arg[k] = fmaf(last_alpha[k], lcg[k] - arg[k], arg[k]);
+                    arb[k] = fmaf(last_alpha[k], lcb[k] - arb[k], arb[k]);
                     lcr[k] = rb.z; lcg[k] = rb.w; lcb[k] = rc.x;
                     float dL_dalpha = (rb.z - arr[k]) * dLr[k] + (rb.w - arg[k]) * dLg[k] + (rc.x - arb[k]) * dLb[k];
-                    v[6] += w * dLr[k];
-                    v[7] += w * dLg[k];
-                    v[8] += w * dLb[k];
-                    dL_dalpha *= T[k];
+                    v[6] = fmaf(w, dLr[k], v[6]);
+                    v[7] = fmaf(w, dLg[k], v[7]);
+                    v[8] = fmaf(w, dLb[k], v[8]);
                     last_alpha[k] = alpha;
-                    dL_dalpha += (-Tfin[k] / om) * bgdot[k];
-                    const float dL_dG = rb.y * dL_dalpha;
-                    const float gdx = G * dx, gdy = G * dy;
-                    const float dG_ddelx = -gdx * ra.z - gdy * ra.w;
-                    const float dG_ddely = -gdy * rb.x - gdx * ra.w;
-                    v[0] += dL_dG * dG_ddelx * ddelx_dx;
-                    v[1] += dL_dG * dG_ddely * ddely_dy;
-                    v[2] += -0.5f * gdx * dx * dL_dG;
-                    v[3] += -0.5f * gdx * dy * dL_dG;
-                    v[4] += -0.5f * gdy * dy * dL_dG;
-                    v[5] += G * dL_dalpha;
+                    // + background term: alpha also scales how much of bg shows through
+                    dL_dalpha = fmaf(dL_dalpha, T[k], -(Tfin[k] * inv) * bgdot[k]);
+                    const float h = G * dL_dalpha;
+                    const float hx = h * dx, hy = h * dy;
+                    v[0] += h;
+                    v[1] += hx;
+                    v[2] += hy;
+                    v[3] = fmaf(hx, dx, v[3]);
+                    v[4] = fmaf(hx, dy, v[4]);
+                    v[5] = fmaf(hy, dy, v[5]);
                 }
                 if (!__any_sync(0xffffffffu, hit)) continue;
-                touched[m] |= 1u << b;
                 // reduce-scatter butterfly over v[0..7]: afterwards lanes 4q..4q+3 hold the warp sum of v[q]
                 float u[4], t2[2], s1;
                 {
@@ -218,57 +212,20 @@ __global__ void __launch_bounds__(RENDER_THREADS) render_bwd_kernel(const Render
                 float s8 = v[8];
 #pragma unroll
                 for (int o = 16; o > 0; o >>= 1) s8 += __shfl_xor_sync(0xffffffffu, s8, o);
-                // lane bits (16,8,4) select the value index: 4*b16 + 2*b8 + b4
-                if ((lane & 3) == 0) sm.acc[warp][j][lane >> 2] = s1;
-                if (lane == 1) sm.acc[warp][j][8] = s8;
-            }
-        }
-#pragma unroll
-        for (int m = 0; m < RB / 32; m++)
-            if (lane == m) sm.mask[warp][m] = touched[m];   // warp-uniform values
-        __syncthreads();
-        // one thread per entry: add the warps' slots, 3 reductions into the packed scratch
-        if (tid < cnt) {
-            const int e = tid;
-            float4 s0 = make_float4(0.f, 0.f, 0.f, 0.f), s1v = s0;
-            float s2 = 0.f;
-            bool any = false;
-#pragma unroll
-            for (int w = 0; w < RENDER_WARPS; w++) {
-                if ((sm.mask[w][e >> 5] >> (e & 31)) & 1u) {
-                    const float4 p0 = *reinterpret_cast<const float4*>(&sm.acc[w][e][0]);
-                    const float4 p1 = *reinterpret_cast<const float4*>(&sm.acc[w][e][4]);
-                    s0.x += p0.x; s0.y += p0.y; s0.z += p0.z; s0.w += p0.w;
-                    s1v.x += p1.x; s1v.y += p1.y; s1v.z += p1.z; s1v.w += p1.w;
-                    s2 += sm.acc[w][e][8];
-                    any = true;
-                }
-            }
-            if (any) {
-                GradRec* g = a.grads + sm.id[i & 1][e];
-                red_add_v4(&g->a, s0);
-                red_add_v4(&g->b, s1v);
-                atomicAdd(&g->c.x, s2);
+                // lane 4q holds sum q (q = 4*b16 + 2*b8 + b4): GradRec floats 0..7; float 8 from lane 1
+                float* g = reinterpret_cast<float*>(a.grads + ids[j]);
+                if ((lane & 3) == 0) atomicAdd(g + (lane >> 2), s1);
+                if (lane == 1) atomicAdd(g + 8, s8);
             }
         }
     }
     cp_async_wait_all();
 }
 
-template <bool FUSED>
-void launch_one(const RenderBwdArgs& a, cudaStream_t s) {
-    static bool configured = false;
-    const size_t bytes = sizeof(BwdSmem);
-    if (!configured) {
-        cudaFuncSetAttribute(render_bwd_kernel<FUSED>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
-        configured = true;
-    }
-    render_bwd_kernel<FUSED><<<dim3(a.grid_x, a.grid_y), RENDER_THREADS, bytes, s>>>(a);
-}
-
 }  // namespace
 
 void launch_render_bwd(const RenderBwdArgs& a, cudaStream_t s) {
-    if (a.dL_dpix == nullptr) launch_one<true>(a, s);
-    else launch_one<false>(a, s);
+    const dim3 grid(a.grid_x, a.grid_y);
+    if (a.dL_dpix == nullptr) render_bwd_kernel<true><<<grid, RENDER_THREADS, 0, s>>>(a);
+    else render_bwd_kernel<false><<<grid, RENDER_THREADS, 0, s>>>(a);
 }

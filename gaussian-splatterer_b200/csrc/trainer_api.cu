@@ -198,7 +198,7 @@ int backward_pass(gsb_trainer* t, int i, int fin, float* avg, float S, cudaEvent
     pb.tan_fovx = t->cams[cam].tan_fovx; pb.tan_fovy = t->cams[cam].tan_fovy;
     pb.focal_y = t->H / (2.0f * pb.tan_fovy);
     pb.focal_x = t->W / (2.0f * pb.tan_fovx);
-    pb.radii = t->g.radii; pb.clamped = t->g.clamped; pb.grads = t->g.grads;
+    pb.radii = t->g.radii; pb.clamped = t->g.clamped; pb.grads = t->g.grads; pb.recs = t->g.recs; pb.W = t->W; pb.H = t->H;
     pb.avg = avg; pb.samples = S;
     launch_preprocess_bwd(pb, s);
     mark(ev, ST_COUNT, s);
