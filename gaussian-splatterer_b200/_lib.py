@@ -100,6 +100,8 @@ def lib():
     L.gsb_trainer_get_stats.restype = i
     L.gsb_trainer_enable_loss.argtypes = [vp, i]
     L.gsb_trainer_enable_loss.restype = i
+    L.gsb_trainer_set_fuse_backgrounds.argtypes = [vp, i]
+    L.gsb_trainer_set_fuse_backgrounds.restype = i
     L.gsb_trainer_profile_pass.argtypes = [vp, i, C.POINTER(C.c_float), C.POINTER(C.c_uint)]
     L.gsb_trainer_profile_pass.restype = i
     L.gsb_image_float_to_int.argtypes = [vp, vp, i, i, vp]

@@ -145,7 +145,11 @@ struct RenderBwdArgs {
     const float* dL_dpix;           // [3][H][W], or null when the loss is fused:
     const uint32_t* truth;          //   RGBA8 truth frame and
     const float* rendered;          //   the forward's out_color (dL = truth/255 - rendered)
-    GradRec* grads;                 // [P], accumulated with vector reds
+    GradRec* grads;                 // [P], accumulated with red.global.add
+    // dual mode (non-null truth2): `truth` is the white-background frame, `truth2` the black one,
+    // `rendered` the black-background image; the black pass accumulates into grads2
+    const uint32_t* truth2;
+    GradRec* grads2;
 };
 void launch_render_bwd(const RenderBwdArgs& a, cudaStream_t s);
 

@@ -20,6 +20,11 @@
 // total issue one red.global.add each into the packed GradRec scratch (two RED instructions per
 // warp and entry).  On the measured scenes 1.2 warps blend a given (tile, splat) duplicate, so a
 // further cross-warp stage would save almost nothing.
+//
+// DUAL mode serves Trainer::train's white and black pass of one camera (src/Trainer.cu:311-314) in
+// a single walk: both passes blend the same splats with the same alpha and T (the background only
+// enters through out = C + T * bg, forward.cu:372), so power / exp / T / colour-behind are computed
+// once and only the two residuals' sums are kept apart (two GradRec sets).
 
 #include "common.cuh"
 #include "render_common.cuh"
@@ -31,8 +36,45 @@ struct BwdSmem {
     uint32_t id[2][RB];
 };
 
-template <bool FUSED_LOSS>
-__global__ void __launch_bounds__(RENDER_THREADS, 6) render_bwd_kernel(const RenderBwdArgs a) {
+// Warp sum of 9 values: lanes 4q..4q+3 end up with the total of v[q] (q < 8), every lane with v[8].
+__device__ __forceinline__ void warp_reduce9(const float (&v)[9], int lane, float& s1, float& s8) {
+    float u[4], t2[2];
+    {
+        const bool hi = lane & 16;
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+            const float send = hi ? v[q] : v[q + 4];
+            const float keep = hi ? v[q + 4] : v[q];
+            u[q] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
+        }
+    }
+    {
+        const bool hi = lane & 8;
+#pragma unroll
+        for (int q = 0; q < 2; q++) {
+            const float send = hi ? u[q] : u[q + 2];
+            const float keep = hi ? u[q + 2] : u[q];
+            t2[q] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
+        }
+    }
+    {
+        const bool hi = lane & 4;
+        const float send = hi ? t2[0] : t2[1];
+        const float keep = hi ? t2[1] : t2[0];
+        s1 = keep + __shfl_xor_sync(0xffffffffu, send, 4);
+    }
+    s1 += __shfl_xor_sync(0xffffffffu, s1, 2);
+    s1 += __shfl_xor_sync(0xffffffffu, s1, 1);
+    s8 = v[8];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s8 += __shfl_xor_sync(0xffffffffu, s8, o);
+}
+
+// MODE 0: dL/dpixel given (Rasterizer::backward).  MODE 1: residual of one truth frame fused.
+// MODE 2: white and black truth frames of one camera fused (two residuals, two GradRec sets).
+template <int MODE>
+__global__ void __launch_bounds__(RENDER_THREADS, MODE == 2 ? 5 : 6) render_bwd_kernel(const RenderBwdArgs a) {
+    constexpr int NS = (MODE == 2) ? 2 : 1;   // residual sets
     __shared__ BwdSmem sm;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -47,11 +89,11 @@ __global__ void __launch_bounds__(RENDER_THREADS, 6) render_bwd_kernel(const Ren
     const int pix_x = bx0 + (lane & 7);
     const float pxf = (float)pix_x;
     const float bcx = (float)bx0 + 3.5f, bcy = (float)by0 + 3.5f;
-    const float bg0 = __ldg(a.bg), bg1 = __ldg(a.bg + 1), bg2 = __ldg(a.bg + 2);
     const size_t plane = (size_t)a.W * a.H;
 
-    float pyf[2], T[2], Tfin[2], bgdot[2], last_alpha[2];
-    float dLr[2], dLg[2], dLb[2], lcr[2], lcg[2], lcb[2], arr[2], arg[2], arb[2];
+    float pyf[2], T[2], Tfin[2], last_alpha[2];
+    float lcr[2], lcg[2], lcb[2], arr[2], arg[2], arb[2];
+    float dLr[NS][2], dLg[NS][2], dLb[NS][2], bgdot[2];   // bgdot: set 0 only (set 1 is the black pass)
     int ncontrib[2];
 #pragma unroll
     for (int k = 0; k < 2; k++) {
@@ -62,21 +104,35 @@ __global__ void __launch_bounds__(RENDER_THREADS, 6) render_bwd_kernel(const Ren
         Tfin[k] = inside ? a.final_T[pid] : 0.f;
         T[k] = Tfin[k];
         ncontrib[k] = inside ? (int)a.n_contrib[pid] : 0;
-        dLr[k] = dLg[k] = dLb[k] = 0.f;
+#pragma unroll
+        for (int s = 0; s < NS; s++) dLr[s][k] = dLg[s][k] = dLb[s][k] = 0.f;
+        bgdot[k] = 0.f;
         if (inside) {
-            if (FUSED_LOSS) {
+            if (MODE == 0) {
+                dLr[0][k] = a.dL_dpix[pid];
+                dLg[0][k] = a.dL_dpix[plane + pid];
+                dLb[0][k] = a.dL_dpix[2 * plane + pid];
+                bgdot[k] = __ldg(a.bg) * dLr[0][k] + __ldg(a.bg + 1) * dLg[0][k] + __ldg(a.bg + 2) * dLb[0][k];
+            } else if (MODE == 1) {
                 // residual = truth/255 - rendered (imageIntToLoss, src/Trainer.cu:38-42)
                 const uint32_t t = a.truth[pid];
-                dLr[k] = (float)(t & 0xFF) / 255.0f - a.rendered[pid];
-                dLg[k] = (float)((t >> 8) & 0xFF) / 255.0f - a.rendered[plane + pid];
-                dLb[k] = (float)((t >> 16) & 0xFF) / 255.0f - a.rendered[2 * plane + pid];
+                dLr[0][k] = (float)(t & 0xFF) / 255.0f - a.rendered[pid];
+                dLg[0][k] = (float)((t >> 8) & 0xFF) / 255.0f - a.rendered[plane + pid];
+                dLb[0][k] = (float)((t >> 16) & 0xFF) / 255.0f - a.rendered[2 * plane + pid];
+                bgdot[k] = __ldg(a.bg) * dLr[0][k] + __ldg(a.bg + 1) * dLg[0][k] + __ldg(a.bg + 2) * dLb[0][k];
             } else {
-                dLr[k] = a.dL_dpix[pid];
-                dLg[k] = a.dL_dpix[plane + pid];
-                dLb[k] = a.dL_dpix[2 * plane + pid];
+                // `rendered` is the black-background image C; the white one is fma(1, T, C) = C + T
+                const float cr = a.rendered[pid], cg = a.rendered[plane + pid], cb = a.rendered[2 * plane + pid];
+                const uint32_t tw = a.truth[pid], tb = a.truth2[pid];
+                dLr[0][k] = (float)(tw & 0xFF) / 255.0f - __fadd_rn(cr, Tfin[k]);
+                dLg[0][k] = (float)((tw >> 8) & 0xFF) / 255.0f - __fadd_rn(cg, Tfin[k]);
+                dLb[0][k] = (float)((tw >> 16) & 0xFF) / 255.0f - __fadd_rn(cb, Tfin[k]);
+                dLr[NS - 1][k] = (float)(tb & 0xFF) / 255.0f - cr;
+                dLg[NS - 1][k] = (float)((tb >> 8) & 0xFF) / 255.0f - cg;
+                dLb[NS - 1][k] = (float)((tb >> 16) & 0xFF) / 255.0f - cb;
+                bgdot[k] = dLr[0][k] + dLg[0][k] + dLb[0][k];   // white background (1,1,1)
             }
         }
-        bgdot[k] = bg0 * dLr[k] + bg1 * dLg[k] + bg2 * dLb[k];
         last_alpha[k] = 0.f;
         lcr[k] = lcg[k] = lcb[k] = 0.f;
         arr[k] = arg[k] = arb[k] = 0.f;
@@ -140,9 +196,11 @@ __global__ void __launch_bounds__(RENDER_THREADS, 6) render_bwd_kernel(const Ren
                 const float dx = __fsub_rn(ra.x, pxf);
                 const float bx = __fmul_rn(dx, ra.z);
                 const float cxy = __fmul_rn(dx, ra.w);
-                float v[9];
+                float v[NS][9];
 #pragma unroll
-                for (int q = 0; q < 9; q++) v[q] = 0.f;
+                for (int s = 0; s < NS; s++)
+#pragma unroll
+                    for (int q = 0; q < 9; q++) v[s][q] = 0.f;
                 bool hit = false;
 #pragma unroll
                 for (int k = 0; k < 2; k++) {
@@ -164,58 +222,37 @@ __global__ void __launch_bounds__(RENDER_THREADS, 6) render_bwd_kernel(const Ren
                     arg[k] = fmaf(last_alpha[k], lcg[k] - arg[k], arg[k]);
                     arb[k] = fmaf(last_alpha[k], lcb[k] - arb[k], arb[k]);
                     lcr[k] = rb.z; lcg[k] = rb.w; lcb[k] = rc.x;
-                    float dL_dalpha = (rb.z - arr[k]) * dLr[k] + (rb.w - arg[k]) * dLg[k] + (rc.x - arb[k]) * dLb[k];
-                    v[6] = fmaf(w, dLr[k], v[6]);
-                    v[7] = fmaf(w, dLg[k], v[7]);
-                    v[8] = fmaf(w, dLb[k], v[8]);
                     last_alpha[k] = alpha;
-                    // + background term: alpha also scales how much of bg shows through
-                    dL_dalpha = fmaf(dL_dalpha, T[k], -(Tfin[k] * inv) * bgdot[k]);
-                    const float h = G * dL_dalpha;
-                    const float hx = h * dx, hy = h * dy;
-                    v[0] += h;
-                    v[1] += hx;
-                    v[2] += hy;
-                    v[3] = fmaf(hx, dx, v[3]);
-                    v[4] = fmaf(hx, dy, v[4]);
-                    v[5] = fmaf(hy, dy, v[5]);
+                    const float er = rb.z - arr[k], eg = rb.w - arg[k], eb = rc.x - arb[k];
+                    const float GT = G * T[k];
+#pragma unroll
+                    for (int s = 0; s < NS; s++) {
+                        v[s][6] = fmaf(w, dLr[s][k], v[s][6]);
+                        v[s][7] = fmaf(w, dLg[s][k], v[s][7]);
+                        v[s][8] = fmaf(w, dLb[s][k], v[s][8]);
+                        // h = G * dL/dalpha; the background term (alpha also scales how much of bg shows
+                        // through) exists for a non-black background only
+                        float h = GT * (er * dLr[s][k] + eg * dLg[s][k] + eb * dLb[s][k]);
+                        if (s == 0) h = fmaf(-(G * Tfin[k] * inv), bgdot[k], h);
+                        const float hx = h * dx, hy = h * dy;
+                        v[s][0] += h;
+                        v[s][1] += hx;
+                        v[s][2] += hy;
+                        v[s][3] = fmaf(hx, dx, v[s][3]);
+                        v[s][4] = fmaf(hx, dy, v[s][4]);
+                        v[s][5] = fmaf(hy, dy, v[s][5]);
+                    }
                 }
                 if (!__any_sync(0xffffffffu, hit)) continue;
-                // reduce-scatter butterfly over v[0..7]: afterwards lanes 4q..4q+3 hold the warp sum of v[q]
-                float u[4], t2[2], s1;
-                {
-                    const bool hi = lane & 16;
-#pragma unroll
-                    for (int q = 0; q < 4; q++) {
-                        const float send = hi ? v[q] : v[q + 4];
-                        const float keep = hi ? v[q + 4] : v[q];
-                        u[q] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
-                    }
-                }
-                {
-                    const bool hi = lane & 8;
-#pragma unroll
-                    for (int q = 0; q < 2; q++) {
-                        const float send = hi ? u[q] : u[q + 2];
-                        const float keep = hi ? u[q + 2] : u[q];
-                        t2[q] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
-                    }
-                }
-                {
-                    const bool hi = lane & 4;
-                    const float send = hi ? t2[0] : t2[1];
-                    const float keep = hi ? t2[1] : t2[0];
-                    s1 = keep + __shfl_xor_sync(0xffffffffu, send, 4);
-                }
-                s1 += __shfl_xor_sync(0xffffffffu, s1, 2);
-                s1 += __shfl_xor_sync(0xffffffffu, s1, 1);
-                float s8 = v[8];
-#pragma unroll
-                for (int o = 16; o > 0; o >>= 1) s8 += __shfl_xor_sync(0xffffffffu, s8, o);
                 // lane 4q holds sum q (q = 4*b16 + 2*b8 + b4): GradRec floats 0..7; float 8 from lane 1
-                float* g = reinterpret_cast<float*>(a.grads + ids[j]);
-                if ((lane & 3) == 0) atomicAdd(g + (lane >> 2), s1);
-                if (lane == 1) atomicAdd(g + 8, s8);
+#pragma unroll
+                for (int s = 0; s < NS; s++) {
+                    float s1, s8;
+                    warp_reduce9(v[s], lane, s1, s8);
+                    float* g = reinterpret_cast<float*>((s == 0 ? a.grads : a.grads2) + ids[j]);
+                    if ((lane & 3) == 0) atomicAdd(g + (lane >> 2), s1);
+                    if (lane == 1) atomicAdd(g + 8, s8);
+                }
             }
         }
     }
@@ -226,6 +263,7 @@ __global__ void __launch_bounds__(RENDER_THREADS, 6) render_bwd_kernel(const Ren
 
 void launch_render_bwd(const RenderBwdArgs& a, cudaStream_t s) {
     const dim3 grid(a.grid_x, a.grid_y);
-    if (a.dL_dpix == nullptr) render_bwd_kernel<true><<<grid, RENDER_THREADS, 0, s>>>(a);
-    else render_bwd_kernel<false><<<grid, RENDER_THREADS, 0, s>>>(a);
+    if (a.dL_dpix != nullptr) render_bwd_kernel<0><<<grid, RENDER_THREADS, 0, s>>>(a);
+    else if (a.truth2 == nullptr) render_bwd_kernel<1><<<grid, RENDER_THREADS, 0, s>>>(a);
+    else render_bwd_kernel<2><<<grid, RENDER_THREADS, 0, s>>>(a);
 }

@@ -40,6 +40,8 @@ struct gsb_trainer {
 
     // arenas
     char* geom = nullptr; size_t geom_P = 0; GeomWs g;
+    GradRec* grads2 = nullptr;        // second scratch set: black pass of a fused camera pass
+    bool fuse_wb = true;              // white + black pass of a camera share one forward / one backward walk
     char* bin = nullptr; uint32_t r_cap = 0; BinWs b;
     char* img = nullptr; ImageWs im;
     float* rendered = nullptr;        // [3][H][W]
@@ -77,6 +79,9 @@ int ensure_geom(gsb_trainer* t, size_t P) {
     GSB_CUDA_OK(cudaMemsetAsync(t->geom, 0, bytes, t->stream));   // look-back words and grad scratch start at zero
     t->geom_P = cap;
     t->g.carve(t->geom, cap);
+    if (t->grads2) GSB_CUDA_OK(cudaFree(t->grads2));
+    GSB_CUDA_OK(cudaMalloc(&t->grads2, cap * sizeof(GradRec)));
+    GSB_CUDA_OK(cudaMemsetAsync(t->grads2, 0, cap * sizeof(GradRec), t->stream));
     return GSB_OK;
 }
 
@@ -167,16 +172,17 @@ int forward_pass(gsb_trainer* t, const float* view, const float* projview, const
     return fin + 100;
 }
 
-// loss + backward + accumulate of training view pass i (white passes first, then black: T:311-314)
-int backward_pass(gsb_trainer* t, int i, int fin, float* avg, float S, cudaEvent_t* ev = nullptr) {
+// loss + backward + accumulate.  Unfused: training view pass i of 2n (white passes first, then black,
+// T:311-314).  Fused: camera i of n, both backgrounds in one walk (the forward ran on black).
+int backward_pass(gsb_trainer* t, int i, bool fused, int fin, float* avg, float S, cudaEvent_t* ev = nullptr) {
     cudaStream_t s = t->stream;
     const int n = (int)t->truthW.size();
-    const bool white = i < n;
+    const bool white = fused || i < n;
     const int cam = i % n;
     const uint32_t* truth = white ? t->truthW[cam] : t->truthB[cam];
     const gsb_camera* dc = t->d_cams + cam;
-    const float* bg = t->d_bg + (white ? 0 : 3);
-    if (t->loss_on) {
+    const float* bg = t->d_bg + ((white && !fused) ? 0 : 3);
+    if (t->loss_on && !fused) {
         launch_sum_sq_residual(truth, t->rendered, t->W, t->H, t->d_loss, s);
         t->stats.kernel_launches++;
     }
@@ -186,6 +192,7 @@ int backward_pass(gsb_trainer* t, int i, int fin, float* avg, float S, cudaEvent
     rb.ranges = t->im.ranges; rb.point_list = t->b.rvals[fin]; rb.recs = t->g.recs; rb.bg = bg;
     rb.final_T = t->im.final_T; rb.n_contrib = t->im.n_contrib; rb.tile_max = t->im.tile_max;
     rb.dL_dpix = nullptr; rb.truth = truth; rb.rendered = t->rendered; rb.grads = t->g.grads;
+    rb.truth2 = fused ? t->truthB[cam] : nullptr; rb.grads2 = fused ? t->grads2 : nullptr;
     launch_render_bwd(rb, s);
 
     mark(ev, ST_PREPROCESS_BWD, s);
@@ -201,20 +208,25 @@ int backward_pass(gsb_trainer* t, int i, int fin, float* avg, float S, cudaEvent
     pb.radii = t->g.radii; pb.clamped = t->g.clamped; pb.grads = t->g.grads; pb.recs = t->g.recs; pb.W = t->W; pb.H = t->H;
     pb.avg = avg; pb.samples = S;
     launch_preprocess_bwd(pb, s);
-    mark(ev, ST_COUNT, s);
     t->stats.kernel_launches += 2;
+    if (fused) {
+        pb.grads = t->grads2;      // the black pass: its own var term, same running means
+        launch_preprocess_bwd(pb, s);
+        t->stats.kernel_launches++;
+    }
+    mark(ev, ST_COUNT, s);
     return GSB_OK;
 }
 
-int view_pass(gsb_trainer* t, int i, float* avg, float S, cudaEvent_t* ev = nullptr) {
+int view_pass(gsb_trainer* t, int i, bool fused, float* avg, float S, cudaEvent_t* ev = nullptr) {
     const int n = (int)t->truthW.size();
     const int cam = i % n;
     const gsb_camera* dc = t->d_cams + cam;
-    const float* bg = t->d_bg + ((i < n) ? 0 : 3);
+    const float* bg = t->d_bg + ((!fused && i < n) ? 0 : 3);
     const int r = forward_pass(t, dc->view, dc->projview, dc->location, t->cams[cam].tan_fovx, t->cams[cam].tan_fovy, 1.0f, bg,
                                t->W, t->H, t->im, t->rendered, t->h_R + i, ev);
     if (r < 100) return r;
-    return backward_pass(t, i, r - 100, avg, S, ev);
+    return backward_pass(t, i, fused, r - 100, avg, S, ev);
 }
 
 }  // namespace
@@ -252,7 +264,7 @@ int gsb_trainer_create(gsb_trainer** out, int width, int height, void* stream) {
 int gsb_trainer_destroy(gsb_trainer* t) {
     if (!t) return GSB_OK;
     cudaStreamSynchronize(t->stream);
-    cudaFree(t->d_cams); cudaFree(t->d_pcam); cudaFree(t->d_bg); cudaFree(t->geom); cudaFree(t->bin); cudaFree(t->img); cudaFree(t->rendered);
+    cudaFree(t->d_cams); cudaFree(t->d_pcam); cudaFree(t->d_bg); cudaFree(t->geom); cudaFree(t->grads2); cudaFree(t->bin); cudaFree(t->img); cudaFree(t->rendered);
     cudaFree(t->pimg); cudaFree(t->pcolor); cudaFree(t->avg_own); cudaFree(t->d_loss);
     cudaFree(t->flags); cudaFree(t->keep_idx); cudaFree(t->aux_idx); cudaFree(t->totals); cudaFree(t->dens_ticket);
     cudaFree(t->dens_lb);
@@ -309,6 +321,12 @@ int gsb_trainer_set_allreduce(gsb_trainer* t, gsb_allreduce_fn fn, void* user) {
 }
 
 
+int gsb_trainer_set_fuse_backgrounds(gsb_trainer* t, int on) {
+    if (!t) return gsb_fail_msg("gsb_trainer_set_fuse_backgrounds: null trainer");
+    t->fuse_wb = on != 0;
+    return GSB_OK;
+}
+
 int gsb_trainer_enable_loss(gsb_trainer* t, int on) {
     if (!t) return gsb_fail_msg("gsb_trainer_enable_loss: null trainer");
     t->loss_on = on != 0;
@@ -343,13 +361,16 @@ int gsb_trainer_accumulate(gsb_trainer* t) {
     for (int attempt = 0; attempt < 4; attempt++) {
         GSB_CUDA_OK(cudaMemsetAsync(avg, 0, grad_floats(t) * sizeof(float), s));
         if (t->loss_on) GSB_CUDA_OK(cudaMemsetAsync(t->d_loss, 0, sizeof(double), s));
-        for (int i = 0; i < 2 * n; i++)
-            if (int e = view_pass(t, i, avg, S)) return e;
+        const bool fused = t->fuse_wb && !t->loss_on;
+        for (int i = 0; i < (fused ? n : 2 * n); i++)
+            if (int e = view_pass(t, i, fused, avg, S)) return e;
         GSB_CUDA_OK(cudaGetLastError());
         // one synchronisation per iteration: learn every view's R, detect arena overflow
         GSB_CUDA_OK(cudaStreamSynchronize(s));
         uint32_t maxR = 0;
         long long total = 0;
+        if (fused)
+            for (int i = 0; i < n; i++) t->h_R[n + i] = t->h_R[i];   // the black pass shares the white pass's lists
         for (int i = 0; i < 2 * n; i++) { maxR = std::max(maxR, t->h_R[i]); total += t->h_R[i]; }
         t->stats.rendered_total = total;
         t->stats.views = 2 * n;
@@ -361,6 +382,7 @@ int gsb_trainer_accumulate(gsb_trainer* t) {
         // (self-clearing) scratch was written, so grow the arena and redo the iteration.
         t->stats.retries++;
         GSB_CUDA_OK(cudaMemsetAsync(t->g.grads, 0, (size_t)t->geom_P * sizeof(GradRec), s));
+        GSB_CUDA_OK(cudaMemsetAsync(t->grads2, 0, (size_t)t->geom_P * sizeof(GradRec), s));
         if (int e = ensure_bin(t, (uint32_t)std::min<size_t>(0x7FFFFFF0u, (size_t)maxR + maxR / 4 + 4096))) return e;
     }
     gsb_fail_msg("gsb_trainer_accumulate: binning arena kept overflowing");
@@ -370,13 +392,14 @@ int gsb_trainer_accumulate(gsb_trainer* t) {
 int gsb_trainer_profile_pass(gsb_trainer* t, int pass_index, float* stage_ms, unsigned int* counters) {
     if (!t || !stage_ms) return gsb_fail_msg("gsb_trainer_profile_pass: invalid argument");
     const int n = (int)t->truthW.size();
-    if (n == 0 || pass_index < 0 || pass_index >= 2 * n || t->count <= 0 || !t->geom || !t->bin) {
+    const bool fused = t->fuse_wb && !t->loss_on;
+    if (n == 0 || pass_index < 0 || pass_index >= (fused ? n : 2 * n) || t->count <= 0 || !t->geom || !t->bin) {
         gsb_fail_msg("gsb_trainer_profile_pass: run gsb_trainer_accumulate once first");
         return GSB_ERR_STATE;
     }
     cudaEvent_t ev[ST_COUNT + 1];
     for (int k = 0; k <= ST_COUNT; k++) GSB_CUDA_OK(cudaEventCreate(&ev[k]));
-    const int e = view_pass(t, pass_index, avg_ptr(t), 2.0f * (float)t->total_cameras, ev);
+    const int e = view_pass(t, pass_index, fused, avg_ptr(t), 2.0f * (float)t->total_cameras, ev);
     if (e) return e;
     GSB_CUDA_OK(cudaStreamSynchronize(t->stream));
     for (int k = 0; k < ST_COUNT; k++) GSB_CUDA_OK(cudaEventElapsedTime(&stage_ms[k], ev[k], ev[k + 1]));

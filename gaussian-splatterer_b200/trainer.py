@@ -223,6 +223,10 @@ class Trainer:
         self._allreduce_cb = ALLREDUCE_FN(hook)
         check(lib().gsb_trainer_set_allreduce(self._h, self._allreduce_cb, None))
 
+    def set_fuse_backgrounds(self, on=True):
+        """White + black pass of a camera in one forward / one backward walk (default on)."""
+        check(lib().gsb_trainer_set_fuse_backgrounds(self._h, int(on)))
+
     def enable_loss(self, on=True):
         check(lib().gsb_trainer_enable_loss(self._h, int(on)))
 

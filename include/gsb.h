@@ -180,6 +180,10 @@ typedef struct gsb_trainer_stats {
 } gsb_trainer_stats;
 int gsb_trainer_get_stats(gsb_trainer* t, gsb_trainer_stats* out);
 int gsb_trainer_enable_loss(gsb_trainer* t, int on);
+/* White and black pass of a camera (T:311-314) share preprocess, sorts, the forward blend and the
+ * alpha / T recomputation of the backward walk (default on; same results up to the summation order
+ * of the running means).  0 = one full pass per (camera, background) in the reference's order. */
+int gsb_trainer_set_fuse_backgrounds(gsb_trainer* t, int on);
 
 /* Measurement: run training view pass `pass_index` (0..2n-1, white passes first) once with CUDA
  * events between its stages and return the milliseconds of each, in this order:

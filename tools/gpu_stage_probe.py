@@ -62,6 +62,8 @@ def main():
                                            cloud["rotations"])
     tr = gsb.Trainer(W, Hh, dev)
     tr.model = gsb.ModelSplatsDevice(host, dev)
+    fuse = "--nofuse" not in sys.argv
+    tr.set_fuse_backgrounds(fuse)
     tr.truthFrameBuffersW, tr.truthFrameBuffersB, tr.truthCameras = tw, tb, cams
     for _ in range(3):
         tr.train(project, False)
@@ -78,14 +80,15 @@ def main():
     print(json.dumps({"impl": "gsb", "cfg": cfg, "cams": len(cams), "ms_per_iter": ms, "ms_per_view": ms / nv,
                       "views_per_s": nv / ms * 1000, "stats": tr.stats(), "ppt": [fwd_ppt, bwd_ppt]}), flush=True)
     tot = {}
-    for i in range(nv):
+    for i in range(nv // 2 if fuse else nv):
         st, cnt = tr.profile_pass(i)
         print(f"pass {i:2d} R={cnt['R']:8d} vis={cnt['visible']:7d} " + " ".join(f"{k}={v * 1000:6.0f}us" for k, v in st.items()),
               flush=True)
         for k, v in st.items():
             tot[k] = tot.get(k, 0.0) + v
     s = sum(tot.values())
-    print("mean/view: " + " ".join(f"{k}={v / nv * 1000:.0f}us({100 * v / s:.0f}%)" for k, v in tot.items()) +
+    print(("mean/view (fused pairs): " if fuse else "mean/view: ") +
+          " ".join(f"{k}={v / nv * 1000:.0f}us({100 * v / s:.0f}%)" for k, v in tot.items()) +
           f" total={s / nv * 1000:.0f}us", flush=True)
 
     if not noref:
