@@ -115,6 +115,9 @@ def lib():
 # Every symbol include/gsb.h declares; the CPU test-suite checks the library exports all of them.
 EXPORTED_SYMBOLS = [
     "gsb_last_error", "gsb_version", "gsb_rasterizer_forward", "gsb_rasterizer_backward",
+    "gsb_rasterizer_mark_visible", "gsb_rasterizer_state", "gsb_rasterizer_sorted_keys",
+    "gsb_trainer_enable_loss", "gsb_trainer_set_fuse_backgrounds", "gsb_trainer_profile_pass",
+    "gsb_image_float_to_int", "gsb_image_int_to_loss",
     "gsb_trainer_create", "gsb_trainer_destroy", "gsb_trainer_bind_model", "gsb_trainer_set_truths",
     "gsb_trainer_set_grad_buffer", "gsb_trainer_grad_floats", "gsb_trainer_grad_buffer",
     "gsb_trainer_set_allreduce", "gsb_trainer_accumulate", "gsb_trainer_apply", "gsb_trainer_train",
