@@ -1,0 +1,486 @@
+#!/usr/bin/env python
+"""bench.py -- views/s (forward + loss + backward + accumulate, apply once per iteration) of the
+training hot path at BASELINE.json's config C4: 32+32 cameras, 1920x1080, 500k splats.
+
+    python bench.py --gpus N --steps K --warmup W            # this repository's CUDA path
+    python bench.py --impl reference --gpus N ...            # the reference's own CUDA build (oracle/_ref)
+
+One step = one Trainer::train iteration over all 64 cameras x 2 backgrounds = 128 view passes
+(reference src/Trainer.cu:252-435).  With N ranks the cameras are partitioned (rank r takes cameras
+r, r+N, ... of each sphere), splats are replicated, and the 24 running-mean floats per splat are
+summed with one NCCL all-reduce per iteration before applyGradients: total work is fixed, so
+`scaling` is "strong".
+
+value   views/s with every input resident in HBM, CUDA events around K steps, max over ranks.
+e2e     the same through Trainer.train with the truth frames in pinned HOST memory: every step
+        uploads that step's RGBA8 truth frames (double-buffered on a copy stream) and reads the
+        loss scalar back.
+roofline  dominant kernel = render backward: achieved FP32 FLOP/s from the reference's per-pair
+        FLOP counts and the kernel's mean launch time measured live with CUDA events
+        inside the timed region.  No stage of this path is a dense contraction or HBM-bound at the
+        top, so the bound is the FP32 SIMT issue rate; the whole-step HBM figure is reported beside it.
+cpu_baseline  the scalar C++ oracle (oracle/liboracle.so, one host thread) on ONE view pass of the
+        same workload -- context only; the graded baseline is `--impl reference`: the reference has
+        no CPU path, its own code for this path is CUDA (north_star).
+"""
+import argparse
+import importlib
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+METRIC = "views/s fwd+bwd+update @500k splats 1080p"
+UNIT = "views/s"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", choices=("gsb", "reference"), default="gsb")
+    ap.add_argument("--config", default="C4", help="BASELINE config (C1..C5); the metric is quoted on C4")
+    ap.add_argument("--cameras", type=int, default=0, help="override cameras per sphere (debug; invalidates the metric)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-fuse", action="store_true", help="one full pass per (camera, background) like the reference")
+    return ap.parse_args()
+
+
+# ---------------------------------------------------------------------------------------------
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+    NAMES = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
+
+    def __init__(self, gpu_id):
+        self.gpu_id, self.proc, self.path = gpu_id, None, None
+
+    def start(self):
+        try:
+            fd, self.path = tempfile.mkstemp(suffix=".csv")
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu_id), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=fd, stderr=subprocess.DEVNULL)
+            os.close(fd)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, pw, reasons = [], [], [], set()
+        with open(self.path) as f:
+            for line in f:
+                c = [x.strip() for x in line.split(",")]
+                if len(c) < 9:
+                    continue
+                try:
+                    sm.append(float(c[1])); mx.append(float(c[2])); pw.append(float(c[3]))
+                except ValueError:
+                    continue
+                for name, v in zip(self.NAMES, c[5:9]):
+                    if v == "Active":
+                        reasons.add(name)
+        os.unlink(self.path)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": max(mx), "power_w_max": max(pw), "samples": len(sm),
+                "reasons": sorted(reasons)}
+
+
+def gpu_identifier(torch, dev_index):
+    try:
+        u = str(torch.cuda.get_device_properties(dev_index).uuid)
+        return u if u.startswith("GPU-") else "GPU-" + u
+    except Exception:
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+        if vis:
+            return vis.split(",")[dev_index]
+        return dev_index
+
+
+def init_dist(args):
+    import torch
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py needs a CUDA device: this path has no CPU fallback")
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist_
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist = dist_
+        if not (args.impl == "reference"):
+            dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", local))
+    return torch, dist, rank, world, local
+
+
+# ---------------------------------------------------------------------------------------------
+def build_scene(gsb, args, rank, world):
+    """Student cloud, teacher cloud and the camera set of the config; cameras sharded by rank."""
+    cfg = args.config
+    W, H, P = gsb.synth.CONFIGS[cfg]
+    project = gsb.synth.project_for(cfg)
+    if args.cameras > 0:
+        project.sphere1.count = args.cameras
+        project.sphere2.count = args.cameras if project.sphere2.count > 0 else 0
+    cams = gsb.Camera.getCameras(project)
+    seed = 0x5EED0000 + int(cfg[1])
+    cloud = gsb.synth.splat_cloud(P, seed)
+    teacher = gsb.synth.splat_cloud(P // 2, seed + 1)
+    mine = gsb.synth.shard_cameras(cams, project.sphere1.count, rank, world)
+    return {"W": W, "H": H, "P": P, "project": project, "cams": cams, "mine": mine, "cloud": cloud, "teacher": teacher}
+
+
+def render_truths(torch, H, gsb, scene, dev, forward_fn, quantise_fn):
+    """Teacher cloud on white and black, quantised like imageFloatToInt (src/Trainer.cu:19-29): the
+    stand-in for captureTruths (the OptiX truth tracer is unavailable on this box)."""
+    W, Hh = scene["W"], scene["H"]
+    sc = H.scene_tensors(scene["teacher"], dev)
+    Pt = scene["teacher"]["opacities"].shape[0]
+    tw, tb, consts = [], [], []
+    for cam in scene["mine"]:
+        c = cam.view_constants(W, Hh, square_fov=(W == Hh))
+        consts.append(c)
+        for bg, dst in (((1.0, 1.0, 1.0), tw), ((0.0, 0.0, 0.0), tb)):
+            vw = H.view_tensors(c, bg, dev)
+            out = forward_fn(sc, vw, Pt, 1, 4, W, Hh)
+            fb = torch.empty(W * Hh, dtype=torch.int32, device=dev)
+            quantise_fn(out, fb, W, Hh)
+            dst.append(fb)
+    torch.cuda.synchronize()
+    return tw, tb, consts
+
+
+def timed_steps(torch, dist, step_fn, steps):
+    """K steps between barrier + synchronize, CUDA events on the launching (legacy default) stream;
+    returns the max over ranks of the elapsed milliseconds."""
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    if dist is not None and dist.is_initialized():
+        dist.barrier()
+    torch.cuda.synchronize()
+    e0.record()
+    for k in range(steps):
+        step_fn(k)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    if dist is not None and dist.is_initialized():
+        t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+        dist.barrier()
+    return ms
+
+
+STREAM_BYTES = {  # algorithmic bytes per view pass and stage group, SURVEY.md 8(d)
+    "preprocess": lambda c: 100 * c["P"] + 67 * c["Pv"],
+    "binning": lambda c: 8 * c["P"] + 20 * c["P"] + 12 * c["R"] + 152 * c["R"] + 8 * c["R"] + 16 * c["tiles"],
+    "preprocess_bwd": lambda c: (92 + 243) * c["Pv"] + 284 * c["P"],
+}
+
+
+def fused_step_bytes(c):
+    """B_fused of SURVEY.md 8(d): external inputs/outputs of one view pass of a fused design."""
+    return 128 * c["P"] + 526 * c["Pv"] + 252 * c["R"] + 44 * c["N_pix"]
+
+
+def fwd_flops(pc):
+    return 11 * pc["eval_f"] + 3 * pc["exp_f"] + 11 * pc["blend_f"]
+
+
+def bwd_flops(pc):
+    return 11 * pc["eval_b"] + 3 * pc["exp_b"] + 64 * pc["blend_b"]
+
+
+# ---------------------------------------------------------------------------------------------
+def cpu_baseline_port(gsb, scene, truth_white0):
+    """One view pass (forward + loss + backward + accumulate) of the same workload on the scalar C++
+    oracle, one host thread.  Context only."""
+    import numpy as np
+    from oracle import pyoracle
+    W, Hh, P, cloud = scene["W"], scene["H"], scene["P"], scene["cloud"]
+    cs = scene["mine"][0].view_constants(W, Hh, square_fov=(W == Hh))
+    M = 4
+    avg = [np.zeros(k, np.float32) for k in (P, 3 * P, 3 * M * P, 3 * P, P, 4 * P)]
+    t0 = time.perf_counter()
+    out, v = pyoracle.forward(P, 1, M, (1.0, 1.0, 1.0), W, Hh, cloud["locations"], cloud["shs"], None, cloud["opacities"],
+                              cloud["scales"], 1.0, cloud["rotations"], None, cs["view"], cs["projview"], cs["location"],
+                              cs["tan_fovx"], cs["tan_fovy"])
+    loss = pyoracle.image_int_to_loss(truth_white0, out, W, Hh)
+    g = v.backward(loss, M)
+    pyoracle.accumulate(avg, [g["dL_dmean3D"], g["dL_dsh"], g["dL_dscale"], g["dL_dopacity"], g["dL_drot"]],
+                        2.0 * len(scene["cams"]), M, P)
+    dt = time.perf_counter() - t0
+    v.close()
+    return {"value": 1.0 / dt, "unit": UNIT, "cores": 1, "kind": "port", "host_cores_total": os.cpu_count(),
+            "sample": f"1 view pass (camera 0, white background; forward+loss+backward+accumulate) of {P} splats at "
+                      f"{W}x{Hh} on oracle/liboracle.so, {dt:.1f} s; the reference has no CPU path"}
+
+
+def run_gsb(args):
+    torch, dist, rank, world, local = init_dist(args)
+    import numpy as np
+    import helpers as H
+    gsb = H.gsb
+    dev = f"cuda:{local}"
+    scene = build_scene(gsb, args, rank, world)
+    W, Hh, P = scene["W"], scene["H"], scene["P"]
+    project, mine = scene["project"], scene["mine"]
+    n_local, n_total = len(mine), len(scene["cams"])
+    views_per_step = 2 * n_total
+
+    L = gsb.lib()
+    tw, tb, _ = render_truths(torch, H, gsb, scene, dev,
+                              lambda sc, vw, *a: H.run_forward_gsb(sc, vw, *a)[1],
+                              lambda out, fb, w, h: L.gsb_image_float_to_int(out.data_ptr(), fb.data_ptr(), w, h, None))
+    cloud = scene["cloud"]
+    host = gsb.ModelSplatsHost.from_arrays(*[cloud[k] for k in ("locations", "shs", "scales", "opacities", "rotations")])
+
+    def new_trainer():
+        tr = gsb.Trainer(W, Hh, dev)
+        tr.set_fuse_backgrounds(not args.no_fuse)
+        tr.set_total_cameras(n_total)
+        tr.model = gsb.ModelSplatsDevice(host, dev)
+        tr.truthFrameBuffersW, tr.truthFrameBuffersB, tr.truthCameras = list(tw), list(tb), mine
+        if world > 1:
+            tr.set_allreduce(lambda t: dist.all_reduce(t, op=dist.ReduceOp.SUM))
+        return tr
+
+    # ---- value: inputs resident in HBM ------------------------------------------------------
+    tr = new_trainer()
+    for _ in range(args.warmup):
+        tr.train(project, False)
+    launches0 = tr.stats()["kernel_launches"]
+    tr.set_stage_timing(True)
+    sampler = ClockSampler(gpu_identifier(torch, local))
+    if rank == 0:
+        sampler.start()
+    ms = timed_steps(torch, dist, lambda k: tr.train(project, False), args.steps)
+    clocks = sampler.stop() if rank == 0 else None
+    stage_ms, passes = tr.stage_times()
+    tr.set_stage_timing(False)
+    stats = tr.stats()
+    launches = stats["kernel_launches"] - launches0
+    value = views_per_step * args.steps / (ms / 1000.0)
+
+    # ---- counters for the roofline (after the timed region) ----------------------------------
+    pcs = [tr.count_pairs(i) for i in range(n_local)]
+    mean = lambda k: float(sum(p[k] for p in pcs)) / max(len(pcs), 1)
+    tiles = ((W + 15) // 16) * ((Hh + 15) // 16)
+    cnt = {"P": P, "Pv": mean("visible"), "R": mean("R"), "N_pix": W * Hh, "tiles": tiles}
+    pair = {k: mean(k) for k in ("eval_f", "exp_f", "blend_f", "eval_b", "exp_b", "blend_b")}
+    fused = not args.no_fuse
+    units = 2 if fused else 1                     # view passes one launch of a stage serves
+    per_launch = {k: v / max(passes, 1) for k, v in stage_ms.items()}
+    tr.close()
+
+    # ---- e2e: truth frames in pinned host memory, uploaded every step, loss read back --------
+    e2e = None
+    if not args.no_e2e:
+        tr = new_trainer()
+        tr.enable_loss(True)
+        host_w = [t.cpu().pin_memory() for t in tw]
+        host_b = [t.cpu().pin_memory() for t in tb]
+        dset = [(list(tw), list(tb)), ([torch.empty_like(t) for t in tw], [torch.empty_like(t) for t in tb])]
+        copy_stream = torch.cuda.Stream()
+        up_ev = [torch.cuda.Event(), torch.cuda.Event()]
+        losses = []
+
+        def upload(which):
+            with torch.cuda.stream(copy_stream):
+                for d, h in zip(dset[which][0] + dset[which][1], host_w + host_b):
+                    d.copy_(h, non_blocking=True)
+                up_ev[which].record(copy_stream)
+
+        def step(k):
+            cur = k & 1
+            torch.cuda.current_stream().wait_event(up_ev[cur])    # this step's inputs have landed
+            upload(cur ^ 1)                                       # next step's inputs, overlapped
+            tr.truthFrameBuffersW, tr.truthFrameBuffersB = dset[cur]
+            tr.train(project, False)
+            losses.append(tr.stats()["sum_sq_residual"])          # device -> host read of the step's result
+
+        upload(0)
+        for k in range(2 * ((args.warmup + 1) // 2)):             # even count: the timed loop starts on set 0
+            step(k)
+        ms_e = timed_steps(torch, dist, step, args.steps)
+        h2d = n_local * 2 * W * Hh * 4 + n_local * 148
+        e2e = {"value": views_per_step * args.steps / (ms_e / 1000.0), "unit": UNIT, "h2d_bytes_per_step": h2d,
+               "d2h_bytes_per_step": 8 + 4 * 2 * n_local, "ms_per_step": ms_e / args.steps,
+               "result": "sum of squared residuals", "last_loss": losses[-1],
+               "how": "Trainer.train with RGBA8 truth frames in pinned host memory; cudaMemcpyAsync of the next step's "
+                      "frames on a copy stream overlaps the current step; per rank"}
+        tr.close()
+
+    if rank != 0:
+        return
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
+    hbm_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650 GB/s"
+    sm_max = float((clocks or {}).get("sm_max_mhz") or peaks.get("sm_max_mhz", 1965.0))
+    fp32_peak = 2 * 128 * 148 * sm_max * 1e6 / 1e12
+    traffic = None
+    try:
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+    except Exception:
+        traffic = {}
+
+    bwd_ms = per_launch["render_bwd"]
+    bwd_fl = units * bwd_flops(pair)
+    fwd_ms = per_launch["render_fwd"]
+    stages = {}
+    total_stage_ms = sum(per_launch.values())
+    for k, v in per_launch.items():
+        stages[k] = {"ms_per_launch": round(v, 4), "share": round(v / total_stage_ms, 4) if total_stage_ms else None}
+    stages["render_fwd"].update({"tflops": fwd_flops(pair) / (fwd_ms * 1e-3) / 1e12 if fwd_ms else None,
+                                 "frac_fp32": fwd_flops(pair) / (fwd_ms * 1e-3) / 1e12 / fp32_peak if fwd_ms else None})
+    bin_ms = sum(per_launch[k] for k in ("depth_sort", "scan", "emit", "tile_sort", "ranges"))
+    for name, ms_k in (("preprocess", per_launch["preprocess"]), ("binning", bin_ms),
+                       ("preprocess_bwd", per_launch["preprocess_bwd"])):
+        by = STREAM_BYTES[name](cnt) * (units if name == "preprocess_bwd" else 1)
+        gbs = by / (ms_k * 1e-3) / 1e9 if ms_k else None
+        stages.setdefault(name, {}).update({"algorithmic_bytes": by, "gb_s": gbs, "frac_hbm": gbs / hbm_peak if gbs else None,
+                                            "ms_per_launch": round(ms_k, 4)})
+    step_bytes = views_per_step / world * fused_step_bytes(cnt)        # per rank and step
+    step_gbs = step_bytes / (ms / args.steps * 1e-3) / 1e9
+
+    out = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"{args.config}: {n_total} cameras x 2 backgrounds = {views_per_step} view passes per step, "
+                               f"{W}x{Hh}, {P} splats, SH degree 1; cameras partitioned over {world} GPU(s), splats replicated",
+                   "views_per_step": views_per_step, "cameras_per_rank": n_local,
+                   "fused_white_black": fused, "parallelism": f"camera-sharded x{world}, NCCL all-reduce of 24 floats/splat",
+                   "l2": "inputs larger than L2: every step streams > 1 GB of truth frames, parameters and per-view state "
+                         "through the 126 MB L2; no explicit flush"},
+        "gpu_launches": int(launches),
+        "clocks": clocks,
+        "counters_per_view": {**{k: round(v, 1) for k, v in cnt.items()}, **{k: round(v, 1) for k, v in pair.items()}},
+        "roofline": {"bound": "fp32", "kernel": "render_bwd_kernel<%d>" % (2 if fused else 1),
+                     "achieved": bwd_fl / (bwd_ms * 1e-3) / 1e12 if bwd_ms else None, "peak": fp32_peak, "unit": "TFLOP/s",
+                     "frac": bwd_fl / (bwd_ms * 1e-3) / 1e12 / fp32_peak if bwd_ms else None,
+                     "traffic": traffic.get("render_bwd"),
+                     "flops_per_launch": bwd_fl, "ms_per_launch": bwd_ms, "share_of_step": stages["render_bwd"]["share"],
+                     "view_passes_per_launch": units,
+                     "peak_source": f"FP32 SIMT issue peak 2 x 128 lanes x 148 SMs x clocks.max.sm ({sm_max:.0f} MHz); no stage "
+                                    "is HBM- or tensor-bound at the top (SURVEY.md 8d), MEASURED_PEAKS.json holds no FP32 figure",
+                     "step_hbm": {"bound": "hbm", "achieved": step_gbs, "peak": hbm_peak, "unit": "GB/s",
+                                  "frac": step_gbs / hbm_peak, "bytes_per_step_per_rank": step_bytes, "peak_source": hbm_src}},
+        "stages": stages,
+        "stats": {"rendered_per_step": stats["rendered_total"], "retries": stats["retries"]},
+    }
+    if e2e is not None:
+        out["e2e"] = e2e
+    if world == 1 and not args.no_cpu_baseline:
+        out["cpu_baseline"] = cpu_baseline_port(gsb, scene, tw[0].cpu().numpy().view(np.uint32))
+    print(json.dumps(out), flush=True)
+
+
+# ---------------------------------------------------------------------------------------------
+def run_reference(args):
+    """The reference's own implementation of the path: its UNMODIFIED CUDA rasterizer compiled for
+    sm_100 (oracle/_ref/libgsref.so) driven in Trainer::train's exact call order.  The reference has
+    no CPU path and no multi-GPU path: rank 0 runs the whole job on one GPU, other ranks exit."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import torch
+    if not torch.cuda.is_available():
+        raise RuntimeError("the reference's implementation of this path is CUDA: a GPU is required")
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    import helpers as H
+    from oracle import refshim
+    gsb = H.gsb                                    # host-side scene / camera generation only
+    if not refshim.available():
+        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/libgsref.so was not built (needs /root/reference)"}))
+        return
+    dev = f"cuda:{local}"
+    scene = build_scene(gsb, args, 0, 1)
+    W, Hh, P = scene["W"], scene["H"], scene["P"]
+    project = scene["project"]
+    n_total = len(scene["cams"])
+    views_per_step = 2 * n_total
+    tw, tb, consts = render_truths(torch, H, gsb, scene, dev,
+                                   lambda sc, vw, *a: H.run_forward_ref(sc, vw, *a)[0],
+                                   lambda out, fb, w, h: refshim.image_float_to_int(out, fb, w, h))
+    cloud = scene["cloud"]
+    rt = refshim.RefTrainer(W, Hh, dev)
+    rt.set_model(cloud, 1000000 if P <= 1000000 else 10000000, 1, 4)
+    rt.set_truths(tw, tb, consts)
+    p13 = project.params13()
+    res = {}
+    clocks = None
+    for name, as_shipped in (("as_shipped", True), ("best_case", False)):
+        for _ in range(args.warmup):
+            rt.train(p13, as_shipped=as_shipped)
+        sampler = ClockSampler(gpu_identifier(torch, local))
+        if not as_shipped:
+            sampler.start()
+        ms = timed_steps(torch, None, lambda k: rt.train(p13, as_shipped=as_shipped), args.steps)
+        if not as_shipped:
+            clocks = sampler.stop()
+        res[name] = {"views_per_s": views_per_step * args.steps / (ms / 1000.0), "ms_per_step": ms / args.steps}
+    rt.close()
+    best = res["best_case"]
+    out = {
+        "impl": "reference", "metric": METRIC, "value": best["views_per_s"], "unit": UNIT, "n_gpus": 1,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": best["ms_per_step"], "higher_is_better": True,
+        "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"{args.config}: {n_total} cameras x 2 backgrounds = {views_per_step} view passes per step, "
+                               f"{W}x{Hh}, {P} splats, SH degree 1; single GPU (the reference has no multi-GPU path)",
+                   "views_per_step": views_per_step,
+                   "variant": "best case for the reference: debug=false, pooled workspaces, no per-view cudaMalloc/cudaFree; "
+                              "the as-shipped call sequence (debug=true, per-view malloc/free) is in `as_shipped`",
+                   "l2": "inputs larger than L2"},
+        "as_shipped": res["as_shipped"],
+        "clocks": clocks,
+        "cpu_baseline": {"value": best["views_per_s"], "unit": UNIT, "cores": 1, "kind": "reference",
+                         "sample": "the reference has no CPU implementation of this path; this is its own CUDA code "
+                                   "(lib/diff-gaussian-rasterization + the Trainer.cu kernels) recompiled for sm_100 and run "
+                                   "on the same B200, one host thread, full workload"},
+        "e2e": {"value": best["views_per_s"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(out), flush=True)
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_gsb(args)
+    try:
+        import torch.distributed as dist
+        if dist.is_initialized():
+            dist.destroy_process_group()
+    except Exception:
+        pass
+
+
+if __name__ == "__main__":
+    main()

@@ -150,8 +150,14 @@ struct RenderBwdArgs {
     // `rendered` the black-background image; the black pass accumulates into grads2
     const uint32_t* truth2;
     GradRec* grads2;
+    double* loss_out;               // optional: += sum of squared residuals (fused-loss modes only)
 };
 void launch_render_bwd(const RenderBwdArgs& a, cudaStream_t s);
+
+// measure.cu -- measurement only: (pixel, splat) pair counts of one view as the reference's
+// algorithm defines them, for the FLOP side of the roofline.
+// out[6] += { E_eval_f, E_exp_f, E_blend_f, E_eval_b, E_exp_b, E_blend_b }
+void launch_count_pairs(const RenderFwdArgs& a, unsigned long long* out, cudaStream_t s);
 
 // preprocess_bwd.cu
 struct PreprocessBwdArgs {

@@ -182,7 +182,7 @@ int gsb_rasterizer_backward(int P, int D, int M, int R, const float* background,
         rb.W = width; rb.H = height; rb.grid_x = grid_x; rb.grid_y = grid_y;
         rb.ranges = im.ranges; rb.point_list = b.rvals[fin]; rb.recs = g.recs; rb.bg = background;
         rb.final_T = im.final_T; rb.n_contrib = im.n_contrib; rb.tile_max = im.tile_max;
-        rb.dL_dpix = dL_dpix; rb.truth = nullptr; rb.rendered = nullptr; rb.grads = g.grads; rb.truth2 = nullptr; rb.grads2 = nullptr;
+        rb.dL_dpix = dL_dpix; rb.truth = nullptr; rb.rendered = nullptr; rb.grads = g.grads; rb.truth2 = nullptr; rb.grads2 = nullptr; rb.loss_out = nullptr;
         launch_render_bwd(rb, s);
         if (int e = check(s, dbg)) return e;
     }

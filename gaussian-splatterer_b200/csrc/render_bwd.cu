@@ -80,7 +80,7 @@ __global__ void __launch_bounds__(RENDER_THREADS, MODE == 2 ? 5 : 6) render_bwd_
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int tile = blockIdx.y * a.grid_x + blockIdx.x;
     const int start = (int)a.tile_max[tile];       // entries at or beyond this index were blended by no pixel
-    if (start == 0) return;
+    if (start == 0 && (MODE == 0 || a.loss_out == nullptr)) return;
     const uint2 range = a.ranges[tile];
     const uint32_t* list = a.point_list + range.x;
     const int rounds = (start + RB - 1) / RB;
@@ -136,6 +136,20 @@ __global__ void __launch_bounds__(RENDER_THREADS, MODE == 2 ? 5 : 6) render_bwd_
         last_alpha[k] = 0.f;
         lcr[k] = lcg[k] = lcb[k] = 0.f;
         arr[k] = arg[k] = arb[k] = 0.f;
+    }
+    if (MODE != 0 && a.loss_out != nullptr) {
+        // monitoring only: sum of squared residuals of the pass(es) this launch serves
+        float sq = 0.f;
+#pragma unroll
+        for (int k = 0; k < 2; k++)
+#pragma unroll
+            for (int s = 0; s < NS; s++)
+                sq += dLr[s][k] * dLr[s][k] + dLg[s][k] * dLg[s][k] + dLb[s][k] * dLb[s][k];
+        double acc = (double)sq;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+        if (lane == 0) atomicAdd(a.loss_out, acc);
+        if (start == 0) return;
     }
     const int warp_max = __reduce_max_sync(0xffffffffu, max(ncontrib[0], ncontrib[1]));
 

@@ -63,6 +63,13 @@ struct gsb_trainer {
     gsb_allreduce_fn allreduce = nullptr; void* allreduce_user = nullptr;
     bool loss_on = false; double* d_loss = nullptr;
     gsb_trainer_stats stats;
+
+    // live stage timing (gsb_trainer_set_stage_timing): one event per stage boundary and view pass
+    bool timing_on = false;
+    std::vector<cudaEvent_t> ev_pool;
+    double stage_ms[GSB_NUM_STAGES] = {0};
+    long long stage_passes = 0;
+    unsigned long long* d_pairs = nullptr;   // gsb_trainer_count_pairs scratch
 };
 
 namespace {
@@ -182,10 +189,6 @@ int backward_pass(gsb_trainer* t, int i, bool fused, int fin, float* avg, float 
     const uint32_t* truth = white ? t->truthW[cam] : t->truthB[cam];
     const gsb_camera* dc = t->d_cams + cam;
     const float* bg = t->d_bg + ((white && !fused) ? 0 : 3);
-    if (t->loss_on && !fused) {
-        launch_sum_sq_residual(truth, t->rendered, t->W, t->H, t->d_loss, s);
-        t->stats.kernel_launches++;
-    }
     mark(ev, ST_RENDER_BWD, s);
     RenderBwdArgs rb;
     rb.W = t->W; rb.H = t->H; rb.grid_x = t->grid_x; rb.grid_y = t->grid_y;
@@ -193,6 +196,7 @@ int backward_pass(gsb_trainer* t, int i, bool fused, int fin, float* avg, float 
     rb.final_T = t->im.final_T; rb.n_contrib = t->im.n_contrib; rb.tile_max = t->im.tile_max;
     rb.dL_dpix = nullptr; rb.truth = truth; rb.rendered = t->rendered; rb.grads = t->g.grads;
     rb.truth2 = fused ? t->truthB[cam] : nullptr; rb.grads2 = fused ? t->grads2 : nullptr;
+    rb.loss_out = t->loss_on ? t->d_loss : nullptr;
     launch_render_bwd(rb, s);
 
     mark(ev, ST_PREPROCESS_BWD, s);
@@ -267,7 +271,8 @@ int gsb_trainer_destroy(gsb_trainer* t) {
     cudaFree(t->d_cams); cudaFree(t->d_pcam); cudaFree(t->d_bg); cudaFree(t->geom); cudaFree(t->grads2); cudaFree(t->bin); cudaFree(t->img); cudaFree(t->rendered);
     cudaFree(t->pimg); cudaFree(t->pcolor); cudaFree(t->avg_own); cudaFree(t->d_loss);
     cudaFree(t->flags); cudaFree(t->keep_idx); cudaFree(t->aux_idx); cudaFree(t->totals); cudaFree(t->dens_ticket);
-    cudaFree(t->dens_lb);
+    cudaFree(t->dens_lb); cudaFree(t->d_pairs);
+    for (cudaEvent_t e : t->ev_pool) cudaEventDestroy(e);
     if (t->h_R) cudaFreeHost(t->h_R);
     delete t;
     return GSB_OK;
@@ -361,9 +366,17 @@ int gsb_trainer_accumulate(gsb_trainer* t) {
     for (int attempt = 0; attempt < 4; attempt++) {
         GSB_CUDA_OK(cudaMemsetAsync(avg, 0, grad_floats(t) * sizeof(float), s));
         if (t->loss_on) GSB_CUDA_OK(cudaMemsetAsync(t->d_loss, 0, sizeof(double), s));
-        const bool fused = t->fuse_wb && !t->loss_on;
-        for (int i = 0; i < (fused ? n : 2 * n); i++)
-            if (int e = view_pass(t, i, fused, avg, S)) return e;
+        const bool fused = t->fuse_wb;
+        const int passes = fused ? n : 2 * n;
+        if (t->timing_on) {
+            while (t->ev_pool.size() < (size_t)passes * (ST_COUNT + 1)) {
+                cudaEvent_t e;
+                GSB_CUDA_OK(cudaEventCreate(&e));
+                t->ev_pool.push_back(e);
+            }
+        }
+        for (int i = 0; i < passes; i++)
+            if (int e = view_pass(t, i, fused, avg, S, t->timing_on ? &t->ev_pool[(size_t)i * (ST_COUNT + 1)] : nullptr)) return e;
         GSB_CUDA_OK(cudaGetLastError());
         // one synchronisation per iteration: learn every view's R, detect arena overflow
         GSB_CUDA_OK(cudaStreamSynchronize(s));
@@ -375,6 +388,16 @@ int gsb_trainer_accumulate(gsb_trainer* t) {
         t->stats.rendered_total = total;
         t->stats.views = 2 * n;
         if (maxR <= t->r_cap) {
+            if (t->timing_on) {
+                for (int i = 0; i < passes; i++)
+                    for (int k = 0; k < ST_COUNT; k++) {
+                        float ms = 0.f;
+                        const cudaEvent_t* ev = &t->ev_pool[(size_t)i * (ST_COUNT + 1)];
+                        GSB_CUDA_OK(cudaEventElapsedTime(&ms, ev[k], ev[k + 1]));
+                        t->stage_ms[k] += ms;
+                    }
+                t->stage_passes += passes;
+            }
             if (t->loss_on) GSB_CUDA_OK(cudaMemcpy(&t->stats.sum_sq_residual, t->d_loss, sizeof(double), cudaMemcpyDeviceToHost));
             return GSB_OK;
         }
@@ -392,7 +415,7 @@ int gsb_trainer_accumulate(gsb_trainer* t) {
 int gsb_trainer_profile_pass(gsb_trainer* t, int pass_index, float* stage_ms, unsigned int* counters) {
     if (!t || !stage_ms) return gsb_fail_msg("gsb_trainer_profile_pass: invalid argument");
     const int n = (int)t->truthW.size();
-    const bool fused = t->fuse_wb && !t->loss_on;
+    const bool fused = t->fuse_wb;
     if (n == 0 || pass_index < 0 || pass_index >= (fused ? n : 2 * n) || t->count <= 0 || !t->geom || !t->bin) {
         gsb_fail_msg("gsb_trainer_profile_pass: run gsb_trainer_accumulate once first");
         return GSB_ERR_STATE;
@@ -408,6 +431,49 @@ int gsb_trainer_profile_pass(gsb_trainer* t, int pass_index, float* stage_ms, un
         counters[0] = t->h_R[pass_index];
         GSB_CUDA_OK(cudaMemcpy(&counters[1], &t->g.ctrl->num_visible, sizeof(unsigned int), cudaMemcpyDeviceToHost));
     }
+    return GSB_OK;
+}
+
+int gsb_trainer_set_stage_timing(gsb_trainer* t, int on) {
+    if (!t) return gsb_fail_msg("gsb_trainer_set_stage_timing: null trainer");
+    t->timing_on = on != 0;
+    for (int k = 0; k < GSB_NUM_STAGES; k++) t->stage_ms[k] = 0.0;
+    t->stage_passes = 0;
+    return GSB_OK;
+}
+
+int gsb_trainer_get_stage_times(gsb_trainer* t, double* stage_ms, long long* passes) {
+    if (!t || !stage_ms || !passes) return gsb_fail_msg("gsb_trainer_get_stage_times: invalid argument");
+    for (int k = 0; k < GSB_NUM_STAGES; k++) stage_ms[k] = t->stage_ms[k];
+    *passes = t->stage_passes;
+    return GSB_OK;
+}
+
+int gsb_trainer_count_pairs(gsb_trainer* t, int camera_index, unsigned long long* out8) {
+    if (!t || !out8) return gsb_fail_msg("gsb_trainer_count_pairs: invalid argument");
+    const int n = (int)t->truthW.size();
+    if (n == 0 || camera_index < 0 || camera_index >= n || t->count <= 0 || !t->geom || !t->bin) {
+        gsb_fail_msg("gsb_trainer_count_pairs: run gsb_trainer_accumulate once first");
+        return GSB_ERR_STATE;
+    }
+    cudaStream_t s = t->stream;
+    if (!t->d_pairs) GSB_CUDA_OK(cudaMalloc(&t->d_pairs, 6 * sizeof(unsigned long long)));
+    GSB_CUDA_OK(cudaMemsetAsync(t->d_pairs, 0, 6 * sizeof(unsigned long long), s));
+    const gsb_camera* dc = t->d_cams + camera_index;
+    const int r = forward_pass(t, dc->view, dc->projview, dc->location, t->cams[camera_index].tan_fovx,
+                               t->cams[camera_index].tan_fovy, 1.0f, t->d_bg + 3, t->W, t->H, t->im, t->rendered, t->h_R);
+    if (r < 100) return r;
+    RenderFwdArgs ra;
+    ra.W = t->W; ra.H = t->H; ra.grid_x = t->grid_x; ra.grid_y = t->grid_y;
+    ra.ranges = t->im.ranges; ra.point_list = t->b.rvals[r - 100]; ra.recs = t->g.recs; ra.bg = t->d_bg + 3;
+    ra.out_color = t->rendered; ra.final_T = t->im.final_T; ra.n_contrib = t->im.n_contrib; ra.tile_max = t->im.tile_max;
+    launch_count_pairs(ra, t->d_pairs, s);
+    GSB_CUDA_OK(cudaMemcpyAsync(out8, t->d_pairs, 6 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
+    uint32_t cnt[2] = {0, 0};
+    GSB_CUDA_OK(cudaMemcpyAsync(cnt, &t->g.ctrl->num_rendered, sizeof(cnt), cudaMemcpyDeviceToHost, s));
+    GSB_CUDA_OK(cudaStreamSynchronize(s));
+    out8[6] = cnt[0];
+    out8[7] = cnt[1];
     return GSB_OK;
 }
 

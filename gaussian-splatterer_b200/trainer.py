@@ -245,6 +245,25 @@ class Trainer:
         check(lib().gsb_trainer_profile_pass(self._h, pass_index, ms, cnt))
         return dict(zip(self.STAGES, [float(x) for x in ms])), {"R": int(cnt[0]), "visible": int(cnt[1])}
 
+    def set_stage_timing(self, on=True):
+        """Bracket every stage of every view pass with CUDA events (resets the totals)."""
+        check(lib().gsb_trainer_set_stage_timing(self._h, int(on)))
+
+    def stage_times(self):
+        """({stage: total ms}, view-pass launches) since set_stage_timing(True)."""
+        ms = (C.c_double * 10)()
+        n = C.c_longlong(0)
+        check(lib().gsb_trainer_get_stage_times(self._h, ms, C.byref(n)))
+        return dict(zip(self.STAGES, [float(x) for x in ms])), int(n.value)
+
+    def count_pairs(self, camera_index):
+        """Pair counts of one local camera under the reference's control flow (roofline FLOPs)."""
+        out = (C.c_ulonglong * 8)()
+        self._bind()
+        self._sync_truths()
+        check(lib().gsb_trainer_count_pairs(self._h, camera_index, out))
+        return dict(zip(("eval_f", "exp_f", "blend_f", "eval_b", "exp_b", "blend_b", "R", "visible"), [int(x) for x in out]))
+
     # -- reference interface -------------------------------------------------------------------
     def render(self, frameBuffer, sizeX, sizeY, splatScale, camera):
         """Trainer::render (src/Trainer.cu:148-216): RGBA8 preview into `frameBuffer` (int32/uint32 tensor)."""

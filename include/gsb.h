@@ -194,6 +194,17 @@ int gsb_trainer_set_fuse_backgrounds(gsb_trainer* t, int on);
 #define GSB_NUM_STAGES 10
 int gsb_trainer_profile_pass(gsb_trainer* t, int pass_index, float* stage_ms, unsigned int* counters);
 
+/* Measurement: with timing on, every view pass of gsb_trainer_accumulate / gsb_trainer_train is
+ * bracketed stage by stage with CUDA events on the trainer's stream; get_stage_times returns the
+ * milliseconds summed per stage (order of gsb_trainer_profile_pass) over `passes` view-pass
+ * launches since timing was switched on (a fused white+black camera pass counts once). */
+int gsb_trainer_set_stage_timing(gsb_trainer* t, int on);
+int gsb_trainer_get_stage_times(gsb_trainer* t, double* stage_ms, long long* passes);
+/* Measurement: (pixel, splat) pair counts of local camera `camera_index` under the reference's
+ * control flow: out8 = { E_eval_f, E_exp_f, E_blend_f, E_eval_b, E_exp_b, E_blend_b, R, visible }
+ * (forward.cu:310-357, backward.cu:476-503).  Needs one prior gsb_trainer_accumulate. */
+int gsb_trainer_count_pairs(gsb_trainer* t, int camera_index, unsigned long long* out8);
+
 /* Image helpers: imageFloatToInt / imageIntToLoss (T:19-44). */
 int gsb_image_float_to_int(const float* dev_src, uint32_t* dev_fb, int w, int h, void* stream);
 int gsb_image_int_to_loss(const uint32_t* dev_truth, const float* dev_rasterized, float* dev_loss,
