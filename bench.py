@@ -41,6 +41,15 @@ METRIC = "views/s fwd+bwd+update @500k splats 1080p"
 UNIT = "views/s"
 
 
+_JSON_OUT = None
+
+
+def emit(obj):
+    f = _JSON_OUT or sys.stdout
+    f.write(json.dumps(obj) + "\n")
+    f.flush()
+
+
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -397,7 +406,7 @@ def run_gsb(args):
         out["e2e"] = e2e
     if world == 1 and not args.no_cpu_baseline:
         out["cpu_baseline"] = cpu_baseline_port(gsb, scene, tw[0].cpu().numpy().view(np.uint32))
-    print(json.dumps(out), flush=True)
+    emit(out)
 
 
 # ---------------------------------------------------------------------------------------------
@@ -417,7 +426,7 @@ def run_reference(args):
     from oracle import refshim
     gsb = H.gsb                                    # host-side scene / camera generation only
     if not refshim.available():
-        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/libgsref.so was not built (needs /root/reference)"}))
+        emit({"impl": "reference", "unavailable": "oracle/_ref/libgsref.so was not built (needs /root/reference)"})
         return
     dev = f"cuda:{local}"
     scene = build_scene(gsb, args, 0, 1)
@@ -465,11 +474,15 @@ def run_reference(args):
                                    "on the same B200, one host thread, full workload"},
         "e2e": {"value": best["views_per_s"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
-    print(json.dumps(out), flush=True)
+    emit(out)
 
 
 def main():
     args = parse_args()
+    # stdout carries exactly one JSON line: libraries that print there (NCCL's version banner) go to stderr
+    global _JSON_OUT
+    _JSON_OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     if args.impl == "reference":
         run_reference(args)
     else:
