@@ -177,6 +177,7 @@ struct PreprocessBwdArgs {
     const int* radii;
     const uint8_t* clamped;
     GradRec* grads;                 // consumed and cleared
+    GradRec* grads2;                // Trainer mode only: second set (black pass of a fused camera pass), or null
     const SplatRec* recs;           // the forward's records (conic, opacity)
     int W, H;
     // mode A (Rasterizer::backward): caller arrays, reference semantics

@@ -30,9 +30,13 @@ __device__ __forceinline__ V3 operator*(float s, V3 v) { return {s * v.x, s * v.
 __device__ __forceinline__ V3 operator+(V3 a, V3 b) { return {a.x + b.x, a.y + b.y, a.z + b.z}; }
 __device__ __forceinline__ float dot(V3 a, V3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
 
-// Writes dL/dsh (M x 3) through `emit(coeff, value)` and returns dL/dmean from the view direction.
+// Derivatives of the colour w.r.t. the (normalised) view direction, plus the unnormalised direction.
+struct ShDirs { V3 d0, dx, dy, dz; };
+
+// Writes dL/dsh (M x 3) through `emit(coeff, value)` for the colour gradient dRGB and returns what the
+// view-direction term of dL/dmean needs (dir_grad below); everything here is linear in dRGB.
 template <typename Emit>
-__device__ V3 sh_backward(int deg, float px, float py, float pz, const float* cam, const float* sh, V3 dRGB, Emit emit) {
+__device__ ShDirs sh_backward(int deg, float px, float py, float pz, const float* cam, const float* sh, V3 dRGB, Emit emit) {
     const V3 d0 = {px - cam[0], py - cam[1], pz - cam[2]};
     const float len = sqrtf(d0.x * d0.x + d0.y * d0.y + d0.z * d0.z);
     const float x = d0.x / len, y = d0.y / len, z = d0.z / len;
@@ -78,8 +82,13 @@ __device__ V3 sh_backward(int deg, float px, float py, float pz, const float* ca
             }
         }
     }
-    // through dir = d0 / |d0|  (dnormvdv, auxiliary.h:108-119)
-    const V3 dd = {dot(dx, dRGB), dot(dy, dRGB), dot(dz, dRGB)};
+    return {d0, dx, dy, dz};
+}
+
+// dL/dmean through dir = d0 / |d0|  (dnormvdv, auxiliary.h:108-119) for one colour gradient
+__device__ __forceinline__ V3 dir_grad(const ShDirs& q, V3 dRGB) {
+    const V3 d0 = q.d0;
+    const V3 dd = {dot(q.dx, dRGB), dot(q.dy, dRGB), dot(q.dz, dRGB)};
     const float sum2 = d0.x * d0.x + d0.y * d0.y + d0.z * d0.z;
     const float inv32 = 1.0f / sqrtf(sum2 * sum2 * sum2);
     V3 g;
@@ -89,44 +98,80 @@ __device__ V3 sh_backward(int deg, float px, float py, float pz, const float* ca
     return g;
 }
 
+// NS = number of GradRec sets consumed in one pass over the splat: 1 everywhere except the Trainer's
+// fused white+black camera pass (NS = 2: a.grads = white pass, a.grads2 = black pass).  Every gradient
+// is linear in a set's moments, so the per-splat geometry (T = W J, Vrk T, the conic Jacobian, the
+// projection Jacobian, the SH direction derivatives) is computed once; only dL/dmean3D is finished
+// per set, because varLocations sums the per-pass norms (src/Trainer.cu:52-54).
+// M4 = the application's shape (SH degree 1, 4 coefficients, src/Config.h:19-20): the 24 running-mean
+// floats of the splat are loaded up front into registers (independent loads in flight together, hidden
+// behind the arithmetic) and stored once at the end, instead of 24 dependent read-modify-writes.
+template <int NS, bool M4>
 __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreprocessBwdArgs a) {
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= a.P || !(a.radii[idx] > 0)) return;
-
-    // take and clear the per-view scratch
-    GradRec g = a.grads[idx];
-    {
-        const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
-        a.grads[idx].a = z; a.grads[idx].b = z; a.grads[idx].c = z;
+    const bool modeA = (a.avg == nullptr);
+    const size_t P = (size_t)a.P;
+    const int M = M4 ? 4 : a.M;
+    float* avg_loc = modeA ? nullptr : a.avg + P;
+    float* avg_sh = modeA ? nullptr : a.avg + 4 * P;
+    float* avg_scale = modeA ? nullptr : a.avg + 4 * P + 3 * (size_t)M * P;
+    float* avg_op = modeA ? nullptr : avg_scale + 3 * P;
+    float* avg_rot = modeA ? nullptr : avg_op + P;
+    float o_var = 0.f, o_loc[3] = {0.f, 0.f, 0.f}, o_op = 0.f, o_scale[3] = {0.f, 0.f, 0.f}, o_rot[4] = {0.f, 0.f, 0.f, 0.f};
+    float o_sh[12];
+    if (!modeA) {
+        o_var = a.avg[idx];
+        o_op = avg_op[idx];
+#pragma unroll
+        for (int k = 0; k < 3; k++) { o_loc[k] = avg_loc[3 * idx + k]; o_scale[k] = avg_scale[3 * idx + k]; }
+#pragma unroll
+        for (int k = 0; k < 4; k++) o_rot[k] = avg_rot[4 * idx + k];
+        if (M4) {
+            const float4* p = reinterpret_cast<const float4*>(avg_sh + 12 * (size_t)idx);   // 48-byte records: 16-byte aligned
+#pragma unroll
+            for (int k = 0; k < 3; k++) {
+                const float4 t = p[k];
+                o_sh[4 * k] = t.x; o_sh[4 * k + 1] = t.y; o_sh[4 * k + 2] = t.z; o_sh[4 * k + 3] = t.w;
+            }
+        }
     }
+
     // The render backward accumulates the moments H0, Hx, Hy, Hxx, Hxy, Hyy of h = G dL/dalpha (see
     // GradRec); the gradients of backward.cu:536-554 are linear in them with per-splat coefficients.
-    float gm2x, gm2y, gcx, gcy, gcw, gop;
+    float gm2x[NS], gm2y[NS], gcx[NS], gcy[NS], gcw[NS], gop[NS];
+    V3 gcol[NS];
     {
         const SplatRec& r = a.recs[idx];
         const float conx = r.a.z, cony = r.a.w, conz = r.b.x, opac = r.b.y;
-        const float H0 = g.a.x, Hx = g.a.y, Hy = g.a.z, Hxx = g.a.w, Hxy = g.b.x, Hyy = g.b.y;
-        gop = H0;
-        gm2x = -(0.5f * a.W) * opac * (conx * Hx + cony * Hy);
-        gm2y = -(0.5f * a.H) * opac * (conz * Hy + cony * Hx);
-        gcx = -0.5f * opac * Hxx;
-        gcy = -0.5f * opac * Hxy;
-        gcw = -0.5f * opac * Hyy;
+#pragma unroll
+        for (int s = 0; s < NS; s++) {
+            GradRec* gp = (s == 0 ? a.grads : a.grads2) + idx;
+            const GradRec g = *gp;
+            const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+            gp->a = z; gp->b = z; gp->c = z;                      // take and clear the per-view scratch
+            const float H0 = g.a.x, Hx = g.a.y, Hy = g.a.z, Hxx = g.a.w, Hxy = g.b.x, Hyy = g.b.y;
+            gop[s] = H0;
+            gm2x[s] = -(0.5f * a.W) * opac * (conx * Hx + cony * Hy);
+            gm2y[s] = -(0.5f * a.H) * opac * (conz * Hy + cony * Hx);
+            gcx[s] = -0.5f * opac * Hxx;
+            gcy[s] = -0.5f * opac * Hxy;
+            gcw[s] = -0.5f * opac * Hyy;
+            gcol[s] = {g.b.z, g.b.w, g.c.x};
+        }
     }
-    V3 gcol = {g.b.z, g.b.w, g.c.x};
-    const bool modeA = (a.avg == nullptr);
     if (modeA) {
         // Rasterizer::backward accumulates into caller arrays (atomicAdd semantics) and the
         // per-splat stage then reads the totals.
-        gm2x = (a.dL_dmean2D[3 * idx] += gm2x);
-        gm2y = (a.dL_dmean2D[3 * idx + 1] += gm2y);
-        gcx = (a.dL_dconic[4 * idx] += gcx);
-        gcy = (a.dL_dconic[4 * idx + 1] += gcy);
-        gcw = (a.dL_dconic[4 * idx + 3] += gcw);
-        gop = (a.dL_dopacity[idx] += gop);
-        gcol.x = (a.dL_dcolor[3 * idx] += gcol.x);
-        gcol.y = (a.dL_dcolor[3 * idx + 1] += gcol.y);
-        gcol.z = (a.dL_dcolor[3 * idx + 2] += gcol.z);
+        gm2x[0] = (a.dL_dmean2D[3 * idx] += gm2x[0]);
+        gm2y[0] = (a.dL_dmean2D[3 * idx + 1] += gm2y[0]);
+        gcx[0] = (a.dL_dconic[4 * idx] += gcx[0]);
+        gcy[0] = (a.dL_dconic[4 * idx + 1] += gcy[0]);
+        gcw[0] = (a.dL_dconic[4 * idx + 3] += gcw[0]);
+        gop[0] = (a.dL_dopacity[idx] += gop[0]);
+        gcol[0].x = (a.dL_dcolor[3 * idx] += gcol[0].x);
+        gcol[0].y = (a.dL_dcolor[3 * idx + 1] += gcol[0].y);
+        gcol[0].z = (a.dL_dcolor[3 * idx + 2] += gcol[0].z);
     }
 
     const float mx = a.means3D[3 * idx], my = a.means3D[3 * idx + 1], mz = a.means3D[3 * idx + 2];
@@ -136,7 +181,7 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreprocessBwd
     const float v4 = __ldg(V + 4), v5 = __ldg(V + 5), v6 = __ldg(V + 6);
     const float v8 = __ldg(V + 8), v9 = __ldg(V + 9), v10 = __ldg(V + 10);
 
-    // ---- conic -> cov2D -> cov3D and the covariance path of the mean ----
+    // ---- per-splat geometry of the covariance path (computeCov2DCUDA) ----
     float c3[6];
 #pragma unroll
     for (int k = 0; k < 6; k++) c3[k] = a.cov3D[6 * idx + k];
@@ -164,82 +209,108 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreprocessBwd
     const float cc = b0 * ub0 + b1 * ub1 + b2 * ub2 + 0.3f;
     const float denom = ca * cc - cb * cb;
     const float denom2inv = 1.0f / ((denom * denom) + 0.0000001f);
-    float dLa = 0.f, dLb = 0.f, dLc = 0.f;
+    const float itz = 1.f / tz, itz2 = itz * itz, itz3 = itz2 * itz;
+    // projection Jacobian of the screen-space mean
+    const float p0 = __ldg(Pm + 0), p1 = __ldg(Pm + 1), p3 = __ldg(Pm + 3);
+    const float p4 = __ldg(Pm + 4), p5 = __ldg(Pm + 5), p7 = __ldg(Pm + 7);
+    const float p8 = __ldg(Pm + 8), p9 = __ldg(Pm + 9), p11 = __ldg(Pm + 11);
+    const float hw = p3 * mx + p7 * my + p11 * mz + __ldg(Pm + 15);
+    const float m_w = 1.0f / (hw + 0.0000001f);
+    const float mul1 = (p0 * mx + p4 * my + p8 * mz + __ldg(Pm + 12)) * m_w * m_w;
+    const float mul2 = (p1 * mx + p5 * my + p9 * mz + __ldg(Pm + 13)) * m_w * m_w;
+
+    // ---- per set: conic -> cov2D, and the mean gradient of that pass ----
+    float dLa[NS], dLb[NS], dLc[NS];
+    V3 gmean[NS];
+#pragma unroll
+    for (int s = 0; s < NS; s++) {
+        dLa[s] = dLb[s] = dLc[s] = 0.f;
+        if (denom2inv != 0.f) {
+            dLa[s] = denom2inv * (-cc * cc * gcx[s] + 2.f * cb * cc * gcy[s] + (denom - ca * cc) * gcw[s]);
+            dLc[s] = denom2inv * (-ca * ca * gcw[s] + 2.f * ca * cb * gcy[s] + (denom - ca * cc) * gcx[s]);
+            dLb[s] = denom2inv * 2.f * (cb * cc * gcx[s] - (denom + 2.f * cb * cb) * gcy[s] + ca * cb * gcw[s]);
+        }
+        const float dT00 = 2.f * ua0 * dLa[s] + ub0 * dLb[s], dT01 = 2.f * ua1 * dLa[s] + ub1 * dLb[s], dT02 = 2.f * ua2 * dLa[s] + ub2 * dLb[s];
+        const float dT10 = 2.f * ub0 * dLc[s] + ua0 * dLb[s], dT11 = 2.f * ub1 * dLc[s] + ua1 * dLb[s], dT12 = 2.f * ub2 * dLc[s] + ua2 * dLb[s];
+        const float dJ00 = v0 * dT00 + v4 * dT01 + v8 * dT02;
+        const float dJ02 = v2 * dT00 + v6 * dT01 + v10 * dT02;
+        const float dJ11 = v1 * dT10 + v5 * dT11 + v9 * dT12;
+        const float dJ12 = v2 * dT10 + v6 * dT11 + v10 * dT12;
+        const float dtx = x_grad_mul * -hx * itz2 * dJ02;
+        const float dty = y_grad_mul * -hy * itz2 * dJ12;
+        const float dtz = -hx * itz2 * dJ00 - hy * itz2 * dJ11 + (2.f * hx * tx) * itz3 * dJ02 + (2.f * hy * ty) * itz3 * dJ12;
+        gmean[s] = {v0 * dtx + v1 * dty + v2 * dtz, v4 * dtx + v5 * dty + v6 * dtz, v8 * dtx + v9 * dty + v10 * dtz};
+        // screen-space mean gradient through the perspective divide
+        gmean[s].x += (p0 * m_w - p3 * mul1) * gm2x[s] + (p1 * m_w - p3 * mul2) * gm2y[s];
+        gmean[s].y += (p4 * m_w - p7 * mul1) * gm2x[s] + (p5 * m_w - p7 * mul2) * gm2y[s];
+        gmean[s].z += (p8 * m_w - p11 * mul1) * gm2x[s] + (p9 * m_w - p11 * mul2) * gm2y[s];
+    }
+    // sums over the sets: everything downstream except the var term only needs these
+    float sLa = dLa[0], sLb = dLb[0], sLc = dLc[0], sop = gop[0];
+#pragma unroll
+    for (int s = 1; s < NS; s++) { sLa += dLa[s]; sLb += dLb[s]; sLc += dLc[s]; sop += gop[s]; }
     float dcov[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     if (denom2inv != 0.f) {
-        dLa = denom2inv * (-cc * cc * gcx + 2.f * cb * cc * gcy + (denom - ca * cc) * gcw);
-        dLc = denom2inv * (-ca * ca * gcw + 2.f * ca * cb * gcy + (denom - ca * cc) * gcx);
-        dLb = denom2inv * 2.f * (cb * cc * gcx - (denom + 2.f * cb * cb) * gcy + ca * cb * gcw);
-        dcov[0] = a0 * a0 * dLa + a0 * b0 * dLb + b0 * b0 * dLc;
-        dcov[3] = a1 * a1 * dLa + a1 * b1 * dLb + b1 * b1 * dLc;
-        dcov[5] = a2 * a2 * dLa + a2 * b2 * dLb + b2 * b2 * dLc;
-        dcov[1] = 2.f * a0 * a1 * dLa + (a0 * b1 + a1 * b0) * dLb + 2.f * b0 * b1 * dLc;
-        dcov[2] = 2.f * a0 * a2 * dLa + (a0 * b2 + a2 * b0) * dLb + 2.f * b0 * b2 * dLc;
-        dcov[4] = 2.f * a2 * a1 * dLa + (a1 * b2 + a2 * b1) * dLb + 2.f * b1 * b2 * dLc;
-    }
-    const float dT00 = 2.f * ua0 * dLa + ub0 * dLb, dT01 = 2.f * ua1 * dLa + ub1 * dLb, dT02 = 2.f * ua2 * dLa + ub2 * dLb;
-    const float dT10 = 2.f * ub0 * dLc + ua0 * dLb, dT11 = 2.f * ub1 * dLc + ua1 * dLb, dT12 = 2.f * ub2 * dLc + ua2 * dLb;
-    const float dJ00 = v0 * dT00 + v4 * dT01 + v8 * dT02;
-    const float dJ02 = v2 * dT00 + v6 * dT01 + v10 * dT02;
-    const float dJ11 = v1 * dT10 + v5 * dT11 + v9 * dT12;
-    const float dJ12 = v2 * dT10 + v6 * dT11 + v10 * dT12;
-    const float itz = 1.f / tz, itz2 = itz * itz, itz3 = itz2 * itz;
-    const float dtx = x_grad_mul * -hx * itz2 * dJ02;
-    const float dty = y_grad_mul * -hy * itz2 * dJ12;
-    const float dtz = -hx * itz2 * dJ00 - hy * itz2 * dJ11 + (2.f * hx * tx) * itz3 * dJ02 + (2.f * hy * ty) * itz3 * dJ12;
-    V3 gmean = {v0 * dtx + v1 * dty + v2 * dtz, v4 * dtx + v5 * dty + v6 * dtz, v8 * dtx + v9 * dty + v10 * dtz};
-
-    // ---- screen-space mean gradient through the perspective divide ----
-    {
-        const float p0 = __ldg(Pm + 0), p1 = __ldg(Pm + 1), p3 = __ldg(Pm + 3);
-        const float p4 = __ldg(Pm + 4), p5 = __ldg(Pm + 5), p7 = __ldg(Pm + 7);
-        const float p8 = __ldg(Pm + 8), p9 = __ldg(Pm + 9), p11 = __ldg(Pm + 11);
-        const float hw = p3 * mx + p7 * my + p11 * mz + __ldg(Pm + 15);
-        const float m_w = 1.0f / (hw + 0.0000001f);
-        const float mul1 = (p0 * mx + p4 * my + p8 * mz + __ldg(Pm + 12)) * m_w * m_w;
-        const float mul2 = (p1 * mx + p5 * my + p9 * mz + __ldg(Pm + 13)) * m_w * m_w;
-        gmean.x += (p0 * m_w - p3 * mul1) * gm2x + (p1 * m_w - p3 * mul2) * gm2y;
-        gmean.y += (p4 * m_w - p7 * mul1) * gm2x + (p5 * m_w - p7 * mul2) * gm2y;
-        gmean.z += (p8 * m_w - p11 * mul1) * gm2x + (p9 * m_w - p11 * mul2) * gm2y;
+        dcov[0] = a0 * a0 * sLa + a0 * b0 * sLb + b0 * b0 * sLc;
+        dcov[3] = a1 * a1 * sLa + a1 * b1 * sLb + b1 * b1 * sLc;
+        dcov[5] = a2 * a2 * sLa + a2 * b2 * sLb + b2 * b2 * sLc;
+        dcov[1] = 2.f * a0 * a1 * sLa + (a0 * b1 + a1 * b0) * sLb + 2.f * b0 * b1 * sLc;
+        dcov[2] = 2.f * a0 * a2 * sLa + (a0 * b2 + a2 * b0) * sLb + 2.f * b0 * b2 * sLc;
+        dcov[4] = 2.f * a2 * a1 * sLa + (a1 * b2 + a2 * b1) * sLb + 2.f * b1 * b2 * sLc;
     }
 
     const float S = a.samples;
-    const size_t P = (size_t)a.P;
-    const int M = a.M;
-    float* avg_loc = modeA ? nullptr : a.avg + P;
-    float* avg_sh = modeA ? nullptr : a.avg + 4 * P;
-    float* avg_scale = modeA ? nullptr : a.avg + 4 * P + 3 * (size_t)M * P;
-    float* avg_op = modeA ? nullptr : avg_scale + 3 * P;
-    float* avg_rot = modeA ? nullptr : avg_op + P;
+    const float invS = 1.0f / S;
 
     // ---- SH backward ----
     if (!a.colors_precomp) {
         const uint8_t cl = a.clamped[idx];
-        const V3 dRGB = {(cl & 1) ? 0.f : gcol.x, (cl & 2) ? 0.f : gcol.y, (cl & 4) ? 0.f : gcol.z};
+        V3 dRGB[NS];
+#pragma unroll
+        for (int s = 0; s < NS; s++)
+            dRGB[s] = {(cl & 1) ? 0.f : gcol[s].x, (cl & 2) ? 0.f : gcol[s].y, (cl & 4) ? 0.f : gcol[s].z};
+        V3 dsum = dRGB[0];
+#pragma unroll
+        for (int s = 1; s < NS; s++) dsum = dsum + dRGB[s];
         const float* sh = a.shs + (size_t)idx * M * 3;
-        V3 gdir;
+        ShDirs dirs;
         if (modeA) {
             float* out = a.dL_dsh + (size_t)idx * M * 3;
-            gdir = sh_backward(a.D, mx, my, mz, a.cam_pos, sh, dRGB, [&](int c, V3 v) {
+            dirs = sh_backward(a.D, mx, my, mz, a.cam_pos, sh, dsum, [&](int c, V3 v) {
                 out[3 * c] = v.x; out[3 * c + 1] = v.y; out[3 * c + 2] = v.z;
             });
+        } else if (M4) {
+            dirs = sh_backward(1, mx, my, mz, a.cam_pos, sh, dsum, [&](int c, V3 v) {
+                o_sh[3 * c] += v.x / S; o_sh[3 * c + 1] += v.y / S; o_sh[3 * c + 2] += v.z / S;
+            });
+            float4* p = reinterpret_cast<float4*>(avg_sh + 12 * (size_t)idx);
+#pragma unroll
+            for (int k = 0; k < 3; k++) p[k] = make_float4(o_sh[4 * k], o_sh[4 * k + 1], o_sh[4 * k + 2], o_sh[4 * k + 3]);
         } else {
             float* out = avg_sh + (size_t)idx * M * 3;
-            gdir = sh_backward(a.D, mx, my, mz, a.cam_pos, sh, dRGB, [&](int c, V3 v) {
+            dirs = sh_backward(a.D, mx, my, mz, a.cam_pos, sh, dsum, [&](int c, V3 v) {
                 out[3 * c] += v.x / S; out[3 * c + 1] += v.y / S; out[3 * c + 2] += v.z / S;
             });
         }
-        gmean = gmean + gdir;
+#pragma unroll
+        for (int s = 0; s < NS; s++) gmean[s] = gmean[s] + dir_grad(dirs, dRGB[s]);
     }
 
     if (modeA) {
-        a.dL_dmean3D[3 * idx] = gmean.x; a.dL_dmean3D[3 * idx + 1] = gmean.y; a.dL_dmean3D[3 * idx + 2] = gmean.z;
+        a.dL_dmean3D[3 * idx] = gmean[0].x; a.dL_dmean3D[3 * idx + 1] = gmean[0].y; a.dL_dmean3D[3 * idx + 2] = gmean[0].z;
 #pragma unroll
         for (int k = 0; k < 6; k++) a.dL_dcov3D[6 * idx + k] = dcov[k];
     } else {
-        a.avg[idx] += sqrtf(gmean.x * gmean.x + gmean.y * gmean.y + gmean.z * gmean.z) / S;
-        avg_loc[3 * idx] += gmean.x / S; avg_loc[3 * idx + 1] += gmean.y / S; avg_loc[3 * idx + 2] += gmean.z / S;
-        avg_op[idx] += gop / S;
+        float var = 0.f;
+        V3 gs_ = {0.f, 0.f, 0.f};
+#pragma unroll
+        for (int s = 0; s < NS; s++) {
+            var += sqrtf(gmean[s].x * gmean[s].x + gmean[s].y * gmean[s].y + gmean[s].z * gmean[s].z) / S;
+            gs_.x += gmean[s].x / S; gs_.y += gmean[s].y / S; gs_.z += gmean[s].z / S;
+        }
+        a.avg[idx] = o_var + var;
+        avg_loc[3 * idx] = o_loc[0] + gs_.x; avg_loc[3 * idx + 1] = o_loc[1] + gs_.y; avg_loc[3 * idx + 2] = o_loc[2] + gs_.z;
+        avg_op[idx] = o_op + sop * invS;
     }
 
     // ---- cov3D -> scale, rotation ----
@@ -280,9 +351,9 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreprocessBwd
             for (int c = 0; c < 4; c++) a.dL_drot[4 * idx + c] = gq[c];
         } else {
 #pragma unroll
-            for (int c = 0; c < 3; c++) avg_scale[3 * idx + c] += gs[c] / S;
+            for (int c = 0; c < 3; c++) avg_scale[3 * idx + c] = o_scale[c] + gs[c] / S;
 #pragma unroll
-            for (int c = 0; c < 4; c++) avg_rot[4 * idx + c] += gq[c] / S;
+            for (int c = 0; c < 4; c++) avg_rot[4 * idx + c] = o_rot[c] + gq[c] / S;
         }
     }
 }
@@ -291,5 +362,17 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreprocessBwd
 
 void launch_preprocess_bwd(const PreprocessBwdArgs& a, cudaStream_t s) {
     if (a.P <= 0) return;
-    preprocess_bwd_kernel<<<gsb_div_up(a.P, 256), 256, 0, s>>>(a);
+    const int grid = gsb_div_up(a.P, 256);
+    const bool trainer = a.avg != nullptr;
+    // the fast shape needs 16-byte aligned 12-float SH records in the running-mean buffer
+    const bool m4 = trainer && a.M == 4 && a.D == 1 && !a.colors_precomp &&
+                    (reinterpret_cast<uintptr_t>(a.avg) % 16 == 0);
+    if (trainer && a.grads2 != nullptr) {
+        if (m4) preprocess_bwd_kernel<2, true><<<grid, 256, 0, s>>>(a);
+        else preprocess_bwd_kernel<2, false><<<grid, 256, 0, s>>>(a);
+    } else if (m4) {
+        preprocess_bwd_kernel<1, true><<<grid, 256, 0, s>>>(a);
+    } else {
+        preprocess_bwd_kernel<1, false><<<grid, 256, 0, s>>>(a);
+    }
 }

@@ -15,11 +15,12 @@
 // preprocess backward (preprocess_bwd.cu) instead of once per pair here.
 //
 // For every surviving list entry the nine partial sums are added over the lane's two pixels in
-// registers, reduced across the warp with a reduce-scatter butterfly (14 shuffles for 9 values
-// instead of 45; skipped when no lane blended the entry) and the nine lanes that end up holding a
-// total issue one red.global.add each into the packed GradRec scratch (two RED instructions per
-// warp and entry).  On the measured scenes 1.2 warps blend a given (tile, splat) duplicate, so a
-// further cross-warp stage would save almost nothing.
+// registers and reduced across the warp (skipped when no lane blended the entry) by a transposed
+// pass through a per-warp shared-memory panel; the lanes that end up holding a total issue one
+// red.global.add each into the packed GradRec scratch (one RED instruction per warp and entry).
+// On the measured scenes 1.2 warps blend a given (tile, splat) duplicate, so a further cross-warp
+// stage would save almost nothing.  (Round-1 ncu: the earlier shuffle butterfly was 48 % of the
+// kernel's warp instructions, profiles/r01_render_bwd_source.txt.)
 //
 // DUAL mode serves Trainer::train's white and black pass of one camera (src/Trainer.cu:311-314) in
 // a single walk: both passes blend the same splats with the same alpha and T (the background only
@@ -31,44 +32,12 @@
 
 namespace {
 
+constexpr int RED_STRIDE = 36;   // floats per row of the reduction panel: 32 lanes + 4 pad (rows stay 16-byte aligned)
+
 struct BwdSmem {
     SplatRec rec[2][RB];
     uint32_t id[2][RB];
 };
-
-// Warp sum of 9 values: lanes 4q..4q+3 end up with the total of v[q] (q < 8), every lane with v[8].
-__device__ __forceinline__ void warp_reduce9(const float (&v)[9], int lane, float& s1, float& s8) {
-    float u[4], t2[2];
-    {
-        const bool hi = lane & 16;
-#pragma unroll
-        for (int q = 0; q < 4; q++) {
-            const float send = hi ? v[q] : v[q + 4];
-            const float keep = hi ? v[q + 4] : v[q];
-            u[q] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
-        }
-    }
-    {
-        const bool hi = lane & 8;
-#pragma unroll
-        for (int q = 0; q < 2; q++) {
-            const float send = hi ? u[q] : u[q + 2];
-            const float keep = hi ? u[q + 2] : u[q];
-            t2[q] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
-        }
-    }
-    {
-        const bool hi = lane & 4;
-        const float send = hi ? t2[0] : t2[1];
-        const float keep = hi ? t2[1] : t2[0];
-        s1 = keep + __shfl_xor_sync(0xffffffffu, send, 4);
-    }
-    s1 += __shfl_xor_sync(0xffffffffu, s1, 2);
-    s1 += __shfl_xor_sync(0xffffffffu, s1, 1);
-    s8 = v[8];
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) s8 += __shfl_xor_sync(0xffffffffu, s8, o);
-}
 
 // MODE 0: dL/dpixel given (Rasterizer::backward).  MODE 1: residual of one truth frame fused.
 // MODE 2: white and black truth frames of one camera fused (two residuals, two GradRec sets).
@@ -76,8 +45,10 @@ template <int MODE>
 __global__ void __launch_bounds__(RENDER_THREADS, MODE == 2 ? 5 : 6) render_bwd_kernel(const RenderBwdArgs a) {
     constexpr int NS = (MODE == 2) ? 2 : 1;   // residual sets
     __shared__ BwdSmem sm;
+    __shared__ __align__(16) float s_red[RENDER_WARPS][9 * NS * RED_STRIDE];
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    float* const red = s_red[warp];
     const int tile = blockIdx.y * a.grid_x + blockIdx.x;
     const int start = (int)a.tile_max[tile];       // entries at or beyond this index were blended by no pixel
     if (start == 0 && (MODE == 0 || a.loss_out == nullptr)) return;
@@ -258,15 +229,28 @@ __global__ void __launch_bounds__(RENDER_THREADS, MODE == 2 ? 5 : 6) render_bwd_
                     }
                 }
                 if (!__any_sync(0xffffffffu, hit)) continue;
-                // lane 4q holds sum q (q = 4*b16 + 2*b8 + b4): GradRec floats 0..7; float 8 from lane 1
+                // Transposed reduction through shared memory: every lane parks its 9*NS partial sums in
+                // column `lane` of the warp's [9*NS][RED_STRIDE] panel (conflict-free: bank = 4*row + lane),
+                // then lane r adds up row r with eight 128-bit loads and issues the one RED for GradRec
+                // float r.  ~60 warp instructions per (warp, entry) against ~95 for two shuffle butterflies.
 #pragma unroll
-                for (int s = 0; s < NS; s++) {
-                    float s1, s8;
-                    warp_reduce9(v[s], lane, s1, s8);
-                    float* g = reinterpret_cast<float*>((s == 0 ? a.grads : a.grads2) + ids[j]);
-                    if ((lane & 3) == 0) atomicAdd(g + (lane >> 2), s1);
-                    if (lane == 1) atomicAdd(g + 8, s8);
+                for (int s = 0; s < NS; s++)
+#pragma unroll
+                    for (int q = 0; q < 9; q++) red[(s * 9 + q) * RED_STRIDE + lane] = v[s][q];
+                __syncwarp();
+                if (lane < 9 * NS) {
+                    const float4* row = reinterpret_cast<const float4*>(red + lane * RED_STRIDE);
+                    float4 acc = row[0];
+#pragma unroll
+                    for (int c = 1; c < 8; c++) {
+                        const float4 t = row[c];
+                        acc.x += t.x; acc.y += t.y; acc.z += t.z; acc.w += t.w;
+                    }
+                    const float sum = (acc.x + acc.y) + (acc.z + acc.w);
+                    GradRec* g = ((NS == 1 || lane < 9) ? a.grads : a.grads2) + ids[j];
+                    atomicAdd(reinterpret_cast<float*>(g) + ((NS == 1 || lane < 9) ? lane : lane - 9), sum);
                 }
+                __syncwarp();
             }
         }
     }

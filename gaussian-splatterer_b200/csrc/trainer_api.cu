@@ -211,13 +211,9 @@ int backward_pass(gsb_trainer* t, int i, bool fused, int fin, float* avg, float 
     pb.focal_x = t->W / (2.0f * pb.tan_fovx);
     pb.radii = t->g.radii; pb.clamped = t->g.clamped; pb.grads = t->g.grads; pb.recs = t->g.recs; pb.W = t->W; pb.H = t->H;
     pb.avg = avg; pb.samples = S;
+    pb.grads2 = fused ? t->grads2 : nullptr;   // both passes of the camera in one sweep over the splats
     launch_preprocess_bwd(pb, s);
     t->stats.kernel_launches += 2;
-    if (fused) {
-        pb.grads = t->grads2;      // the black pass: its own var term, same running means
-        launch_preprocess_bwd(pb, s);
-        t->stats.kernel_launches++;
-    }
     mark(ev, ST_COUNT, s);
     return GSB_OK;
 }
