@@ -181,11 +181,12 @@ __global__ void __launch_bounds__(RENDER_THREADS, MODE == 2 ? 5 : 6) render_bwd_
                 const float dx = __fsub_rn(ra.x, pxf);
                 const float bx = __fmul_rn(dx, ra.z);
                 const float cxy = __fmul_rn(dx, ra.w);
-                float v[NS][9];
+                // per lane and set: A = sum h, B = sum h dy, C = sum h dy^2 over the lane's two pixels (they
+                // share dx, so the dx factors of the six moments are applied once after the pixel loop) and
+                // the three colour sums
+                float mA[NS], mB[NS], mC[NS], vr[NS], vg[NS], vb[NS];
 #pragma unroll
-                for (int s = 0; s < NS; s++)
-#pragma unroll
-                    for (int q = 0; q < 9; q++) v[s][q] = 0.f;
+                for (int s = 0; s < NS; s++) mA[s] = mB[s] = mC[s] = vr[s] = vg[s] = vb[s] = 0.f;
                 bool hit = false;
 #pragma unroll
                 for (int k = 0; k < 2; k++) {
@@ -212,20 +213,17 @@ __global__ void __launch_bounds__(RENDER_THREADS, MODE == 2 ? 5 : 6) render_bwd_
                     const float GT = G * T[k];
 #pragma unroll
                     for (int s = 0; s < NS; s++) {
-                        v[s][6] = fmaf(w, dLr[s][k], v[s][6]);
-                        v[s][7] = fmaf(w, dLg[s][k], v[s][7]);
-                        v[s][8] = fmaf(w, dLb[s][k], v[s][8]);
+                        vr[s] = fmaf(w, dLr[s][k], vr[s]);
+                        vg[s] = fmaf(w, dLg[s][k], vg[s]);
+                        vb[s] = fmaf(w, dLb[s][k], vb[s]);
                         // h = G * dL/dalpha; the background term (alpha also scales how much of bg shows
                         // through) exists for a non-black background only
                         float h = GT * (er * dLr[s][k] + eg * dLg[s][k] + eb * dLb[s][k]);
                         if (s == 0) h = fmaf(-(G * Tfin[k] * inv), bgdot[k], h);
-                        const float hx = h * dx, hy = h * dy;
-                        v[s][0] += h;
-                        v[s][1] += hx;
-                        v[s][2] += hy;
-                        v[s][3] = fmaf(hx, dx, v[s][3]);
-                        v[s][4] = fmaf(hx, dy, v[s][4]);
-                        v[s][5] = fmaf(hy, dy, v[s][5]);
+                        const float hy = h * dy;
+                        mA[s] += h;
+                        mB[s] += hy;
+                        mC[s] = fmaf(hy, dy, mC[s]);
                     }
                 }
                 if (!__any_sync(0xffffffffu, hit)) continue;
@@ -234,9 +232,19 @@ __global__ void __launch_bounds__(RENDER_THREADS, MODE == 2 ? 5 : 6) render_bwd_
                 // then lane r adds up row r with eight 128-bit loads and issues the one RED for GradRec
                 // float r.  ~60 warp instructions per (warp, entry) against ~95 for two shuffle butterflies.
 #pragma unroll
-                for (int s = 0; s < NS; s++)
-#pragma unroll
-                    for (int q = 0; q < 9; q++) red[(s * 9 + q) * RED_STRIDE + lane] = v[s][q];
+                for (int s = 0; s < NS; s++) {
+                    float* col = red + s * 9 * RED_STRIDE + lane;
+                    const float ax = mA[s] * dx;
+                    col[0 * RED_STRIDE] = mA[s];          // H0
+                    col[1 * RED_STRIDE] = ax;             // Hx
+                    col[2 * RED_STRIDE] = mB[s];          // Hy
+                    col[3 * RED_STRIDE] = ax * dx;        // Hxx
+                    col[4 * RED_STRIDE] = mB[s] * dx;     // Hxy
+                    col[5 * RED_STRIDE] = mC[s];          // Hyy
+                    col[6 * RED_STRIDE] = vr[s];
+                    col[7 * RED_STRIDE] = vg[s];
+                    col[8 * RED_STRIDE] = vb[s];
+                }
                 __syncwarp();
                 if (lane < 9 * NS) {
                     const float4* row = reinterpret_cast<const float4*>(red + lane * RED_STRIDE);
