@@ -17,7 +17,7 @@ e2e     the same through Trainer.train with the truth frames in pinned HOST memo
         loss scalar back.
 roofline  dominant kernel = render backward: achieved FP32 FLOP/s from the reference's per-pair
         FLOP counts and the kernel's mean launch time measured live with CUDA events
-        inside the timed region.  No stage of this path is a dense contraction or HBM-bound at the
+        around every stage of every view pass in a second loop over the same K steps.  No stage of this path is a dense contraction or HBM-bound at the
         top, so the bound is the FP32 SIMT issue rate; the whole-step HBM figure is reported beside it.
 cpu_baseline  the scalar C++ oracle (oracle/liboracle.so, one host thread) on ONE view pass of the
         same workload -- context only; the graded baseline is `--impl reference`: the reference has
@@ -279,17 +279,23 @@ def run_gsb(args):
     for _ in range(args.warmup):
         tr.train(project, False)
     launches0 = tr.stats()["kernel_launches"]
-    tr.set_stage_timing(True)
     sampler = ClockSampler(gpu_identifier(torch, local))
     if rank == 0:
         sampler.start()
     ms = timed_steps(torch, dist, lambda k: tr.train(project, False), args.steps)
     clocks = sampler.stop() if rank == 0 else None
-    stage_ms, passes = tr.stage_times()
-    tr.set_stage_timing(False)
     stats = tr.stats()
     launches = stats["kernel_launches"] - launches0
     value = views_per_step * args.steps / (ms / 1000.0)
+
+    # ---- per-kernel launch times, live: the same K steps again with every stage of every view pass
+    # bracketed by CUDA events on the launching stream.  Stage timing serialises the kernels (in the
+    # loop above the next pass's forward chain overlaps the current backward), so a stage's time is
+    # its own and `ms_serial` is the un-overlapped step.
+    tr.set_stage_timing(True)
+    ms_serial = timed_steps(torch, dist, lambda k: tr.train(project, False), args.steps)
+    stage_ms, passes = tr.stage_times()
+    tr.set_stage_timing(False)
 
     # ---- counters for the roofline (after the timed region) ----------------------------------
     pcs = [tr.count_pairs(i) for i in range(n_local)]
@@ -400,7 +406,8 @@ def run_gsb(args):
                      "step_hbm": {"bound": "hbm", "achieved": step_gbs, "peak": hbm_peak, "unit": "GB/s",
                                   "frac": step_gbs / hbm_peak, "bytes_per_step_per_rank": step_bytes, "peak_source": hbm_src}},
         "stages": stages,
-        "stats": {"rendered_per_step": stats["rendered_total"], "retries": stats["retries"]},
+        "stats": {"rendered_per_step": stats["rendered_total"], "retries": stats["retries"],
+                  "ms_per_step_serialised_with_stage_events": ms_serial / args.steps},
     }
     if e2e is not None:
         out["e2e"] = e2e

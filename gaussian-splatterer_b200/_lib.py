@@ -104,6 +104,8 @@ def lib():
     L.gsb_trainer_set_fuse_backgrounds.restype = i
     L.gsb_trainer_profile_pass.argtypes = [vp, i, C.POINTER(C.c_float), C.POINTER(C.c_uint)]
     L.gsb_trainer_profile_pass.restype = i
+    L.gsb_trainer_set_overlap.argtypes = [vp, i]
+    L.gsb_trainer_set_overlap.restype = i
     L.gsb_trainer_set_stage_timing.argtypes = [vp, i]
     L.gsb_trainer_set_stage_timing.restype = i
     L.gsb_trainer_get_stage_times.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(C.c_longlong)]
@@ -123,7 +125,7 @@ EXPORTED_SYMBOLS = [
     "gsb_last_error", "gsb_version", "gsb_rasterizer_forward", "gsb_rasterizer_backward",
     "gsb_rasterizer_mark_visible", "gsb_rasterizer_state", "gsb_rasterizer_sorted_keys",
     "gsb_trainer_enable_loss", "gsb_trainer_set_fuse_backgrounds", "gsb_trainer_profile_pass",
-    "gsb_trainer_set_stage_timing", "gsb_trainer_get_stage_times", "gsb_trainer_count_pairs",
+    "gsb_trainer_set_stage_timing", "gsb_trainer_get_stage_times", "gsb_trainer_count_pairs", "gsb_trainer_set_overlap",
     "gsb_image_float_to_int", "gsb_image_int_to_loss",
     "gsb_trainer_create", "gsb_trainer_destroy", "gsb_trainer_bind_model", "gsb_trainer_set_truths",
     "gsb_trainer_set_grad_buffer", "gsb_trainer_grad_floats", "gsb_trainer_grad_buffer",

@@ -45,6 +45,21 @@ struct gsb_trainer {
     char* bin = nullptr; uint32_t r_cap = 0; BinWs b;
     char* img = nullptr; ImageWs im;
     float* rendered = nullptr;        // [3][H][W]
+    // The members above are the ACTIVE view workspace.  Two complete sets exist (slot[0], slot[1]) so the
+    // forward chain of view pass i+1 (latency-bound, small grids) can run on a second stream underneath
+    // the render backward of view pass i (issue-bound); activate() swaps a set into the members before
+    // a pass is enqueued (kernel arguments are captured at launch).
+    struct ViewSlot {
+        char* geom = nullptr; GeomWs g; GradRec* grads2 = nullptr;
+        char* bin = nullptr; BinWs b;
+        char* img = nullptr; ImageWs im;
+        float* rendered = nullptr;
+    } slot[2];
+    int active = 0;
+    bool overlap = true;              // gsb_trainer_set_overlap
+    cudaStream_t sF = nullptr, sB = nullptr;          // non-blocking: forward chain / backward chain
+    cudaStream_t exec_f = nullptr, exec_b = nullptr;  // null = everything on `stream`
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_fdone[2] = {nullptr, nullptr}, ev_bdone[2] = {nullptr, nullptr};
     // preview arena (Trainer::render at another resolution)
     char* pimg = nullptr; size_t pimg_bytes = 0; float* pcolor = nullptr; size_t pcolor_floats = 0;
 
@@ -74,32 +89,60 @@ struct gsb_trainer {
 
 namespace {
 
+void save_slot(gsb_trainer* t) {
+    gsb_trainer::ViewSlot& v = t->slot[t->active];
+    v.geom = t->geom; v.g = t->g; v.grads2 = t->grads2; v.bin = t->bin; v.b = t->b; v.img = t->img; v.im = t->im;
+    v.rendered = t->rendered;
+}
+void activate(gsb_trainer* t, int k) {
+    if (k == t->active) return;
+    save_slot(t);
+    const gsb_trainer::ViewSlot& v = t->slot[k];
+    t->geom = v.geom; t->g = v.g; t->grads2 = v.grads2; t->bin = v.bin; t->b = v.b; t->img = v.img; t->im = v.im;
+    t->rendered = v.rendered;
+    t->active = k;
+}
+
 float* avg_ptr(gsb_trainer* t) { return t->avg_ext ? t->avg_ext : t->avg_own; }
 size_t grad_floats(const gsb_trainer* t) { return (size_t)t->count * (12 + 3 * (size_t)t->M); }
 
 int ensure_geom(gsb_trainer* t, size_t P) {
-    if (t->geom && P <= t->geom_P) { t->g.carve(t->geom, t->geom_P); return GSB_OK; }
-    if (t->geom) GSB_CUDA_OK(cudaFree(t->geom));
+    if (t->slot[0].geom && t->slot[1].geom && t->geom && P <= t->geom_P) return GSB_OK;
+    GSB_CUDA_OK(cudaStreamSynchronize(t->stream));
     const size_t cap = P + P / 8 + 1024;
     const size_t bytes = GeomWs::required(cap);
-    GSB_CUDA_OK(cudaMalloc(&t->geom, bytes));
-    GSB_CUDA_OK(cudaMemsetAsync(t->geom, 0, bytes, t->stream));   // look-back words and grad scratch start at zero
+    const int was = t->active;
+    for (int k = 0; k < 2; k++) {
+        activate(t, k);
+        if (t->geom) GSB_CUDA_OK(cudaFree(t->geom));
+        GSB_CUDA_OK(cudaMalloc(&t->geom, bytes));
+        GSB_CUDA_OK(cudaMemsetAsync(t->geom, 0, bytes, t->stream));   // look-back words and grad scratch start at zero
+        t->g.carve(t->geom, cap);
+        if (t->grads2) GSB_CUDA_OK(cudaFree(t->grads2));
+        GSB_CUDA_OK(cudaMalloc(&t->grads2, cap * sizeof(GradRec)));
+        GSB_CUDA_OK(cudaMemsetAsync(t->grads2, 0, cap * sizeof(GradRec), t->stream));
+        save_slot(t);
+    }
     t->geom_P = cap;
-    t->g.carve(t->geom, cap);
-    if (t->grads2) GSB_CUDA_OK(cudaFree(t->grads2));
-    GSB_CUDA_OK(cudaMalloc(&t->grads2, cap * sizeof(GradRec)));
-    GSB_CUDA_OK(cudaMemsetAsync(t->grads2, 0, cap * sizeof(GradRec), t->stream));
+    activate(t, was);
     return GSB_OK;
 }
 
 int ensure_bin(gsb_trainer* t, uint32_t r_cap) {
     if (t->bin && r_cap <= t->r_cap) return GSB_OK;
-    if (t->bin) GSB_CUDA_OK(cudaFree(t->bin));
+    GSB_CUDA_OK(cudaStreamSynchronize(t->stream));
     const size_t bytes = BinWs::required(r_cap);
-    GSB_CUDA_OK(cudaMalloc(&t->bin, bytes));
-    GSB_CUDA_OK(cudaMemsetAsync(t->bin, 0, bytes, t->stream));
+    const int was = t->active;
+    for (int k = 0; k < 2; k++) {
+        activate(t, k);
+        if (t->bin) GSB_CUDA_OK(cudaFree(t->bin));
+        GSB_CUDA_OK(cudaMalloc(&t->bin, bytes));
+        GSB_CUDA_OK(cudaMemsetAsync(t->bin, 0, bytes, t->stream));
+        t->b.carve(t->bin, r_cap);
+        save_slot(t);
+    }
     t->r_cap = r_cap;
-    t->b.carve(t->bin, r_cap);
+    activate(t, was);
     return GSB_OK;
 }
 
@@ -124,7 +167,7 @@ inline void mark(cudaEvent_t* ev, int k, cudaStream_t s) {
 int forward_pass(gsb_trainer* t, const float* view, const float* projview, const float* campos, float tanx, float tany,
                  float scale_modifier, const float* bg, int W, int H, ImageWs& im, float* out_color, uint32_t* h_R,
                  cudaEvent_t* ev = nullptr) {
-    cudaStream_t s = t->stream;
+    cudaStream_t s = t->exec_f ? t->exec_f : t->stream;
     const int grid_x = (W + GSB_TILE - 1) / GSB_TILE, grid_y = (H + GSB_TILE - 1) / GSB_TILE;
     const int tiles = grid_x * grid_y;
     const int P = t->count;
@@ -182,7 +225,7 @@ int forward_pass(gsb_trainer* t, const float* view, const float* projview, const
 // loss + backward + accumulate.  Unfused: training view pass i of 2n (white passes first, then black,
 // T:311-314).  Fused: camera i of n, both backgrounds in one walk (the forward ran on black).
 int backward_pass(gsb_trainer* t, int i, bool fused, int fin, float* avg, float S, cudaEvent_t* ev = nullptr) {
-    cudaStream_t s = t->stream;
+    cudaStream_t s = t->exec_b ? t->exec_b : t->stream;
     const int n = (int)t->truthW.size();
     const bool white = fused || i < n;
     const int cam = i % n;
@@ -226,7 +269,14 @@ int view_pass(gsb_trainer* t, int i, bool fused, float* avg, float S, cudaEvent_
     const int r = forward_pass(t, dc->view, dc->projview, dc->location, t->cams[cam].tan_fovx, t->cams[cam].tan_fovy, 1.0f, bg,
                                t->W, t->H, t->im, t->rendered, t->h_R + i, ev);
     if (r < 100) return r;
-    return backward_pass(t, i, fused, r - 100, avg, S, ev);
+    if (t->exec_f) {   // pipelined: the backward chain of this pass waits for its forward chain
+        GSB_CUDA_OK(cudaEventRecord(t->ev_fdone[t->active], t->exec_f));
+        GSB_CUDA_OK(cudaStreamWaitEvent(t->exec_b, t->ev_fdone[t->active], 0));
+    }
+    const int e = backward_pass(t, i, fused, r - 100, avg, S, ev);
+    if (e) return e;
+    if (t->exec_b) GSB_CUDA_OK(cudaEventRecord(t->ev_bdone[t->active], t->exec_b));
+    return GSB_OK;
 }
 
 }  // namespace
@@ -249,9 +299,26 @@ int gsb_trainer_create(gsb_trainer** out, int width, int height, void* stream) {
     GSB_CUDA_OK(cudaMalloc(&t->d_bg, sizeof(bg)));
     GSB_CUDA_OK(cudaMemcpy(t->d_bg, bg, sizeof(bg), cudaMemcpyHostToDevice));
     const size_t N = (size_t)width * height;
-    GSB_CUDA_OK(cudaMalloc(&t->img, ImageWs::required(N, (size_t)t->tiles)));
-    t->im.carve(t->img, N, (size_t)t->tiles);
-    GSB_CUDA_OK(cudaMalloc(&t->rendered, 3 * N * sizeof(float)));
+    for (int k = 0; k < 2; k++) {
+        activate(t, k);
+        GSB_CUDA_OK(cudaMalloc(&t->img, ImageWs::required(N, (size_t)t->tiles)));
+        t->im.carve(t->img, N, (size_t)t->tiles);
+        GSB_CUDA_OK(cudaMalloc(&t->rendered, 3 * N * sizeof(float)));
+        save_slot(t);
+    }
+    activate(t, 0);
+    // The forward chain is a string of small, latency-bound grids: at high priority its CTAs take whatever
+    // an SM frees while the (low-priority, register-heavy) backward kernel drains.
+    int prio_lo = 0, prio_hi = 0;
+    GSB_CUDA_OK(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+    GSB_CUDA_OK(cudaStreamCreateWithPriority(&t->sF, cudaStreamNonBlocking, prio_hi));
+    GSB_CUDA_OK(cudaStreamCreateWithPriority(&t->sB, cudaStreamNonBlocking, prio_lo));
+    GSB_CUDA_OK(cudaEventCreateWithFlags(&t->ev_fork, cudaEventDisableTiming));
+    GSB_CUDA_OK(cudaEventCreateWithFlags(&t->ev_join, cudaEventDisableTiming));
+    for (int k = 0; k < 2; k++) {
+        GSB_CUDA_OK(cudaEventCreateWithFlags(&t->ev_fdone[k], cudaEventDisableTiming));
+        GSB_CUDA_OK(cudaEventCreateWithFlags(&t->ev_bdone[k], cudaEventDisableTiming));
+    }
     GSB_CUDA_OK(cudaMalloc(&t->d_loss, sizeof(double)));
     GSB_CUDA_OK(cudaMemset(t->d_loss, 0, sizeof(double)));
     GSB_CUDA_OK(cudaMalloc(&t->totals, 4 * sizeof(uint32_t)));
@@ -264,7 +331,18 @@ int gsb_trainer_create(gsb_trainer** out, int width, int height, void* stream) {
 int gsb_trainer_destroy(gsb_trainer* t) {
     if (!t) return GSB_OK;
     cudaStreamSynchronize(t->stream);
-    cudaFree(t->d_cams); cudaFree(t->d_pcam); cudaFree(t->d_bg); cudaFree(t->geom); cudaFree(t->grads2); cudaFree(t->bin); cudaFree(t->img); cudaFree(t->rendered);
+    if (t->sF) { cudaStreamSynchronize(t->sF); cudaStreamDestroy(t->sF); }
+    if (t->sB) { cudaStreamSynchronize(t->sB); cudaStreamDestroy(t->sB); }
+    save_slot(t);
+    for (int k = 0; k < 2; k++) {
+        cudaFree(t->slot[k].geom); cudaFree(t->slot[k].grads2); cudaFree(t->slot[k].bin); cudaFree(t->slot[k].img);
+        cudaFree(t->slot[k].rendered);
+        if (t->ev_fdone[k]) cudaEventDestroy(t->ev_fdone[k]);
+        if (t->ev_bdone[k]) cudaEventDestroy(t->ev_bdone[k]);
+    }
+    if (t->ev_fork) cudaEventDestroy(t->ev_fork);
+    if (t->ev_join) cudaEventDestroy(t->ev_join);
+    cudaFree(t->d_cams); cudaFree(t->d_pcam); cudaFree(t->d_bg);
     cudaFree(t->pimg); cudaFree(t->pcolor); cudaFree(t->avg_own); cudaFree(t->d_loss);
     cudaFree(t->flags); cudaFree(t->keep_idx); cudaFree(t->aux_idx); cudaFree(t->totals); cudaFree(t->dens_ticket);
     cudaFree(t->dens_lb); cudaFree(t->d_pairs);
@@ -371,8 +449,31 @@ int gsb_trainer_accumulate(gsb_trainer* t) {
                 t->ev_pool.push_back(e);
             }
         }
-        for (int i = 0; i < passes; i++)
-            if (int e = view_pass(t, i, fused, avg, S, t->timing_on ? &t->ev_pool[(size_t)i * (ST_COUNT + 1)] : nullptr)) return e;
+        // Pipelined mode: forward chains on sF, backward chains on sB, alternating workspace slots; a
+        // slot is reused only after the backward chain that read it has finished.  With stage timing on
+        // everything runs on `stream`, one kernel at a time, so a stage's time is its own.
+        const bool pipe = t->overlap && !t->timing_on && passes > 1;
+        if (pipe) {
+            GSB_CUDA_OK(cudaEventRecord(t->ev_fork, s));
+            GSB_CUDA_OK(cudaStreamWaitEvent(t->sF, t->ev_fork, 0));
+            GSB_CUDA_OK(cudaStreamWaitEvent(t->sB, t->ev_fork, 0));
+            t->exec_f = t->sF; t->exec_b = t->sB;
+        }
+        int err = GSB_OK;
+        for (int i = 0; i < passes && !err; i++) {
+            if (pipe) {
+                activate(t, i & 1);
+                if (i >= 2) err = cudaStreamWaitEvent(t->sF, t->ev_bdone[i & 1], 0) == cudaSuccess ? GSB_OK : GSB_ERR_CUDA;
+            }
+            if (!err) err = view_pass(t, i, fused, avg, S, t->timing_on ? &t->ev_pool[(size_t)i * (ST_COUNT + 1)] : nullptr);
+        }
+        if (pipe) {
+            t->exec_f = t->exec_b = nullptr;
+            cudaEventRecord(t->ev_join, t->sB);          // sB's last chain waited on sF's last chain
+            cudaStreamWaitEvent(s, t->ev_join, 0);
+            activate(t, 0);
+        }
+        if (err) return err;
         GSB_CUDA_OK(cudaGetLastError());
         // one synchronisation per iteration: learn every view's R, detect arena overflow
         GSB_CUDA_OK(cudaStreamSynchronize(s));
@@ -400,8 +501,11 @@ int gsb_trainer_accumulate(gsb_trainer* t) {
         // Some view did not fit: its gradients are incomplete.  Nothing but the running means and the
         // (self-clearing) scratch was written, so grow the arena and redo the iteration.
         t->stats.retries++;
-        GSB_CUDA_OK(cudaMemsetAsync(t->g.grads, 0, (size_t)t->geom_P * sizeof(GradRec), s));
-        GSB_CUDA_OK(cudaMemsetAsync(t->grads2, 0, (size_t)t->geom_P * sizeof(GradRec), s));
+        save_slot(t);
+        for (int k = 0; k < 2; k++) {
+            GSB_CUDA_OK(cudaMemsetAsync(t->slot[k].g.grads, 0, (size_t)t->geom_P * sizeof(GradRec), s));
+            GSB_CUDA_OK(cudaMemsetAsync(t->slot[k].grads2, 0, (size_t)t->geom_P * sizeof(GradRec), s));
+        }
         if (int e = ensure_bin(t, (uint32_t)std::min<size_t>(0x7FFFFFF0u, (size_t)maxR + maxR / 4 + 4096))) return e;
     }
     gsb_fail_msg("gsb_trainer_accumulate: binning arena kept overflowing");
@@ -427,6 +531,12 @@ int gsb_trainer_profile_pass(gsb_trainer* t, int pass_index, float* stage_ms, un
         counters[0] = t->h_R[pass_index];
         GSB_CUDA_OK(cudaMemcpy(&counters[1], &t->g.ctrl->num_visible, sizeof(unsigned int), cudaMemcpyDeviceToHost));
     }
+    return GSB_OK;
+}
+
+int gsb_trainer_set_overlap(gsb_trainer* t, int on) {
+    if (!t) return gsb_fail_msg("gsb_trainer_set_overlap: null trainer");
+    t->overlap = on != 0;
     return GSB_OK;
 }
 

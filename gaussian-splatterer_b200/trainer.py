@@ -245,6 +245,10 @@ class Trainer:
         check(lib().gsb_trainer_profile_pass(self._h, pass_index, ms, cnt))
         return dict(zip(self.STAGES, [float(x) for x in ms])), {"R": int(cnt[0]), "visible": int(cnt[1])}
 
+    def set_overlap(self, on=True):
+        """Forward chain of the next view pass underneath the backward chain of the current one (default on)."""
+        check(lib().gsb_trainer_set_overlap(self._h, int(on)))
+
     def set_stage_timing(self, on=True):
         """Bracket every stage of every view pass with CUDA events (resets the totals)."""
         check(lib().gsb_trainer_set_stage_timing(self._h, int(on)))

@@ -194,6 +194,11 @@ int gsb_trainer_set_fuse_backgrounds(gsb_trainer* t, int on);
 #define GSB_NUM_STAGES 10
 int gsb_trainer_profile_pass(gsb_trainer* t, int pass_index, float* stage_ms, unsigned int* counters);
 
+/* View pass i+1's forward chain (preprocess, sorts, forward blend) runs on a second internal stream
+ * underneath view pass i's backward chain (default on; same results: the two chains share no writable
+ * state).  0 = every kernel on the trainer's stream, one at a time. */
+int gsb_trainer_set_overlap(gsb_trainer* t, int on);
+
 /* Measurement: with timing on, every view pass of gsb_trainer_accumulate / gsb_trainer_train is
  * bracketed stage by stage with CUDA events on the trainer's stream; get_stage_times returns the
  * milliseconds summed per stage (order of gsb_trainer_profile_pass) over `passes` view-pass

@@ -202,3 +202,37 @@ def test_iterations_track_reference_replay_over_several_steps():
         assert np.linalg.norm(diff) <= 1e-3 * np.linalg.norm(move), k
         assert np.abs(diff).max() <= max(1e-2 * np.abs(move).max(), 5e-6), k
     rt.close(); tr.close()
+
+
+def test_overlapped_pipeline_equals_serial_execution():
+    """The two-stream pipeline (forward chain of pass i+1 under the backward chain of pass i, alternating
+    workspace slots) must give the running means of the serial order; also exercised with an odd pass count."""
+    import sys, os
+    sys.path.insert(0, os.path.join(GC.ROOT, "tools"))
+    from gpu_stage_probe import make_truths
+    W, Hh, P = 320, 200, 6000
+    project = gsb.synth.project_for("C2")
+    project.sphere1.count = 5
+    cams = gsb.Camera.getCameras(project)
+    cloud = gsb.synth.splat_cloud(P, 31, scale_hi=0.12)
+    tw, tb, _ = make_truths(gsb.synth.splat_cloud(P // 2, 32, scale_hi=0.12), cams, W, Hh, DEV)
+    res = {}
+    for fuse in (True, False):
+        for overlap in (False, True):
+            tr = gsb.Trainer(W, Hh, DEV, square_fov=False)
+            tr.set_fuse_backgrounds(fuse)
+            tr.set_overlap(overlap)
+            tr.enable_loss(True)
+            tr.model = gsb.ModelSplatsDevice(gsb.ModelSplatsHost.from_arrays(*[cloud[k] for k in KEYS]), DEV)
+            tr.truthFrameBuffersW, tr.truthFrameBuffersB, tr.truthCameras = tw, tb, cams
+            avg = tr.grad_tensor()
+            for _ in range(3):                      # repeated: slots and events are reused across iterations
+                tr.accumulate()
+            res[(fuse, overlap)] = (avg.clone(), tr.stats())
+            tr.close()
+    for fuse in (True, False):
+        a, sa = res[(fuse, False)]
+        b, sb = res[(fuse, True)]
+        assert sa["rendered_total"] == sb["rendered_total"]
+        assert abs(sa["sum_sq_residual"] - sb["sum_sq_residual"]) <= 1e-9 * sa["sum_sq_residual"]
+        assert H.rel_l2(b, a) <= 1e-5
