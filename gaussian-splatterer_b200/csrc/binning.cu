@@ -22,8 +22,11 @@ namespace {
 
 constexpr int RS_THREADS = 256;
 constexpr int RS_WARPS = RS_THREADS / 32;
-constexpr int RS_IPT = 16;
-constexpr int RS_TILE = RS_THREADS * RS_IPT;   // 4096 items per tile
+#ifndef GSB_RS_IPT
+#define GSB_RS_IPT 16
+#endif
+constexpr int RS_IPT = GSB_RS_IPT;
+constexpr int RS_TILE = RS_THREADS * RS_IPT;   // items per tile
 
 constexpr uint32_t LB_AGG = 1u, LB_INCL = 2u;
 

@@ -106,8 +106,12 @@ __device__ __forceinline__ V3 dir_grad(const ShDirs& q, V3 dRGB) {
 // M4 = the application's shape (SH degree 1, 4 coefficients, src/Config.h:19-20): the 24 running-mean
 // floats of the splat are loaded up front into registers (independent loads in flight together, hidden
 // behind the arithmetic) and stored once at the end, instead of 24 dependent read-modify-writes.
+#ifndef GSB_PB_THREADS
+#define GSB_PB_THREADS 256
+#define GSB_PB_BLOCKS 1
+#endif
 template <int NS, bool M4>
-__global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreprocessBwdArgs a) {
+__global__ void __launch_bounds__(GSB_PB_THREADS, GSB_PB_BLOCKS) preprocess_bwd_kernel(const PreprocessBwdArgs a) {
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= a.P || !(a.radii[idx] > 0)) return;
     const bool modeA = (a.avg == nullptr);
@@ -362,17 +366,17 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreprocessBwd
 
 void launch_preprocess_bwd(const PreprocessBwdArgs& a, cudaStream_t s) {
     if (a.P <= 0) return;
-    const int grid = gsb_div_up(a.P, 256);
+    const int grid = gsb_div_up(a.P, GSB_PB_THREADS);
     const bool trainer = a.avg != nullptr;
     // the fast shape needs 16-byte aligned 12-float SH records in the running-mean buffer
     const bool m4 = trainer && a.M == 4 && a.D == 1 && !a.colors_precomp &&
                     (reinterpret_cast<uintptr_t>(a.avg) % 16 == 0);
     if (trainer && a.grads2 != nullptr) {
-        if (m4) preprocess_bwd_kernel<2, true><<<grid, 256, 0, s>>>(a);
-        else preprocess_bwd_kernel<2, false><<<grid, 256, 0, s>>>(a);
+        if (m4) preprocess_bwd_kernel<2, true><<<grid, GSB_PB_THREADS, 0, s>>>(a);
+        else preprocess_bwd_kernel<2, false><<<grid, GSB_PB_THREADS, 0, s>>>(a);
     } else if (m4) {
-        preprocess_bwd_kernel<1, true><<<grid, 256, 0, s>>>(a);
+        preprocess_bwd_kernel<1, true><<<grid, GSB_PB_THREADS, 0, s>>>(a);
     } else {
-        preprocess_bwd_kernel<1, false><<<grid, 256, 0, s>>>(a);
+        preprocess_bwd_kernel<1, false><<<grid, GSB_PB_THREADS, 0, s>>>(a);
     }
 }

@@ -34,9 +34,11 @@ namespace {
 
 constexpr int RED_STRIDE = 36;   // floats per row of the reduction panel: 32 lanes + 4 pad (rows stay 16-byte aligned)
 
+constexpr int WB = 32;           // list entries per warp-private chunk (one per lane)
+
 struct BwdSmem {
-    SplatRec rec[2][RB];
-    uint32_t id[2][RB];
+    SplatRec rec[RENDER_WARPS][2][WB];
+    uint32_t id[RENDER_WARPS][2][WB];
 };
 
 // MODE 0: dL/dpixel given (Rasterizer::backward).  MODE 1: residual of one truth frame fused.
@@ -54,7 +56,6 @@ __global__ void __launch_bounds__(RENDER_THREADS, MODE == 2 ? 5 : 6) render_bwd_
     if (start == 0 && (MODE == 0 || a.loss_out == nullptr)) return;
     const uint2 range = a.ranges[tile];
     const uint32_t* list = a.point_list + range.x;
-    const int rounds = (start + RB - 1) / RB;
 
     const int bx0 = blockIdx.x * GSB_TILE + (warp & 1) * 8, by0 = blockIdx.y * GSB_TILE + (warp >> 1) * 8;
     const int pix_x = bx0 + (lane & 7);
@@ -124,55 +125,53 @@ __global__ void __launch_bounds__(RENDER_THREADS, MODE == 2 ? 5 : 6) render_bwd_
     }
     const int warp_max = __reduce_max_sync(0xffffffffu, max(ncontrib[0], ncontrib[1]));
 
-    // back to front: entry p of batch b is list position start - 1 - (b * RB + p)
-    auto fetch_id = [&](int batch) -> uint32_t {
-        const int q = start - 1 - (batch * RB + tid);
+    // Every warp walks the list on its own: no block-wide barrier, a warp whose 64 pixels blended
+    // nothing at or beyond `wstart` never looks at those entries, and warps of one tile drift apart
+    // freely.  Chunk c holds list positions wstart-1-32c ... (one entry per lane), back to front.
+    const int wstart = min(start, warp_max);
+    if (wstart == 0) return;
+    const int chunks = (wstart + WB - 1) / WB;
+    auto fetch_id = [&](int c) -> uint32_t {
+        const int q = wstart - 1 - (c * WB + lane);
         return q >= 0 ? list[q] : 0xFFFFFFFFu;
     };
     uint32_t next_id = fetch_id(0);
     auto issue = [&](int buf) {
         if (next_id != 0xFFFFFFFFu) {
             const SplatRec* g = a.recs + next_id;
-            cp_async16(&sm.rec[buf][tid].a, &g->a);
-            cp_async16(&sm.rec[buf][tid].b, &g->b);
-            cp_async16(&sm.rec[buf][tid].c, &g->c);
-            sm.id[buf][tid] = next_id;
+            SplatRec* d = &sm.rec[warp][buf][lane];
+            cp_async16(&d->a, &g->a);
+            cp_async16(&d->b, &g->b);
+            cp_async16(&d->c, &g->c);
+            sm.id[warp][buf][lane] = next_id;
         }
         cp_async_commit();
     };
     issue(0);
     next_id = fetch_id(1);
 
-    for (int i = 0; i < rounds; i++) {
+    for (int i = 0; i < chunks; i++) {
         cp_async_wait_all();
-        __syncthreads();   // batch i visible, batch i-1 fully consumed
-        if (i + 1 < rounds) {
+        __syncwarp();   // chunk i visible to the whole warp, chunk i-1 fully consumed
+        if (i + 1 < chunks) {
             issue((i + 1) & 1);
             next_id = fetch_id(i + 2);
         }
-        const SplatRec* buf = sm.rec[i & 1];
-        const uint32_t* ids = sm.id[i & 1];
-        const int cnt = min(RB, start - i * RB);
-        const int idx0 = start - 1 - i * RB;          // list position of entry 0 of this batch
-        if (idx0 - (cnt - 1) >= warp_max) continue;   // nothing in this batch reaches this warp's pixels
+        const SplatRec* buf = sm.rec[warp][i & 1];
+        const uint32_t* ids = sm.id[warp][i & 1];
+        const int cnt = min(WB, wstart - i * WB);
+        const int idx0 = wstart - 1 - i * WB;         // list position of entry 0 of this chunk
 
-        uint32_t mask[RB / 32];
-#pragma unroll
-        for (int m = 0; m < RB / 32; m++) {
-            const int e = m * 32 + lane;
-            bool hit = false;
-            if (e < cnt && idx0 - e < warp_max) {
-                const float2 xy = *reinterpret_cast<const float2*>(&buf[e].a);
-                const float2 ext = *reinterpret_cast<const float2*>(&buf[e].c.z);
-                hit = (fabsf(xy.x - bcx) <= ext.x + 3.5f) && (fabsf(xy.y - bcy) <= ext.y + 3.5f);
-            }
-            mask[m] = __ballot_sync(0xffffffffu, hit);
+        bool keep = false;
+        if (lane < cnt) {
+            const float2 xy = *reinterpret_cast<const float2*>(&buf[lane].a);
+            const float2 ext = *reinterpret_cast<const float2*>(&buf[lane].c.z);
+            keep = (fabsf(xy.x - bcx) <= ext.x + 3.5f) && (fabsf(xy.y - bcy) <= ext.y + 3.5f);
         }
-#pragma unroll
-        for (int m = 0; m < RB / 32; m++) {
-            uint32_t bits = mask[m];
+        {
+            uint32_t bits = __ballot_sync(0xffffffffu, keep);
             while (bits) {
-                const int j = m * 32 + __ffs(bits) - 1;
+                const int j = __ffs(bits) - 1;
                 bits &= bits - 1;
                 const int idx = idx0 - j;
                 const float4 ra = buf[j].a;   // x, y, conic.x, conic.y

@@ -2,12 +2,13 @@
 // Replaces renderCUDA<3> forward (reference cuda_rasterizer/forward.cu:261-374).
 //
 // One 128-thread CTA per 16x16 tile.  Each warp owns an 8x8 pixel sub-block (two pixels per lane,
-// same column, four rows apart) so a staged record read from shared memory serves two pixels.
-// Per batch of 128 list entries:
-//   * records (48 B, see SplatRec) are gathered into a double-buffered shared-memory ring with
-//     16-byte cp.async copies issued one batch ahead; the list indices of the batch after that are
+// same column, four rows apart) so a staged record read from shared memory serves two pixels, and
+// walks the tile's list independently of the other three warps (no barrier inside the loop).
+// Per chunk of 32 list entries (one per lane):
+//   * records (48 B, see SplatRec) are gathered into the warp's double-buffered shared-memory ring with
+//     16-byte cp.async copies issued one chunk ahead; the list indices of the chunk after that are
 //     prefetched into registers, so neither the dependent gather nor the index load is exposed;
-//   * every warp builds a 128-bit survivor mask with four ballots: an entry survives if the bounding
+//   * the warp builds a survivor mask with one ballot: an entry survives if the bounding
 //     box of { opacity * exp(power) >= 1/255 } (stored, conservatively inflated, in the record) meets
 //     the warp's sub-block.  The blend loop then visits survivors only (ffs over the mask), in list
 //     order.  Culled pairs are exactly those the reference would `continue` over, so nothing changes
@@ -23,8 +24,10 @@
 
 namespace {
 
+constexpr int WB = 32;   // list entries per warp-private chunk (one per lane)
+
 __global__ void __launch_bounds__(RENDER_THREADS) render_fwd_kernel(const RenderFwdArgs a) {
-    __shared__ SplatRec s_rec[2][RB];
+    __shared__ SplatRec s_rec[RENDER_WARPS][2][WB];
     __shared__ uint32_t s_max;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -45,55 +48,51 @@ __global__ void __launch_bounds__(RENDER_THREADS) render_fwd_kernel(const Render
 
     const uint2 range = a.ranges[tile];
     const int len = (int)(range.y - range.x);
-    const int rounds = (len + RB - 1) / RB;
+    const int chunks = (len + WB - 1) / WB;
     const uint32_t* list = a.point_list + range.x;
 
-    uint32_t next_id = (tid < len) ? list[tid] : 0xFFFFFFFFu;
+    // Every warp walks the tile's list on its own (no block-wide barrier in the loop): chunk c holds
+    // list positions 32c ... 32c+31, one entry per lane, gathered one chunk ahead.
+    uint32_t next_id = (lane < len) ? list[lane] : 0xFFFFFFFFu;
     auto issue = [&](int buf) {
         if (next_id != 0xFFFFFFFFu) {
             const SplatRec* g = a.recs + next_id;
-            cp_async16(&s_rec[buf][tid].a, &g->a);
-            cp_async16(&s_rec[buf][tid].b, &g->b);
-            cp_async16(&s_rec[buf][tid].c, &g->c);
+            SplatRec* d = &s_rec[warp][buf][lane];
+            cp_async16(&d->a, &g->a);
+            cp_async16(&d->b, &g->b);
+            cp_async16(&d->c, &g->c);
         }
         cp_async_commit();
     };
-    if (rounds > 0) {
+    if (chunks > 0) {
         issue(0);
-        next_id = (RB + tid < len) ? list[RB + tid] : 0xFFFFFFFFu;
+        next_id = (WB + lane < len) ? list[WB + lane] : 0xFFFFFFFFu;
     }
 
-    for (int i = 0; i < rounds; i++) {
-        const bool all = done[0] && done[1];
+    for (int i = 0; i < chunks; i++) {
+        // the warp stops as soon as its 64 pixels are finished (the reference votes per block, forward.cu:306-311;
+        // a finished pixel ignores every later entry either way)
+        if (__all_sync(0xffffffffu, done[0] && done[1])) break;
         cp_async_wait_all();
-        // batch i visible, batch i-1 fully consumed; vote like the reference's __syncthreads_count
-        if (__syncthreads_and(all)) break;
-        if (i + 1 < rounds) {
+        __syncwarp();   // chunk i visible to the whole warp, chunk i-1 fully consumed
+        if (i + 1 < chunks) {
             issue((i + 1) & 1);
-            const int q = (i + 2) * RB + tid;
+            const int q = (i + 2) * WB + lane;
             next_id = (q < len) ? list[q] : 0xFFFFFFFFu;
         }
-        const SplatRec* buf = s_rec[i & 1];
-        const int cnt = min(RB, len - i * RB);
-        if (__all_sync(0xffffffffu, all)) continue;   // this warp's 64 pixels are finished
+        const SplatRec* buf = s_rec[warp][i & 1];
+        const int cnt = min(WB, len - i * WB);
 
-        uint32_t mask[RB / 32];
-#pragma unroll
-        for (int m = 0; m < RB / 32; m++) {
-            const int e = m * 32 + lane;
-            bool hit = false;
-            if (e < cnt) {
-                const float2 xy = *reinterpret_cast<const float2*>(&buf[e].a);
-                const float2 ext = *reinterpret_cast<const float2*>(&buf[e].c.z);
-                hit = (fabsf(xy.x - bcx) <= ext.x + 3.5f) && (fabsf(xy.y - bcy) <= ext.y + 3.5f);
-            }
-            mask[m] = __ballot_sync(0xffffffffu, hit);
+        bool keep = false;
+        if (lane < cnt) {
+            const float2 xy = *reinterpret_cast<const float2*>(&buf[lane].a);
+            const float2 ext = *reinterpret_cast<const float2*>(&buf[lane].c.z);
+            keep = (fabsf(xy.x - bcx) <= ext.x + 3.5f) && (fabsf(xy.y - bcy) <= ext.y + 3.5f);
         }
-#pragma unroll
-        for (int m = 0; m < RB / 32; m++) {
-            uint32_t bits = mask[m];
+        {
+            uint32_t bits = __ballot_sync(0xffffffffu, keep);
             while (bits) {
-                const int j = m * 32 + __ffs(bits) - 1;
+                const int j = __ffs(bits) - 1;
                 bits &= bits - 1;
                 const float4 ra = buf[j].a;   // x, y, conic.x, conic.y
                 const float4 rb = buf[j].b;   // conic.z, opacity, r, g
@@ -121,7 +120,7 @@ __global__ void __launch_bounds__(RENDER_THREADS) render_fwd_kernel(const Render
                     Cg[k] = __fmaf_rn(T[k], __fmul_rn(alpha, rb.w), Cg[k]);
                     Cb[k] = __fmaf_rn(T[k], __fmul_rn(alpha, rc.x), Cb[k]);
                     T[k] = test_T;
-                    last[k] = (uint32_t)(i * RB + j + 1);
+                    last[k] = (uint32_t)(i * WB + j + 1);
                 }
             }
         }

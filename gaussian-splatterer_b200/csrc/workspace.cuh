@@ -33,8 +33,8 @@ struct GeomWs {
     GradRec* grads;
     unsigned long long* lookback;
 
-    // scan tiles are 2048 items, sort tiles 4096: the scan bounds the tile count
-    static size_t lookback_tiles(size_t P) { return (P + 2047) / 2048 + 1; }
+    // scan tiles are 2048 items, sort tiles >= 1024: the sort bounds the tile count
+    static size_t lookback_tiles(size_t P) { return (P + 1023) / 1024 + 1; }
 
     char* carve(char* base, size_t P) {
         Carver c(base);
@@ -66,7 +66,7 @@ struct BinWs {
     uint32_t* rvals[2];
     unsigned long long* lookback;
 
-    static size_t lookback_tiles(size_t R) { return (R + 4095) / 4096 + 1; }
+    static size_t lookback_tiles(size_t R) { return (R + 1023) / 1024 + 1; }
 
     char* carve(char* base, size_t R) {
         Carver c(base);
