@@ -1,0 +1,124 @@
+/* gsb_app.h -- C ABI of the headless application layer around the training hot path.
+ *
+ * The reference is a wxWidgets application; what sits either side of Trainer::train is re-built here without any GUI
+ * or graphics API, in C++ inside libgsb200.so, behind plain-C entry points:
+ *
+ *   gsb_project_*      Project + settings.json             src/Project.h:6-73, src/ui/UiFrame.cpp:323-331,358-370   (PJ, UF)
+ *   gsb_cameras_*      Camera::getCameras / preview        src/Camera.cpp:29-86, src/Camera.h:8-26                  (CA)
+ *   gsb_model_host_*   ModelSplatsHost                      src/ModelSplatsHost.{h,cpp}                              (MH)
+ *   gsb_gobj_*         .gobj text format                    src/ui/UiFrame.cpp:333-356,372-450                       (UF)
+ *   gsb_field_*        grid / mono / per-triangle fields    src/ui/UiFrame.cpp:137-264                               (UF)
+ *   gsb_png_*          screenshot PNG (vertical flip)       src/ui/tools/UiPanelToolsView.cpp:227-259, lib/stb       (TV)
+ *   gsb_rtx_*          truth ray caster (RtxHost/RtxDevice) src/rtx/RtxHost.{h,cpp}, src/rtx/RtxDevice.{cu,cuh}      (RH, RD)
+ *   gsb_app_*          the UiFrame::update scheduler        src/ui/UiFrame.cpp:266-298, src/ui/tools/UiPanelToolsTruth.cpp:185-197
+ *
+ * Conventions as in gsb.h: every function returns GSB_OK or an error code and sets gsb_last_error(); pointers are host
+ * pointers unless named dev_*; no torch / C++ types cross the boundary.
+ */
+#ifndef GSB_APP_H
+#define GSB_APP_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#include "gsb.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ------------------------------------------------------------------------------------------------ Project (PJ:6-73) */
+typedef struct gsb_camera_sphere {          /* Project::CameraSphere PJ:14-22 */
+    int count;
+    float distance, fovDeg, rotX, rotY;
+} gsb_camera_sphere;
+
+/* Every non-string member of Project in declaration order (PJ:14-62); bools are ints. */
+typedef struct gsb_project_data {
+    gsb_camera_sphere sphere1, sphere2;
+    int rtSamples;
+    float lrLocation, lrSh, lrScale, lrOpacity, lrRotation;
+    float paramScaleMax;
+    float paramCullOpacity, paramCullSize, paramDensifyVariance, paramSplitSize, paramSplitDistance, paramSplitScale,
+        paramCloneDistance;
+    int iterations, intervalCapture, intervalDensify;
+    float previewTimer;
+    int previewRtSamples;
+    float previewSplatScale;
+    int previewTruth, previewTruthIndex;
+    int previewFreeOrbit;
+    float previewFreeOrbitSpeed, previewFreeDistance, previewFreeFovDeg, previewFreeRotX, previewFreeRotY;
+    int renderResX, renderResY;
+} gsb_project_data;
+
+typedef struct gsb_project gsb_project;     /* gsb_project_data + perspective, pathModel, pathTextureDiffuse */
+
+int gsb_project_create(gsb_project** out);                       /* Project{} defaults (PJ) */
+int gsb_project_init_new(gsb_project* p);                        /* UiFrame::initProject UF:130-135: sphere2 = {0 cameras, fov 30} */
+int gsb_project_destroy(gsb_project* p);
+gsb_project_data* gsb_project_fields(gsb_project* p);            /* live pointer, valid until destroy */
+const char* gsb_project_get_string(gsb_project* p, const char* name);           /* "perspective" | "pathModel" | "pathTextureDiffuse" */
+int gsb_project_set_string(gsb_project* p, const char* name, const char* value);
+/* nlohmann to_json + dump(): compact, keys sorted, floats widened to double and printed shortest-round-trip (UF:323-331).
+ * Writes at most cap bytes including the terminator; *needed = strlen + 1. */
+int gsb_project_to_json(gsb_project* p, char* buf, size_t cap, size_t* needed);
+/* nlohmann from_json of NLOHMANN_DEFINE_TYPE_INTRUSIVE_WITH_DEFAULT: absent keys become Project{} defaults, wrong types
+ * are errors (the messages of json.exception.type_error.302/306, parse_error.101), unknown keys are ignored (UF:358-370). */
+int gsb_project_from_json(gsb_project* p, const char* text);
+int gsb_project_save(gsb_project* p, const char* path);          /* UiFrame::saveSettings (perspective is whatever was set) */
+int gsb_project_load(gsb_project* p, const char* path);          /* UiFrame::loadSettings: missing file is an error */
+int gsb_project_train_params(const gsb_project_data* d, gsb_project_params* out);    /* the 13 floats Trainer::train reads */
+
+/* ------------------------------------------------------------------------------------------------- Camera (CA:29-86) */
+typedef struct gsb_camera_desc {            /* Camera CA(h):16-21 */
+    float location[3];
+    float target[3];
+    float fovDegY;
+} gsb_camera_desc;
+
+int gsb_cameras_count(const gsb_project_data* d);                                  /* Camera::getCamerasCount */
+int gsb_cameras_get(const gsb_project_data* d, gsb_camera_desc* out, int cap);     /* Camera::getCameras, sphere1 then sphere2 */
+int gsb_camera_preview(const gsb_project_data* d, gsb_camera_desc* out);           /* Camera::getPreviewCamera */
+/* view = -lookAt, projview = perspective(fovY, w/h, 0.1, 100) * view; square_fov != 0 is Trainer::train's
+ * tan_fovx = tan_fovy (src/Trainer.cu:355-356), else Trainer::render's aspect-scaled angle (src/Trainer.cu:196-197). */
+int gsb_camera_constants(const gsb_camera_desc* c, int width, int height, int square_fov, gsb_camera* out);
+int gsb_camera_inverse_projview(const gsb_camera_desc* c, float aspect, float out16[16]);   /* glm::inverse, RH:212 */
+
+/* ----------------------------------------------------------------------------------- ModelSplatsHost (MH), .gobj, fields */
+typedef struct gsb_model_host gsb_model_host;
+
+typedef struct gsb_model_host_view {        /* the public members of ModelSplatsHost MH(h):11-21 */
+    int capacity, shDegree, shCoeffs, count;
+    float *locations, *shs, *scales, *opacities, *rotations;
+} gsb_model_host_view;
+
+int gsb_model_host_create(gsb_model_host** out, int capacity, int shDegree, int shCoeffs);           /* MH:6-15 */
+/* The five-vector constructor MH:31-63: capacity = 1e6 * 10^k >= count, shCoeffs / shDegree derived from the SH vector,
+ * "Inconsistent feature dimensions supplied when creating a host model!" on mismatch. n_* are float counts. */
+int gsb_model_host_from_arrays(gsb_model_host** out, const float* locations, size_t n_locations, const float* shs, size_t n_shs,
+                               const float* scales, size_t n_scales, const float* opacities, size_t n_opacities,
+                               const float* rotations, size_t n_rotations);
+int gsb_model_host_destroy(gsb_model_host* m);
+int gsb_model_host_get(gsb_model_host* m, gsb_model_host_view* out);
+int gsb_model_host_push_back(gsb_model_host* m, const float location[3], const float* sh, int n_sh, const float scale[3],
+                             float opacity, const float rotation_wxyz[4]);                           /* MH:72-84 */
+int gsb_model_host_copy(gsb_model_host* m, int indexTo, int indexFrom);                              /* MH:86-98 */
+int gsb_gobj_save(gsb_model_host* m, const char* path);          /* UiFrame::saveSplats UF:333-356 (ostream default precision 6) */
+int gsb_gobj_load(gsb_model_host** out, const char* path);       /* UiFrame::loadSplats UF:372-450 ("Inconsistent SH degree!") */
+int gsb_field_grid(gsb_model_host** out);                        /* UiFrame::initFieldGrid UF:137-160: 17^3 splats, capacity 1e6 */
+int gsb_field_mono(gsb_model_host** out);                        /* UiFrame::initFieldMono UF:162-176 */
+int gsb_field_model(gsb_model_host** out, const char* obj_path); /* UiFrame::initFieldModel UF:178-264: one splat per triangle */
+
+/* --------------------------------------------------------------------------------------------------------- PNG (TV, stb) */
+/* stbi_flip_vertically_on_write(flip) + stbi_write_png(path, w, h, 4, rgba, w*4) (TV:236-238,254-256). host memory. */
+int gsb_png_write(const char* path, const uint32_t* rgba, int width, int height, int flip_vertically);
+/* stbi_load(path, &w, &h, nullptr, STBI_rgb_alpha) for PNG files (RH:15-17): 8/16-bit grey, grey+alpha, RGB, RGBA, palette,
+ * non-interlaced.  *rgba_out is malloc'ed; release with gsb_free. */
+int gsb_png_read(const char* path, uint8_t** rgba_out, int* width, int* height);
+void gsb_free(void* p);
+
+#ifdef __cplusplus
+}
+#endif
+
+#endif /* GSB_APP_H */
