@@ -1,0 +1,263 @@
+"""ctypes mirror of include/gsb_app.h: the headless application layer.
+
+Python here is only the test / bench harness over the C ABI; the logic (settings.json, cameras, .gobj, field
+initialisers, PNG, the truth ray caster, the UiFrame::update scheduler) lives in C++ / CUDA inside libgsb200.so.
+Names follow the reference: Project (src/Project.h), Camera (src/Camera.h), ModelSplatsHost (src/ModelSplatsHost.h),
+UiFrame::saveSplats / loadSplats / saveSettings / loadSettings / initField* (src/ui/UiFrame.cpp).
+"""
+import ctypes as C
+
+import numpy as np
+
+from ._lib import CameraC, ProjectParams, check, lib
+
+
+class CameraSphereC(C.Structure):
+    _fields_ = [("count", C.c_int), ("distance", C.c_float), ("fovDeg", C.c_float), ("rotX", C.c_float), ("rotY", C.c_float)]
+
+
+class ProjectData(C.Structure):
+    """gsb_project_data: every non-string member of Project in declaration order."""
+    _fields_ = [("sphere1", CameraSphereC), ("sphere2", CameraSphereC), ("rtSamples", C.c_int)] + \
+        [(n, C.c_float) for n in ("lrLocation", "lrSh", "lrScale", "lrOpacity", "lrRotation", "paramScaleMax",
+                                  "paramCullOpacity", "paramCullSize", "paramDensifyVariance", "paramSplitSize",
+                                  "paramSplitDistance", "paramSplitScale", "paramCloneDistance")] + \
+        [("iterations", C.c_int), ("intervalCapture", C.c_int), ("intervalDensify", C.c_int), ("previewTimer", C.c_float),
+         ("previewRtSamples", C.c_int), ("previewSplatScale", C.c_float), ("previewTruth", C.c_int),
+         ("previewTruthIndex", C.c_int), ("previewFreeOrbit", C.c_int), ("previewFreeOrbitSpeed", C.c_float),
+         ("previewFreeDistance", C.c_float), ("previewFreeFovDeg", C.c_float), ("previewFreeRotX", C.c_float),
+         ("previewFreeRotY", C.c_float), ("renderResX", C.c_int), ("renderResY", C.c_int)]
+
+
+class CameraDesc(C.Structure):
+    """gsb_camera_desc = Camera{location, target, fovDegY}."""
+    _fields_ = [("location", C.c_float * 3), ("target", C.c_float * 3), ("fovDegY", C.c_float)]
+
+
+class ModelHostView(C.Structure):
+    _fields_ = [("capacity", C.c_int), ("shDegree", C.c_int), ("shCoeffs", C.c_int), ("count", C.c_int)] + \
+        [(n, C.POINTER(C.c_float)) for n in ("locations", "shs", "scales", "opacities", "rotations")]
+
+
+_bound = False
+
+
+def L():
+    """libgsb200.so with the gsb_app.h prototypes attached."""
+    global _bound
+    lb = lib()
+    if _bound:
+        return lb
+    vp, i, f, sz, cp = C.c_void_p, C.c_int, C.c_float, C.c_size_t, C.c_char_p
+    PD, CD = C.POINTER(ProjectData), C.POINTER(CameraDesc)
+    FP = C.POINTER(C.c_float)
+    sigs = {
+        "gsb_project_create": ([C.POINTER(vp)], i), "gsb_project_init_new": ([vp], i), "gsb_project_destroy": ([vp], i),
+        "gsb_project_fields": ([vp], PD), "gsb_project_get_string": ([vp, cp], cp), "gsb_project_set_string": ([vp, cp, cp], i),
+        "gsb_project_to_json": ([vp, vp, sz, C.POINTER(sz)], i), "gsb_project_from_json": ([vp, cp], i),
+        "gsb_project_save": ([vp, cp], i), "gsb_project_load": ([vp, cp], i),
+        "gsb_project_train_params": ([PD, C.POINTER(ProjectParams)], i),
+        "gsb_cameras_count": ([PD], i), "gsb_cameras_get": ([PD, CD, i], i), "gsb_camera_preview": ([PD, CD], i),
+        "gsb_camera_constants": ([CD, i, i, i, C.POINTER(CameraC)], i), "gsb_camera_inverse_projview": ([CD, f, FP], i),
+        "gsb_model_host_create": ([C.POINTER(vp), i, i, i], i),
+        "gsb_model_host_from_arrays": ([C.POINTER(vp), FP, sz, FP, sz, FP, sz, FP, sz, FP, sz], i),
+        "gsb_model_host_destroy": ([vp], i), "gsb_model_host_get": ([vp, C.POINTER(ModelHostView)], i),
+        "gsb_model_host_push_back": ([vp, FP, FP, i, FP, f, FP], i), "gsb_model_host_copy": ([vp, i, i], i),
+        "gsb_gobj_save": ([vp, cp], i), "gsb_gobj_load": ([C.POINTER(vp), cp], i),
+        "gsb_field_grid": ([C.POINTER(vp)], i), "gsb_field_mono": ([C.POINTER(vp)], i), "gsb_field_model": ([C.POINTER(vp), cp], i),
+        "gsb_png_write": ([cp, vp, i, i, i], i), "gsb_png_read": ([cp, C.POINTER(vp), C.POINTER(i), C.POINTER(i)], i),
+        "gsb_free": ([vp], None),
+    }
+    for name, (args, res) in sigs.items():
+        fn = getattr(lb, name)
+        fn.argtypes, fn.restype = args, res
+    _bound = True
+    return lb
+
+
+APP_SYMBOLS_HOST = [
+    "gsb_project_create", "gsb_project_init_new", "gsb_project_destroy", "gsb_project_fields", "gsb_project_get_string",
+    "gsb_project_set_string", "gsb_project_to_json", "gsb_project_from_json", "gsb_project_save", "gsb_project_load",
+    "gsb_project_train_params", "gsb_cameras_count", "gsb_cameras_get", "gsb_camera_preview", "gsb_camera_constants",
+    "gsb_camera_inverse_projview", "gsb_model_host_create", "gsb_model_host_from_arrays", "gsb_model_host_destroy",
+    "gsb_model_host_get", "gsb_model_host_push_back", "gsb_model_host_copy", "gsb_gobj_save", "gsb_gobj_load",
+    "gsb_field_grid", "gsb_field_mono", "gsb_field_model", "gsb_png_write", "gsb_png_read", "gsb_free"]
+
+
+def _fp(a):
+    return a.ctypes.data_as(C.POINTER(C.c_float))
+
+
+class Project:
+    """Project (src/Project.h): numeric members through `.d` (live struct), the three strings as properties."""
+
+    def __init__(self, new=False):
+        self._h = C.c_void_p()
+        check(L().gsb_project_create(C.byref(self._h)))
+        if new:
+            check(L().gsb_project_init_new(self._h))        # UiFrame::initProject
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            L().gsb_project_destroy(self._h)
+            self._h = None
+
+    @property
+    def d(self):
+        return L().gsb_project_fields(self._h).contents
+
+    def __getattr__(self, name):
+        if name in ("perspective", "pathModel", "pathTextureDiffuse"):
+            return L().gsb_project_get_string(self._h, name.encode()).decode("utf-8")
+        if name.startswith("_"):
+            raise AttributeError(name)
+        return getattr(self.d, name)
+
+    def __setattr__(self, name, value):
+        if name == "_h":
+            object.__setattr__(self, name, value)
+        elif name in ("perspective", "pathModel", "pathTextureDiffuse"):
+            check(L().gsb_project_set_string(self._h, name.encode(), value.encode("utf-8")))
+        else:
+            setattr(self.d, name, value)
+
+    def dumps(self):
+        need = C.c_size_t(0)
+        check(L().gsb_project_to_json(self._h, None, 0, C.byref(need)))
+        buf = C.create_string_buffer(need.value)
+        check(L().gsb_project_to_json(self._h, buf, need.value, None))
+        return buf.value.decode("utf-8")
+
+    def loads(self, text):
+        check(L().gsb_project_from_json(self._h, text.encode("utf-8")))
+
+    def save(self, path):
+        check(L().gsb_project_save(self._h, str(path).encode()))
+
+    def load(self, path):
+        check(L().gsb_project_load(self._h, str(path).encode()))
+
+    def train_params(self):
+        q = ProjectParams()
+        check(L().gsb_project_train_params(C.byref(self.d), C.byref(q)))
+        return q
+
+    # ---- Camera statics (src/Camera.h:11-13)
+    def cameras(self):
+        n = L().gsb_cameras_count(C.byref(self.d))
+        arr = (CameraDesc * max(n, 1))()
+        check(L().gsb_cameras_get(C.byref(self.d), arr, n))
+        return [arr[k] for k in range(n)]
+
+    def preview_camera(self):
+        c = CameraDesc()
+        check(L().gsb_camera_preview(C.byref(self.d), C.byref(c)))
+        return c
+
+
+def camera_desc(location, target=(0.0, 0.0, 0.0), fov=60.0):
+    c = CameraDesc()
+    c.location[:] = [float(x) for x in location]
+    c.target[:] = [float(x) for x in target]
+    c.fovDegY = float(fov)
+    return c
+
+
+def camera_constants(desc, width, height, square_fov=False):
+    out = CameraC()
+    check(L().gsb_camera_constants(C.byref(desc), width, height, int(square_fov), C.byref(out)))
+    return out
+
+
+def camera_inverse_projview(desc, aspect):
+    out = np.zeros(16, np.float32)
+    check(L().gsb_camera_inverse_projview(C.byref(desc), float(aspect), _fp(out)))
+    return out
+
+
+class ModelSplatsHostC:
+    """ModelSplatsHost held by the library (handle); arrays come back as numpy copies."""
+
+    def __init__(self, handle):
+        self._h = handle
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            L().gsb_model_host_destroy(self._h)
+            self._h = None
+
+    @classmethod
+    def create(cls, capacity, shDegree, shCoeffs):
+        h = C.c_void_p()
+        check(L().gsb_model_host_create(C.byref(h), capacity, shDegree, shCoeffs))
+        return cls(h)
+
+    @classmethod
+    def from_arrays(cls, locations, shs, scales, opacities, rotations):
+        a = [np.ascontiguousarray(x, dtype=np.float32).reshape(-1) for x in (locations, shs, scales, opacities, rotations)]
+        h = C.c_void_p()
+        args = []
+        for x in a:
+            args += [_fp(x), x.size]
+        check(L().gsb_model_host_from_arrays(C.byref(h), *args))
+        return cls(h)
+
+    @classmethod
+    def _make(cls, fn, *args):
+        h = C.c_void_p()
+        check(fn(C.byref(h), *args))
+        return cls(h)
+
+    @classmethod
+    def load_gobj(cls, path):
+        return cls._make(L().gsb_gobj_load, str(path).encode())
+
+    @classmethod
+    def field_grid(cls):
+        return cls._make(L().gsb_field_grid)
+
+    @classmethod
+    def field_mono(cls):
+        return cls._make(L().gsb_field_mono)
+
+    @classmethod
+    def field_model(cls, obj_path):
+        return cls._make(L().gsb_field_model, str(obj_path).encode())
+
+    def view(self):
+        v = ModelHostView()
+        check(L().gsb_model_host_get(self._h, C.byref(v)))
+        return v
+
+    def arrays(self):
+        v = self.view()
+        n, M = v.count, v.shCoeffs
+        grab = lambda p, k: np.ctypeslib.as_array(p, shape=(k,)).copy() if k else np.zeros(0, np.float32)
+        return {"locations": grab(v.locations, 3 * n), "shs": grab(v.shs, 3 * M * n), "scales": grab(v.scales, 3 * n),
+                "opacities": grab(v.opacities, n), "rotations": grab(v.rotations, 4 * n)}
+
+    def push_back(self, location, sh, scale, opacity, rotation):
+        loc, s, sc, r = [np.ascontiguousarray(x, dtype=np.float32) for x in (location, sh, scale, rotation)]
+        check(L().gsb_model_host_push_back(self._h, _fp(loc), _fp(s), s.size, _fp(sc), float(opacity), _fp(r)))
+
+    def copy(self, to, frm):
+        check(L().gsb_model_host_copy(self._h, to, frm))
+
+    def save_gobj(self, path):
+        check(L().gsb_gobj_save(self._h, str(path).encode()))
+
+
+def png_write(path, rgba_u32, width, height, flip_vertically=True):
+    a = np.ascontiguousarray(rgba_u32, dtype=np.uint32)
+    assert a.size == width * height
+    check(L().gsb_png_write(str(path).encode(), a.ctypes.data_as(C.c_void_p), width, height, int(flip_vertically)))
+
+
+def png_read(path):
+    p, w, h = C.c_void_p(), C.c_int(), C.c_int()
+    check(L().gsb_png_read(str(path).encode(), C.byref(p), C.byref(w), C.byref(h)))
+    try:
+        buf = (C.c_uint8 * (w.value * h.value * 4)).from_address(p.value)
+        return np.frombuffer(buf, dtype=np.uint8).reshape(h.value, w.value, 4).copy()
+    finally:
+        L().gsb_free(p)

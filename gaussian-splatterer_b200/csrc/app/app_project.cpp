@@ -75,7 +75,7 @@ struct Parser {
             if (*q == '\n') { line++; col = 0; } else col++;
         }
         std::ostringstream os;
-        os << "[json.exception.parse_error.101] parse error at line " << line << ", column " << col + 1 << ": " << what;
+        os << "[json.exception.parse_error.101] parse error at line " << line << ", column " << col << ": " << what;
         throw std::runtime_error(os.str());
     }
     void ws() { while (p < end && (*p == ' ' || *p == '\t' || *p == '\n' || *p == '\r')) p++; }
