@@ -117,6 +117,35 @@ int gsb_png_write(const char* path, const uint32_t* rgba, int width, int height,
 int gsb_png_read(const char* path, uint8_t** rgba_out, int* width, int* height);
 void gsb_free(void* p);
 
+/* ------------------------------------------------------------------------------- truth ray caster (RH, RD): SURVEY 8 f1 */
+/* RtxHost + RtxDevice without OptiX/OWL: a CUDA path tracer over a BVH of the triangle mesh, one thread per pixel,
+ * `samples` jittered primary rays per pixel, <= 50 bounces, alpha-tested lambertian scattering, sky = min(1, 1 + dir.y),
+ * the background colour where no surface reflected, RGBA8 packing int(c * 256) (RD:8-158, owl_device.h:79-90).
+ * Per-pixel random numbers come from owl's LCG<4> seeded with (pixel.x, pixel.y): the reference leaves the generator
+ * state uninitialised (RD:57 `PerRayData prd;`, owl random.h:52-55), so its sequence is undefined; this is the seeding owl's
+ * own samples use.  The hardware triangle test of OptiX is replaced by Moeller-Trumbore (no culling). */
+typedef struct gsb_rtx gsb_rtx;
+
+int gsb_rtx_create(gsb_rtx** out);                               /* RtxHost::RtxHost: no model, blank 8x8 grey texture */
+int gsb_rtx_destroy(gsb_rtx* r);
+int gsb_rtx_reset(gsb_rtx* r);                                   /* RtxHost::reset RH:72-75 */
+int gsb_rtx_load_model(gsb_rtx* r, const char* obj_path);        /* RtxHost::loadModel RH:107-182 (missing path: no-op like :108) */
+/* The same from memory (procedural meshes): vertices[3*nv], triangles[3*nt] zero-based, texcoords[6*nt] per corner or NULL. */
+int gsb_rtx_set_mesh(gsb_rtx* r, const float* vertices, int nv, const int* triangles, int nt, const float* texcoords);
+int gsb_rtx_load_texture_diffuse(gsb_rtx* r, const char* png_path);                  /* RtxHost::loadTextureDiffuse RH:184-189 */
+int gsb_rtx_set_texture_diffuse(gsb_rtx* r, const uint8_t* rgba, int width, int height);
+int gsb_rtx_model_present(gsb_rtx* r);
+/* RtxHost::render RH:191-221.  dev_frame_buffer: width*height RGBA8 on the device.  splat_cameras: n x 3 host floats (the
+ * camera indicator orbs of the preview, RD:33-47) or NULL.  Without a model the frame is cleared to 0 (RH:220). */
+int gsb_rtx_render(gsb_rtx* r, uint32_t* dev_frame_buffer, int width, int height, const gsb_camera_desc* camera,
+                   const float background[3], int samples, const float* splat_cameras, int n_splat_cameras, void* stream);
+/* Both truth frames of one camera (white and black background, src/Trainer.cu:230-237) from ONE trace: with a seeded
+ * generator the two renders follow identical paths and differ only where no surface reflected. */
+int gsb_rtx_render_pair(gsb_rtx* r, uint32_t* dev_frame_white, uint32_t* dev_frame_black, int width, int height,
+                        const gsb_camera_desc* camera, int samples, void* stream);
+/* rays traced (primary + bounce segments) by the last render call, for the Mray/s figure */
+int gsb_rtx_last_ray_count(gsb_rtx* r, unsigned long long* out);
+
 #ifdef __cplusplus
 }
 #endif
