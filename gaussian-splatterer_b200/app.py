@@ -261,3 +261,87 @@ def png_read(path):
         return np.frombuffer(buf, dtype=np.uint8).reshape(h.value, w.value, 4).copy()
     finally:
         L().gsb_free(p)
+
+
+# ------------------------------------------------------------------------------------------------ truth ray caster (f1)
+APP_SYMBOLS_RTX = ["gsb_rtx_create", "gsb_rtx_destroy", "gsb_rtx_reset", "gsb_rtx_load_model", "gsb_rtx_set_mesh",
+                   "gsb_rtx_load_texture_diffuse", "gsb_rtx_set_texture_diffuse", "gsb_rtx_model_present", "gsb_rtx_render",
+                   "gsb_rtx_render_pair", "gsb_rtx_last_ray_count"]
+_rtx_bound = False
+
+
+def _LR():
+    global _rtx_bound
+    lb = L()
+    if not _rtx_bound:
+        vp, i, cp = C.c_void_p, C.c_int, C.c_char_p
+        CD, FP = C.POINTER(CameraDesc), C.POINTER(C.c_float)
+        sigs = {
+            "gsb_rtx_create": ([C.POINTER(vp)], i), "gsb_rtx_destroy": ([vp], i), "gsb_rtx_reset": ([vp], i),
+            "gsb_rtx_load_model": ([vp, cp], i), "gsb_rtx_set_mesh": ([vp, FP, i, C.POINTER(i), i, FP], i),
+            "gsb_rtx_load_texture_diffuse": ([vp, cp], i), "gsb_rtx_set_texture_diffuse": ([vp, vp, i, i], i),
+            "gsb_rtx_model_present": ([vp], i), "gsb_rtx_render": ([vp, vp, i, i, CD, FP, i, FP, i, vp], i),
+            "gsb_rtx_render_pair": ([vp, vp, vp, i, i, CD, i, vp], i),
+            "gsb_rtx_last_ray_count": ([vp, C.POINTER(C.c_ulonglong)], i),
+        }
+        for name, (args, res) in sigs.items():
+            fn = getattr(lb, name)
+            fn.argtypes, fn.restype = args, res
+        _rtx_bound = True
+    return lb
+
+
+class RtxHost:
+    """RtxHost (src/rtx/RtxHost.h:16-41): reset / loadModel / loadTextureDiffuse / render, plus in-memory setters."""
+
+    def __init__(self):
+        self._h = C.c_void_p()
+        check(_LR().gsb_rtx_create(C.byref(self._h)))
+
+    def close(self):
+        if getattr(self, "_h", None):
+            _LR().gsb_rtx_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    def reset(self):
+        check(_LR().gsb_rtx_reset(self._h))
+
+    def loadModel(self, path):
+        check(_LR().gsb_rtx_load_model(self._h, str(path).encode()))
+
+    def loadTextureDiffuse(self, path):
+        check(_LR().gsb_rtx_load_texture_diffuse(self._h, str(path).encode()))
+
+    def set_mesh(self, vertices, triangles, texcoords=None):
+        v = np.ascontiguousarray(vertices, dtype=np.float32).reshape(-1)
+        t = np.ascontiguousarray(triangles, dtype=np.int32).reshape(-1)
+        tc = None if texcoords is None else np.ascontiguousarray(texcoords, dtype=np.float32).reshape(-1)
+        check(_LR().gsb_rtx_set_mesh(self._h, _fp(v), v.size // 3, t.ctypes.data_as(C.POINTER(C.c_int)), t.size // 3,
+                                     None if tc is None else _fp(tc)))
+
+    def set_texture(self, rgba):
+        a = np.ascontiguousarray(rgba, dtype=np.uint8)
+        check(_LR().gsb_rtx_set_texture_diffuse(self._h, a.ctypes.data_as(C.c_void_p), a.shape[1], a.shape[0]))
+
+    @property
+    def modelPresent(self):
+        return bool(_LR().gsb_rtx_model_present(self._h))
+
+    def render(self, frameBuffer, size, camera, background, samples, cameras=(), stream=None):
+        """RtxHost::render(frameBuffer, size, camera, background, samples, cameras): frameBuffer is an int32/uint32 CUDA
+        tensor of size.x * size.y elements; `cameras` are CameraDesc whose locations become the indicator orbs."""
+        bg = np.ascontiguousarray(background, dtype=np.float32)
+        orbs = np.array([list(c.location) for c in cameras], np.float32).reshape(-1) if len(cameras) else None
+        check(_LR().gsb_rtx_render(self._h, C.c_void_p(frameBuffer.data_ptr()), size[0], size[1], C.byref(camera), _fp(bg),
+                                   int(samples), None if orbs is None else _fp(orbs), len(cameras), stream))
+
+    def render_pair(self, fbW, fbB, size, camera, samples, stream=None):
+        check(_LR().gsb_rtx_render_pair(self._h, C.c_void_p(fbW.data_ptr()), C.c_void_p(fbB.data_ptr()), size[0], size[1],
+                                        C.byref(camera), int(samples), stream))
+
+    def last_ray_count(self):
+        n = C.c_ulonglong(0)
+        check(_LR().gsb_rtx_last_ray_count(self._h, C.byref(n)))
+        return n.value

@@ -87,3 +87,63 @@ def shard_cameras(cameras, n1, rank, world):
     every rank gets the same wide / close-up mix."""
     s1, s2 = cameras[:n1], cameras[n1:]
     return s1[rank::world] + s2[rank::world]
+
+
+def textured_mesh(rings=24, segments=48, seed=7, radius=2.5, bumps=0.35, floor=True):
+    """Procedural textured mesh for the truth ray tracer (north_star: "a procedural textured mesh"): a bumpy UV sphere
+    (radius modulated by a few low-frequency lobes) over an optional floor quad.  Returns (vertices[nv,3] f32,
+    triangles[nt,3] i32 zero-based, texcoords[nt,3,2] f32 per corner) -- the three arrays RtxHost buffers
+    (src/rtx/RtxHost.h:20-22)."""
+    rng_phase = uniform(6, seed, 40) * 2.0 * math.pi
+    th = np.linspace(0.0, math.pi, rings + 1)
+    ph = np.linspace(0.0, 2.0 * math.pi, segments + 1)
+    T, Pp = np.meshgrid(th, ph, indexing="ij")
+    r = radius * (1.0 + bumps * (0.5 * np.sin(3 * T + rng_phase[0]) * np.cos(2 * Pp + rng_phase[1]) +
+                                 0.3 * np.sin(5 * Pp + rng_phase[2]) * np.sin(T) + 0.2 * np.cos(4 * T + rng_phase[3])))
+    x, y, z = r * np.sin(T) * np.cos(Pp), r * np.cos(T), r * np.sin(T) * np.sin(Pp)
+    verts = np.stack([x, y, z], -1).reshape(-1, 3)
+    uv = np.stack([Pp / (2.0 * math.pi) * 3.0, 1.0 - T / math.pi], -1).reshape(-1, 2)      # u repeats 3x: exercises wrap
+    tris, tcs = [], []
+    idx = lambda i, j: i * (segments + 1) + j
+    for i in range(rings):
+        for j in range(segments):
+            a, b, c, d = idx(i, j), idx(i + 1, j), idx(i + 1, j + 1), idx(i, j + 1)
+            for t in ((a, b, c), (a, c, d)):
+                tris.append(t)
+                tcs.append([uv[t[0]], uv[t[1]], uv[t[2]]])
+    if floor:
+        n0 = verts.shape[0]
+        fy = -radius * (1.0 + bumps) - 0.25
+        verts = np.concatenate([verts, np.array([[-8, fy, -8], [8, fy, -8], [8, fy, 8], [-8, fy, 8]], np.float64)])
+        fuv = np.array([[0, 0], [4, 0], [4, 4], [0, 4]], np.float64)
+        for t in ((0, 2, 1), (0, 3, 2)):
+            tris.append((n0 + t[0], n0 + t[1], n0 + t[2]))
+            tcs.append([fuv[t[0]], fuv[t[1]], fuv[t[2]]])
+    return verts.astype(np.float32), np.asarray(tris, np.int32), np.asarray(tcs, np.float32)
+
+
+def procedural_texture(size=64, seed=11):
+    """RGBA8 [size, size, 4]: coloured checker with smooth gradients; every 4th cell is see-through (alpha 0) and a band is
+    half transparent, so the alpha test of the closest-hit program (src/rtx/RtxDevice.cu:124) takes both branches."""
+    yy, xx = np.mgrid[0:size, 0:size]
+    cell = (xx // (size // 8) + yy // (size // 8))
+    base = uniform(3 * 64, seed, 50).reshape(64, 3)
+    rgb = base[(cell * 7 + (xx // (size // 8))) % 64] * 0.6 + 0.35
+    rgb = rgb * (0.75 + 0.25 * np.sin(xx / size * 2 * math.pi)[..., None])
+    alpha = np.full((size, size), 255.0)
+    alpha[(cell % 4) == 3] = 0.0
+    alpha[size // 2:size // 2 + size // 16] = 128.0
+    out = np.concatenate([np.clip(rgb, 0, 1) * 255.0, alpha[..., None]], -1)
+    return np.ascontiguousarray(out.astype(np.uint8))
+
+
+def write_obj(path, vertices, triangles, texcoords):
+    """The mesh as an OBJ file the reference's loader reads (v / vt / f a/ta b/tb c/tc, src/rtx/RtxHost.cpp:119-160)."""
+    with open(path, "w") as f:
+        for v in vertices:
+            f.write("v %.9g %.9g %.9g\n" % tuple(v))
+        flat = texcoords.reshape(-1, 2)
+        for t in flat:
+            f.write("vt %.9g %.9g\n" % tuple(t))
+        for k, t in enumerate(triangles):
+            f.write("f %d/%d %d/%d %d/%d\n" % (t[0] + 1, 3 * k + 1, t[1] + 1, 3 * k + 2, t[2] + 1, 3 * k + 3))

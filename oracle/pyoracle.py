@@ -159,3 +159,27 @@ def densify(cloud, count, capacity, M, var, avg_loc, params13):
     n = lib().oracle_densify(count, capacity, M, _p(bufs["locations"]), _p(bufs["shs"]), _p(bufs["scales"]), _p(bufs["opacities"]),
                              _p(bufs["rotations"]), _p(v), _p(g), _p(p))
     return {k: bufs[k][:n * w].copy() for k, w in (("locations", 3), ("shs", 3 * M), ("scales", 3), ("opacities", 1), ("rotations", 4))}
+
+
+def rtx_render(W, H, cam_location, inv_projview, bg, samples, vertices, triangles, texcoords, tex_rgba, rect=None,
+               orbs=None, frame=None):
+    """oracle_rtx.cpp: one frame of the truth ray tracer (RtxHost::render) on the CPU, brute-force intersection.
+    rect = (x0, y0, x1, y1) limits the work to a pixel rectangle.  Returns (frame uint32[H, W], ray segments)."""
+    L = lib()
+    L.oracle_rtx_render.restype = C.c_ulonglong
+    L.oracle_rtx_render.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
+                                    C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int,
+                                    C.c_int, C.c_void_p, C.c_int]
+    v = _f32(np.asarray(vertices).reshape(-1))
+    t = np.ascontiguousarray(np.asarray(triangles).reshape(-1), dtype=np.int32)
+    nt = t.size // 3
+    tc = _f32(np.zeros(6 * nt) if texcoords is None else np.asarray(texcoords).reshape(-1))
+    tex = np.ascontiguousarray(tex_rgba, dtype=np.uint8)
+    th, tw = tex.shape[:2]
+    if frame is None:
+        frame = np.zeros((H, W), np.uint32)
+    x0, y0, x1, y1 = rect or (0, 0, W, H)
+    o = None if orbs is None else _f32(np.asarray(orbs).reshape(-1))
+    rays = L.oracle_rtx_render(_p(frame), W, H, x0, y0, x1, y1, _p(_f32(cam_location)), _p(_f32(inv_projview)), _p(_f32(bg)),
+                               samples, _p(v), _p(t), nt, _p(tc), _p(tex), tw, th, _p(o), 0 if o is None else o.size // 3)
+    return frame, int(rays)
