@@ -91,16 +91,20 @@ def _fp(a):
 class Project:
     """Project (src/Project.h): numeric members through `.d` (live struct), the three strings as properties."""
 
-    def __init__(self, new=False):
+    def __init__(self, new=False, _borrow=None):
+        object.__setattr__(self, "_owned", _borrow is None)
+        if _borrow is not None:                                 # a handle owned by an App
+            object.__setattr__(self, "_h", C.c_void_p(_borrow))
+            return
         self._h = C.c_void_p()
         check(L().gsb_project_create(C.byref(self._h)))
         if new:
             check(L().gsb_project_init_new(self._h))        # UiFrame::initProject
 
     def __del__(self):
-        if getattr(self, "_h", None):
+        if getattr(self, "_h", None) and getattr(self, "_owned", False):
             L().gsb_project_destroy(self._h)
-            self._h = None
+        object.__setattr__(self, "_h", None)
 
     @property
     def d(self):
@@ -114,7 +118,7 @@ class Project:
         return getattr(self.d, name)
 
     def __setattr__(self, name, value):
-        if name == "_h":
+        if name in ("_h", "_owned"):
             object.__setattr__(self, name, value)
         elif name in ("perspective", "pathModel", "pathTextureDiffuse"):
             check(L().gsb_project_set_string(self._h, name.encode(), value.encode("utf-8")))
@@ -294,14 +298,18 @@ def _LR():
 class RtxHost:
     """RtxHost (src/rtx/RtxHost.h:16-41): reset / loadModel / loadTextureDiffuse / render, plus in-memory setters."""
 
-    def __init__(self):
+    def __init__(self, _borrow=None):
+        self._owned = _borrow is None
+        if _borrow is not None:                                 # a handle owned by an App
+            self._h = C.c_void_p(_borrow)
+            return
         self._h = C.c_void_p()
         check(_LR().gsb_rtx_create(C.byref(self._h)))
 
     def close(self):
-        if getattr(self, "_h", None):
+        if getattr(self, "_h", None) and self._owned:
             _LR().gsb_rtx_destroy(self._h)
-            self._h = None
+        self._h = None
 
     __del__ = close
 
@@ -345,3 +353,124 @@ class RtxHost:
         n = C.c_ulonglong(0)
         check(_LR().gsb_rtx_last_ray_count(self._h, C.byref(n)))
         return n.value
+
+
+# --------------------------------------------------------------------------------------- headless UiFrame (f2, f4)
+APP_SYMBOLS_DRIVER = [
+    "gsb_app_create", "gsb_app_destroy", "gsb_app_project", "gsb_app_rtx", "gsb_app_trainer", "gsb_app_new_project",
+    "gsb_app_init_field", "gsb_app_set_model", "gsb_app_get_model", "gsb_app_model_count", "gsb_app_model_device",
+    "gsb_app_load_input", "gsb_app_random_rotate", "gsb_app_capture_truths", "gsb_app_truth_count", "gsb_app_truth_frames",
+    "gsb_app_set_truths", "gsb_app_train", "gsb_app_set_auto_training", "gsb_app_update", "gsb_app_save_settings",
+    "gsb_app_load_settings", "gsb_app_save_splats", "gsb_app_load_splats", "gsb_app_render_splats",
+    "gsb_app_render_splats_png", "gsb_app_render_rtx_png"]
+_app_bound = False
+
+
+def _LA():
+    global _app_bound
+    lb = _LR()
+    if not _app_bound:
+        vp, i, f, cp = C.c_void_p, C.c_int, C.c_float, C.c_char_p
+        CD, IP = C.POINTER(CameraDesc), C.POINTER(C.c_int)
+        sigs = {
+            "gsb_app_create": ([C.POINTER(vp), i, i], i), "gsb_app_destroy": ([vp], i), "gsb_app_project": ([vp], vp),
+            "gsb_app_rtx": ([vp], vp), "gsb_app_trainer": ([vp], vp), "gsb_app_new_project": ([vp], i),
+            "gsb_app_init_field": ([vp, i], i), "gsb_app_set_model": ([vp, vp], i), "gsb_app_get_model": ([vp, C.POINTER(vp)], i),
+            "gsb_app_model_count": ([vp], i), "gsb_app_model_device": ([vp, IP, IP, IP, IP, C.POINTER(vp)], i),
+            "gsb_app_load_input": ([vp], i), "gsb_app_random_rotate": ([vp], i), "gsb_app_capture_truths": ([vp], i),
+            "gsb_app_truth_count": ([vp], i), "gsb_app_truth_frames": ([vp, i, C.POINTER(vp), C.POINTER(vp), CD], i),
+            "gsb_app_set_truths": ([vp, i, C.POINTER(vp), C.POINTER(vp), CD], i), "gsb_app_train": ([vp, i], i),
+            "gsb_app_set_auto_training": ([vp, i], i), "gsb_app_update": ([vp, f, IP], i),
+            "gsb_app_save_settings": ([vp, cp], i), "gsb_app_load_settings": ([vp, cp], i), "gsb_app_save_splats": ([vp, cp], i),
+            "gsb_app_load_splats": ([vp, cp], i), "gsb_app_render_splats": ([vp, vp, i, i, f, CD], i),
+            "gsb_app_render_splats_png": ([vp, cp], i), "gsb_app_render_rtx_png": ([vp, cp], i),
+        }
+        for name, (args, res) in sigs.items():
+            fn = getattr(lb, name)
+            fn.argtypes, fn.restype = args, res
+        _app_bound = True
+    return lb
+
+
+class App:
+    """The headless UiFrame (src/ui/UiFrame.{h,cpp}): project, trainer + model, rtx, update()."""
+    RAN_TRAINED, RAN_CAPTURED, RAN_DENSIFIED = 1, 2, 4
+
+    def __init__(self, train_width=1024, train_height=1024):
+        self._h = C.c_void_p()
+        check(_LA().gsb_app_create(C.byref(self._h), train_width, train_height))
+        self.size = (train_width, train_height)
+        self.project = Project(_borrow=_LA().gsb_app_project(self._h))
+        self.rtx = RtxHost(_borrow=_LA().gsb_app_rtx(self._h))
+
+    def close(self):
+        if getattr(self, "_h", None):
+            _LA().gsb_app_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    def _call(self, name, *args):
+        check(getattr(_LA(), name)(self._h, *args))
+
+    def new_project(self): self._call("gsb_app_new_project")
+    def initFieldGrid(self): self._call("gsb_app_init_field", 0)
+    def initFieldMono(self): self._call("gsb_app_init_field", 1)
+    def initFieldModel(self): self._call("gsb_app_init_field", 2)
+    def load_input(self): self._call("gsb_app_load_input")
+    def random_rotate(self): self._call("gsb_app_random_rotate")
+    def captureTruths(self): self._call("gsb_app_capture_truths")
+    def train(self, densify=False): self._call("gsb_app_train", int(bool(densify)))
+    def set_auto_training(self, on): self._call("gsb_app_set_auto_training", int(bool(on)))
+    def saveSettings(self, path): self._call("gsb_app_save_settings", str(path).encode())
+    def loadSettings(self, path): self._call("gsb_app_load_settings", str(path).encode())
+    def saveSplats(self, path): self._call("gsb_app_save_splats", str(path).encode())
+    def loadSplats(self, path): self._call("gsb_app_load_splats", str(path).encode())
+    def render_splats_png(self, path): self._call("gsb_app_render_splats_png", str(path).encode())
+    def render_rtx_png(self, path): self._call("gsb_app_render_rtx_png", str(path).encode())
+
+    def update(self, delta_seconds):
+        ran = C.c_int(0)
+        self._call("gsb_app_update", float(delta_seconds), C.byref(ran))
+        return ran.value
+
+    @property
+    def model_count(self):
+        return _LA().gsb_app_model_count(self._h)
+
+    def set_model(self, host):
+        self._call("gsb_app_set_model", host._h)
+
+    def get_model(self):
+        h = C.c_void_p()
+        self._call("gsb_app_get_model", C.byref(h))
+        return ModelSplatsHostC(h)
+
+    def model_device(self):
+        cnt, cap, deg, M = C.c_int(), C.c_int(), C.c_int(), C.c_int()
+        ptrs = (C.c_void_p * 5)()
+        self._call("gsb_app_model_device", C.byref(cnt), C.byref(cap), C.byref(deg), C.byref(M), ptrs)
+        return {"count": cnt.value, "capacity": cap.value, "shDegree": deg.value, "shCoeffs": M.value, "ptrs": list(ptrs)}
+
+    @property
+    def truth_count(self):
+        return _LA().gsb_app_truth_count(self._h)
+
+    def truth_frames(self, index):
+        """(white, black) as torch int32 CUDA tensors (copies) and the camera of truth frame `index`."""
+        from .rasterizer import _view
+        import torch
+        w, b, cam = C.c_void_p(), C.c_void_p(), CameraDesc()
+        self._call("gsb_app_truth_frames", index, C.byref(w), C.byref(b), C.byref(cam))
+        n = self.size[0] * self.size[1]
+        return _view(w.value, (n,), torch.int32, "cuda"), _view(b.value, (n,), torch.int32, "cuda"), cam
+
+    def set_truths(self, whites, blacks, cameras):
+        n = len(whites)
+        aw = (C.c_void_p * n)(*[t.data_ptr() for t in whites])
+        ab = (C.c_void_p * n)(*[t.data_ptr() for t in blacks])
+        cams = (CameraDesc * n)(*cameras)
+        self._call("gsb_app_set_truths", n, aw, ab, cams)
+
+    def render_splats(self, frameBuffer, width, height, splat_scale, camera):
+        self._call("gsb_app_render_splats", C.c_void_p(frameBuffer.data_ptr()), width, height, float(splat_scale), C.byref(camera))

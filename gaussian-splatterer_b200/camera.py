@@ -121,8 +121,10 @@ def fibonacci_sphere(count, distance):
         t = f32(i) / f32(count)
         a1 = f32(math.acos(f32(1.0) - f32(2.0) * t))
         a2 = f32(step * f32(i))
-        out.append(np.array([math.sin(a1) * math.cos(a2) * distance, math.sin(a1) * math.sin(a2) * distance,
-                             math.cos(a1) * distance], dtype=f32))
+        # sinf / cosf results and every product rounded to float32, like the reference's float expressions
+        s1, c1, s2, c2 = f32(math.sin(a1)), f32(math.cos(a1)), f32(math.sin(a2)), f32(math.cos(a2))
+        d = f32(distance)
+        out.append(np.array([f32(s1 * c2) * d, f32(s1 * s2) * d, c1 * d], dtype=f32))
     return out
 
 
@@ -146,14 +148,21 @@ class Camera:
 
     @staticmethod
     def getCameras(project):
-        """Camera::getCameras (src/Camera.cpp:33-58): two Fibonacci spheres with a rotation offset."""
-        out = []
-        for sph in (project.sphere1, project.sphere2):
-            rot = mat_mul(angle_axis_mat(math.radians(sph.rotX), (0, 1, 0)), angle_axis_mat(math.radians(sph.rotY), (1, 0, 0)))
-            for loc in fibonacci_sphere(sph.count, sph.distance):
-                v = rot[0] * loc[0] + rot[1] * loc[1] + rot[2] * loc[2] + rot[3] * f32(1.0)
-                out.append(Camera(v[:3] / v[3], (0.0, 0.0, 0.0), sph.fovDeg))
-        return out
+        """Camera::getCameras (src/Camera.cpp:33-58): two Fibonacci spheres with a rotation offset.
+
+        Delegates to the C++ implementation behind gsb_cameras_get (csrc/app/app_camera.cpp), which runs the reference's
+        float expressions with the same libm calls (acosf / sinf / cosf) and is pinned by tests/golden/cameras.json; a
+        double-precision restatement in Python differs from it by an ulp for some camera counts."""
+        import ctypes as C
+        from . import app
+        d = app.ProjectData()
+        for name in ("sphere1", "sphere2"):
+            src, dst = getattr(project, name), getattr(d, name)
+            dst.count, dst.distance, dst.fovDeg, dst.rotX, dst.rotY = src.count, src.distance, src.fovDeg, src.rotX, src.rotY
+        n = app.L().gsb_cameras_count(C.byref(d))
+        arr = (app.CameraDesc * max(n, 1))()
+        app.check(app.L().gsb_cameras_get(C.byref(d), arr, n))
+        return [Camera(np.array(arr[k].location[:], dtype=f32), (0.0, 0.0, 0.0), arr[k].fovDegY) for k in range(n)]
 
     def view_constants(self, width, height, square_fov=False):
         """What Trainer hands to the rasterizer for this camera at width x height.

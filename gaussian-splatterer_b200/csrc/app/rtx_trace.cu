@@ -172,7 +172,7 @@ __global__ void __launch_bounds__(128) rtx_trace_kernel(const RtxParams p) {
             float tmin = 0.f, tmax = 1e30f;                            // owl::Ray defaults, owl_device.h:147
             // ---- tracePath, RD:17-50
             V3 atten = mk(1.f, 1.f, 1.f);
-            bool has_reflected = false, finished = false;
+            bool has_reflected = false;
             for (int i = 0; i < 50; i++) {
                 Hit h;
                 const bool hit = closest_hit(p, origin, dir, tmin, tmax, h);
@@ -230,12 +230,11 @@ __global__ void __launch_bounds__(128) rtx_trace_kernel(const RtxParams p) {
                     const V3 out1 = has_reflected ? atten : mk(p.bg1[0], p.bg1[1], p.bg1[2]);
                     color0 = color0 + clamp01(out0 * 1.0f);             // PROGRAM_EXPOSURE_FACTOR 1
                     color1 = color1 + clamp01(out1 * 1.0f);
-                    finished = true;
                     break;
                 }
                 origin = hit_origin; dir = bounce; tmin = 1e-3f; tmax = 1e10f;
             }
-            (void)finished;                                             // 50 segments exceeded: the sample adds (0,0,0), RD:49
+            // 50 segments exceeded: the sample adds (0,0,0), RD:49
         }
         const float ns = (float)p.samples;
         V3 c0 = mk(color0.x / ns, color0.y / ns, color0.z / ns), c1 = mk(color1.x / ns, color1.y / ns, color1.z / ns);

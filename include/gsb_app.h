@@ -146,6 +146,52 @@ int gsb_rtx_render_pair(gsb_rtx* r, uint32_t* dev_frame_white, uint32_t* dev_fra
 /* rays traced (primary + bounce segments) by the last render call, for the Mray/s figure */
 int gsb_rtx_last_ray_count(gsb_rtx* r, unsigned long long* out);
 
+/* ------------------------------------------------------------- headless UiFrame: the training driver */
+/* The application object without its windows: one Project, one Trainer (with its ModelSplatsDevice), one RtxHost, and
+ * the idle-loop scheduler of UiFrame::update (UF:266-298).  The training resolution is RENDER_RESOLUTION_X/Y of
+ * src/Config.h:13-14 in the reference (1024 x 1024); here it is a constructor argument. */
+typedef struct gsb_app gsb_app;
+
+int gsb_app_create(gsb_app** out, int train_width, int train_height);   /* UiFrame ctor: initProject + initFieldGrid (UF:126-160) */
+int gsb_app_destroy(gsb_app* a);
+gsb_project* gsb_app_project(gsb_app* a);
+gsb_rtx* gsb_app_rtx(gsb_app* a);
+gsb_trainer* gsb_app_trainer(gsb_app* a);
+int gsb_app_new_project(gsb_app* a);                             /* FILE_NEW_PROJECT: initProject, initFieldGrid, rtx reset (UF:452-458,300-301) */
+int gsb_app_init_field(gsb_app* a, int kind);                    /* 0 grid, 1 mono, 2 from project.pathModel; iterations = 0 (UF:137-264) */
+int gsb_app_set_model(gsb_app* a, gsb_model_host* m);            /* delete trainer->model; model = new ModelSplatsDevice(host) (UF:157-158) */
+int gsb_app_get_model(gsb_app* a, gsb_model_host** out);         /* ModelSplatsHost(*trainer->model) (MH:17-29) */
+int gsb_app_model_count(gsb_app* a);
+/* the five device arrays of trainer->model (src/ModelSplatsDevice.h:15-19) for callers that render or inspect them */
+int gsb_app_model_device(gsb_app* a, int* count, int* capacity, int* shDegree, int* shCoeffs, float** dev5);
+int gsb_app_load_input(gsb_app* a);                              /* rtx.loadModel(project.pathModel) + loadTextureDiffuse(project.pathTextureDiffuse) */
+int gsb_app_random_rotate(gsb_app* a);                           /* UiPanelToolsTruth::onButtonRandomRotate: four rand() / RAND_MAX * 360 */
+int gsb_app_capture_truths(gsb_app* a);                          /* Trainer::captureTruths (src/Trainer.cu:218-250) through the ray caster */
+int gsb_app_truth_count(gsb_app* a);
+int gsb_app_truth_frames(gsb_app* a, int index, uint32_t** dev_white, uint32_t** dev_black, gsb_camera_desc* camera);
+/* Caller-supplied truth frames instead of the ray caster (device RGBA8 at the training resolution, copied). */
+int gsb_app_set_truths(gsb_app* a, int n, const uint32_t* const* dev_white, const uint32_t* const* dev_black,
+                       const gsb_camera_desc* cameras);
+int gsb_app_train(gsb_app* a, int densify);                      /* Trainer::train(project, densify), the manual buttons (UiPanelToolsTrain.cpp:166-169) */
+int gsb_app_set_auto_training(gsb_app* a, int on);               /* autoTraining flag (UF(h)) ; budget restarts at 0 */
+/* UiFrame::update with `delta_seconds` in place of the wall clock: previewTimer += delta; if auto-training, the budget
+ * grows by delta * AUTO_TRAIN_BUDGET (100 / s) capped at 1, and a full budget buys one iteration: capture (random
+ * rotation + captureTruths) when iterations % intervalCapture == 0, densify when iterations % intervalDensify == 0,
+ * then Trainer::train.  *ran (optional): 0 none, 1 trained, |2 captured, |4 densified. */
+int gsb_app_update(gsb_app* a, float delta_seconds, int* ran);
+int gsb_app_save_settings(gsb_app* a, const char* path);         /* UF:323-331 */
+int gsb_app_load_settings(gsb_app* a, const char* path);         /* UF:358-370 */
+int gsb_app_save_splats(gsb_app* a, const char* path);           /* UF:333-356 */
+int gsb_app_load_splats(gsb_app* a, const char* path);           /* UF:372-450 */
+/* Trainer::render at (width, height) from `camera` -> RGBA8 in caller device memory (the preview panel's frame buffer,
+ * src/ui/UiPanelViewOutput.cpp:47-55; the GL blit of FboRenderer is unavailable on this box). */
+int gsb_app_render_splats(gsb_app* a, uint32_t* dev_frame_buffer, int width, int height, float splat_scale,
+                          const gsb_camera_desc* camera);
+/* onButtonRenderSplats / onButtonRenderRtx (TV:227-259): project.renderResX x renderResY from Camera::getPreviewCamera,
+ * previewSplatScale / rtSamples, written as a vertically flipped PNG. */
+int gsb_app_render_splats_png(gsb_app* a, const char* path);
+int gsb_app_render_rtx_png(gsb_app* a, const char* path);
+
 #ifdef __cplusplus
 }
 #endif
