@@ -221,6 +221,56 @@ def bwd_flops(pc):
 
 
 # ---------------------------------------------------------------------------------------------
+def measure_render_mpix(torch, render_one, cams, W, Hh, reps=3):
+    """BASELINE.json's second metric: Mpix/s of the Trainer::render path (forward + float -> RGBA8, src/Trainer.cu:148-216)
+    over the local cameras.  render_one(cam) must leave the frame in device memory; CUDA events around reps x cameras."""
+    for cam in cams[:2]:
+        render_one(cam)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        for cam in cams:
+            render_one(cam)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    frames = reps * len(cams)
+    return {"mpix_per_s": W * Hh * frames / (ms * 1e-3) / 1e6, "ms_per_frame": ms / frames, "frames": frames,
+            "resolution": [W, Hh]}
+
+
+def measure_truth_tracer(torch, gsb, dev, cams, size=1024, samples=100):
+    """captureTruths through the CUDA ray caster: one white+black frame pair per camera at the
+    reference's truth resolution and rtSamples default (src/Config.h:13-14, src/Project.h:24), procedural textured mesh."""
+    import importlib
+    app = importlib.import_module("gaussian-splatterer_b200.app")
+    rtx = app.RtxHost()
+    v, t, tc = gsb.synth.textured_mesh(rings=96, segments=192, seed=3)
+    rtx.set_mesh(v, t, tc)
+    rtx.set_texture(gsb.synth.procedural_texture(256, 5))
+    w = torch.zeros(size * size, dtype=torch.int32, device=dev)
+    b = torch.zeros(size * size, dtype=torch.int32, device=dev)
+    descs = [app.camera_desc(c.location, (0.0, 0.0, 0.0), c.fovDegY) for c in cams]
+    rtx.render_pair(w, b, (size, size), descs[0], 4)                      # warm-up
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    rays = 0
+    e0.record()
+    for d in descs:
+        rtx.render_pair(w, b, (size, size), d, samples)
+        rays += rtx.last_ray_count()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    rtx.close()
+    return {"mray_per_s": rays / (ms * 1e-3) / 1e6, "ms_per_camera_pair": ms / len(descs), "cameras": len(descs),
+            "triangles": int(t.shape[0]), "resolution": [size, size], "samples": samples,
+            "ray_segments_per_pixel_sample": rays / (len(descs) * size * size * samples),
+            "note": "white and black truth frame of a camera come from one trace (gsb_rtx_render_pair); the reference's "
+                    "OptiX/OWL tracer is unavailable on this box, so there is no reference number beside this one"}
+
+
+# ---------------------------------------------------------------------------------------------
 def cpu_baseline_port(gsb, scene, truth_white0):
     """One view pass (forward + loss + backward + accumulate) of the same workload on the scalar C++
     oracle, one host thread.  Context only."""
@@ -346,6 +396,14 @@ def run_gsb(args):
                       "frames on a copy stream overlaps the current step; per rank"}
         tr.close()
 
+    render_stats = truth_stats = None
+    if rank == 0 and world == 1 and not args.no_e2e:
+        tr = new_trainer()
+        fb = torch.empty(W * Hh, dtype=torch.int32, device=dev)
+        render_stats = measure_render_mpix(torch, lambda cam: tr.render(fb, W, Hh, 1.0, cam), mine[:16], W, Hh)
+        tr.close()
+        truth_stats = measure_truth_tracer(torch, gsb, dev, mine[:4])
+
     if rank != 0:
         return
     peaks = {}
@@ -411,6 +469,9 @@ def run_gsb(args):
     }
     if e2e is not None:
         out["e2e"] = e2e
+    if render_stats is not None:
+        out["render"] = render_stats              # "render Mpix/s" of BASELINE.json's metric, Trainer::render path
+        out["truth_tracer"] = truth_stats
     if world == 1 and not args.no_cpu_baseline:
         out["cpu_baseline"] = cpu_baseline_port(gsb, scene, tw[0].cpu().numpy().view(np.uint32))
     emit(out)
@@ -462,6 +523,17 @@ def run_reference(args):
             clocks = sampler.stop()
         res[name] = {"views_per_s": views_per_step * args.steps / (ms / 1000.0), "ms_per_step": ms / args.steps}
     rt.close()
+    # render Mpix/s of the reference's Trainer::render (src/Trainer.cu:148-216): forward(debug=true) + imageFloatToInt + sync
+    sc_r = H.scene_tensors(cloud, dev)
+    fb_r = torch.empty(W * Hh, dtype=torch.int32, device=dev)
+
+    def ref_render(cam):
+        vw = H.view_tensors(cam.view_constants(W, Hh, square_fov=False), (0.0, 0.0, 0.0), dev)
+        out_c, _ = H.run_forward_ref(sc_r, vw, P, 1, 4, W, Hh, debug=True)
+        refshim.image_float_to_int(out_c, fb_r, W, Hh)
+        torch.cuda.synchronize()
+    render_stats = measure_render_mpix(torch, ref_render, scene["cams"][:16], W, Hh)
+    render_stats["variant"] = "forward(debug=true) + imageFloatToInt + cudaDeviceSynchronize as in Trainer::render, but with pooled workspaces (no per-call cudaMalloc/cudaFree): favourable to the reference"
     best = res["best_case"]
     out = {
         "impl": "reference", "metric": METRIC, "value": best["views_per_s"], "unit": UNIT, "n_gpus": 1,
@@ -474,6 +546,7 @@ def run_reference(args):
                               "the as-shipped call sequence (debug=true, per-view malloc/free) is in `as_shipped`",
                    "l2": "inputs larger than L2"},
         "as_shipped": res["as_shipped"],
+        "render": render_stats,
         "clocks": clocks,
         "cpu_baseline": {"value": best["views_per_s"], "unit": UNIT, "cores": 1, "kind": "reference",
                          "sample": "the reference has no CPU implementation of this path; this is its own CUDA code "

@@ -155,86 +155,98 @@ __global__ void __launch_bounds__(128) rtx_trace_kernel(const RtxParams p) {
         V3 color0 = mk(0.f, 0.f, 0.f), color1 = mk(0.f, 0.f, 0.f);
         bool touches_orb = false;
         const V3 cam = mk(p.cam[0], p.cam[1], p.cam[2]);
-        for (int s = 0; s < p.samples; s++) {
-            // ---- ray generation, RD:63-77
-            const float r0 = random(), r1 = random();
-            const float fx = ((float)px + r0) + 0.5f, fy = ((float)py + r1) + 0.5f;
-            const float vx = (float)(((double)fx * 2.0 / (double)p.W) - 1.0);
-            const float vy = (float)(((double)fy * 2.0 / (double)p.H) - 1.0);
-            const float vz = 1.0f;
-            const float* M = p.M;
-            const float hx = vx * M[0] + vy * M[4] + vz * M[8] + M[12];
-            const float hy = vx * M[1] + vy * M[5] + vz * M[9] + M[13];
-            const float hz = vx * M[2] + vy * M[6] + vz * M[10] + M[14];
-            const float hw = vx * M[3] + vy * M[7] + vz * M[11] + M[15];
-            V3 origin = cam;
-            V3 dir = normalize(mk(hx / hw, hy / hw, hz / hw) - cam);
-            float tmin = 0.f, tmax = 1e30f;                            // owl::Ray defaults, owl_device.h:147
-            // ---- tracePath, RD:17-50
-            V3 atten = mk(1.f, 1.f, 1.f);
-            bool has_reflected = false;
-            for (int i = 0; i < 50; i++) {
-                Hit h;
-                const bool hit = closest_hit(p, origin, dir, tmin, tmax, h);
-                rays++;
-                V3 prd_color, hit_origin = mk(0.f, 0.f, 0.f), bounce = mk(0.f, 0.f, 0.f);
-                bool reflected = false;
-                if (hit) {                                              // closest hit program, RD:102-143
-                    const float2 tc0 = __ldg(&p.texcoords[3 * h.prim]), tc1 = __ldg(&p.texcoords[3 * h.prim + 1]), tc2 = __ldg(&p.texcoords[3 * h.prim + 2]);
-                    const float4 q1 = __ldg(&p.tris[3 * h.slot + 1]), q2 = __ldg(&p.tris[3 * h.slot + 2]);
-                    const V3 normal = normalize(cross(mk(q1.x, q1.y, q1.z), mk(q2.x, q2.y, q2.z)));     // RD:112-113
-                    const float w0 = 1.0f - h.u - h.v;
-                    const float tcx = w0 * tc0.x + h.u * tc1.x + h.v * tc2.x;
-                    const float tcy = w0 * tc0.y + h.u * tc1.y + h.v * tc2.y;
-                    const float su = tcx, sv = 1.0f - tcy;
-                    const float fu = su - floorf(su), fv = sv - floorf(sv);
-                    const int ix = min((int)floorf(fu * (float)p.texW), p.texW - 1), iy = min((int)floorf(fv * (float)p.texH), p.texH - 1);
-                    const uchar4 tx = __ldg(&p.tex[iy * p.texW + ix]);
-                    const float cr = (float)tx.x / 255.f, cg = (float)tx.y / 255.f, cb = (float)tx.z / 255.f, ca = (float)tx.w / 255.f;
-                    hit_origin = origin + h.t * dir;
-                    if (ca > random()) {
-                        V3 refl = dir - 2.0f * dot(dir, normal) * normal;
-                        if (random() > 0.0f) {                          // MATERIAL_REFLECTIVITY 0, RD(h):14
-                            V3 v;
-                            do {
-                                const float a = random(), b = random(), c = random();
-                                v = 2.0f * mk(a, b, c) - mk(1.0f, 1.0f, 1.0f);
-                            } while (dot(v, v) >= 1.0f);
-                            refl = normal + v;
-                        }
-                        bounce = refl;
-                        prd_color = mk(cr, cg, cb);
-                        reflected = true;
-                    } else {
-                        bounce = dir;
-                        prd_color = mk(1.f, 1.f, 1.f);
+        // The reference's two nested loops (samples, RD:60; path segments, RD:23) run here as ONE loop over path segments: a
+        // lane that finishes a sample early starts its next one at once instead of idling until the longest path of its
+        // warp ends.  Per pixel the sequence of operations and random draws is unchanged.
+        V3 origin = cam, dir = cam, atten = mk(1.f, 1.f, 1.f);
+        float tmin = 0.f, tmax = 1e30f;
+        bool has_reflected = false;
+        int s = 0, i = 0;
+        bool fresh = true;
+        while (true) {
+            if (fresh) {
+                if (s == p.samples) break;
+                // ---- ray generation, RD:63-77
+                const float r0 = random(), r1 = random();
+                const float fx = ((float)px + r0) + 0.5f, fy = ((float)py + r1) + 0.5f;
+                const float vx = (float)(((double)fx * 2.0 / (double)p.W) - 1.0);
+                const float vy = (float)(((double)fy * 2.0 / (double)p.H) - 1.0);
+                const float vz = 1.0f;
+                const float* M = p.M;
+                const float hx = vx * M[0] + vy * M[4] + vz * M[8] + M[12];
+                const float hy = vx * M[1] + vy * M[5] + vz * M[9] + M[13];
+                const float hz = vx * M[2] + vy * M[6] + vz * M[10] + M[14];
+                const float hw = vx * M[3] + vy * M[7] + vz * M[11] + M[15];
+                origin = cam;
+                dir = normalize(mk(hx / hw, hy / hw, hz / hw) - cam);
+                tmin = 0.f; tmax = 1e30f;                                // owl::Ray defaults, owl_device.h:147
+                atten = mk(1.f, 1.f, 1.f);                               // tracePath, RD:17-21
+                has_reflected = false;
+                i = 0;
+                fresh = false;
+            }
+            Hit h;
+            const bool hit = closest_hit(p, origin, dir, tmin, tmax, h);
+            rays++;
+            V3 prd_color, hit_origin = mk(0.f, 0.f, 0.f), bounce = mk(0.f, 0.f, 0.f);
+            bool reflected = false;
+            if (hit) {                                                  // closest hit program, RD:102-143
+                const float2 tc0 = __ldg(&p.texcoords[3 * h.prim]), tc1 = __ldg(&p.texcoords[3 * h.prim + 1]), tc2 = __ldg(&p.texcoords[3 * h.prim + 2]);
+                const float4 q1 = __ldg(&p.tris[3 * h.slot + 1]), q2 = __ldg(&p.tris[3 * h.slot + 2]);
+                const V3 normal = normalize(cross(mk(q1.x, q1.y, q1.z), mk(q2.x, q2.y, q2.z)));     // RD:112-113
+                const float w0 = 1.0f - h.u - h.v;
+                const float tcx = w0 * tc0.x + h.u * tc1.x + h.v * tc2.x;
+                const float tcy = w0 * tc0.y + h.u * tc1.y + h.v * tc2.y;
+                const float su = tcx, sv = 1.0f - tcy;
+                const float fu = su - floorf(su), fv = sv - floorf(sv);
+                const int ix = min((int)floorf(fu * (float)p.texW), p.texW - 1), iy = min((int)floorf(fv * (float)p.texH), p.texH - 1);
+                const uchar4 tx = __ldg(&p.tex[iy * p.texW + ix]);
+                const float cr = (float)tx.x / 255.f, cg = (float)tx.y / 255.f, cb = (float)tx.z / 255.f, ca = (float)tx.w / 255.f;
+                hit_origin = origin + h.t * dir;
+                if (ca > random()) {
+                    V3 refl = dir - 2.0f * dot(dir, normal) * normal;
+                    if (random() > 0.0f) {                              // MATERIAL_REFLECTIVITY 0, RD(h):14
+                        V3 v;
+                        do {
+                            const float a = random(), b = random(), c = random();
+                            v = 2.0f * mk(a, b, c) - mk(1.0f, 1.0f, 1.0f);
+                        } while (dot(v, v) >= 1.0f);
+                        refl = normal + v;
                     }
-                } else {                                                // miss program, RD:146-157
-                    const V3 n = normalize(dir);
-                    const float sky = fminf(1.0f, 1.0f + n.y);
-                    prd_color = mk(sky, sky, sky);
+                    bounce = refl;
+                    prd_color = mk(cr, cg, cb);
+                    reflected = true;
+                } else {
+                    bounce = dir;
+                    prd_color = mk(1.f, 1.f, 1.f);
                 }
-                atten = atten * prd_color;
-                if (reflected) has_reflected = true;
-                if (i == 0) {                                           // camera indicator orbs, RD:33-47
-                    for (int c = 0; c < p.n_orbs; c++) {
-                        const V3 orb = mk(p.orbs[3 * c], p.orbs[3 * c + 1], p.orbs[3 * c + 2]);
-                        if (hit && dot(dir, orb - origin) > dot(dir, hit_origin - origin)) continue;
-                        const V3 closest = origin + dir * dot(dir, orb - origin);
-                        const V3 delta = orb - closest;
-                        if (dot(delta, delta) < 0.025f * 0.025f) { touches_orb = true; break; }
-                    }
+            } else {                                                    // miss program, RD:146-157
+                const V3 n = normalize(dir);
+                const float sky = fminf(1.0f, 1.0f + n.y);
+                prd_color = mk(sky, sky, sky);
+            }
+            atten = atten * prd_color;
+            if (reflected) has_reflected = true;
+            if (i == 0) {                                               // camera indicator orbs, RD:33-47
+                for (int c = 0; c < p.n_orbs; c++) {
+                    const V3 orb = mk(p.orbs[3 * c], p.orbs[3 * c + 1], p.orbs[3 * c + 2]);
+                    if (hit && dot(dir, orb - origin) > dot(dir, hit_origin - origin)) continue;
+                    const V3 closest = origin + dir * dot(dir, orb - origin);
+                    const V3 delta = orb - closest;
+                    if (dot(delta, delta) < 0.025f * 0.025f) { touches_orb = true; break; }
                 }
-                if (!hit) {
-                    const V3 out0 = has_reflected ? atten : mk(p.bg0[0], p.bg0[1], p.bg0[2]);
-                    const V3 out1 = has_reflected ? atten : mk(p.bg1[0], p.bg1[1], p.bg1[2]);
-                    color0 = color0 + clamp01(out0 * 1.0f);             // PROGRAM_EXPOSURE_FACTOR 1
-                    color1 = color1 + clamp01(out1 * 1.0f);
-                    break;
-                }
+            }
+            if (!hit) {
+                const V3 out0 = has_reflected ? atten : mk(p.bg0[0], p.bg0[1], p.bg0[2]);
+                const V3 out1 = has_reflected ? atten : mk(p.bg1[0], p.bg1[1], p.bg1[2]);
+                color0 = color0 + clamp01(out0 * 1.0f);                 // PROGRAM_EXPOSURE_FACTOR 1
+                color1 = color1 + clamp01(out1 * 1.0f);
+                s++; fresh = true;
+            } else if (++i == 50) {
+                s++; fresh = true;                                      // 50 segments exceeded: the sample adds (0,0,0), RD:49
+            } else {
                 origin = hit_origin; dir = bounce; tmin = 1e-3f; tmax = 1e10f;
             }
-            // 50 segments exceeded: the sample adds (0,0,0), RD:49
         }
         const float ns = (float)p.samples;
         V3 c0 = mk(color0.x / ns, color0.y / ns, color0.z / ns), c1 = mk(color1.x / ns, color1.y / ns, color1.z / ns);
