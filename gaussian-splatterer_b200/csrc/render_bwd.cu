@@ -44,7 +44,7 @@ struct BwdSmem {
 // MODE 0: dL/dpixel given (Rasterizer::backward).  MODE 1: residual of one truth frame fused.
 // MODE 2: white and black truth frames of one camera fused (two residuals, two GradRec sets).
 template <int MODE>
-__global__ void __launch_bounds__(RENDER_THREADS, MODE == 2 ? 5 : 6) render_bwd_kernel(const RenderBwdArgs a) {
+__global__ void __launch_bounds__(RENDER_THREADS, 6) render_bwd_kernel(const RenderBwdArgs a) {
     constexpr int NS = (MODE == 2) ? 2 : 1;   // residual sets
     __shared__ BwdSmem sm;
     __shared__ __align__(16) float s_red[RENDER_WARPS][9 * NS * RED_STRIDE];
