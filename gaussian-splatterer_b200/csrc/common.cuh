@@ -28,6 +28,12 @@ struct __align__(16) GradRec {
     float4 c;   // dL/db, unused x3
 };
 
+// Fused white+black camera pass (Trainer): the same nine sums of both passes, interleaved as (white, black) pairs
+// so the render backward adds a pair with one 64-bit RED; v[r] follows the float order of GradRec (r < 9).
+struct __align__(16) GradRec2 {
+    float2 v[12];   // v[0..5] = H0, Hx, Hy, Hxx, Hxy, Hyy; v[6..8] = dL/dr, dL/dg, dL/db; v[9..11] unused
+};
+
 // Device-resident control block, cleared by one memset per view.
 struct GsbCtrl {
     uint32_t num_rendered;          // R: total duplicates (device copy; host copy is optional)
@@ -147,9 +153,9 @@ struct RenderBwdArgs {
     const float* rendered;          //   the forward's out_color (dL = truth/255 - rendered)
     GradRec* grads;                 // [P], accumulated with red.global.add
     // dual mode (non-null truth2): `truth` is the white-background frame, `truth2` the black one,
-    // `rendered` the black-background image; the black pass accumulates into grads2
+    // `rendered` the black-background image; both passes accumulate into grads2 (grads is not touched)
     const uint32_t* truth2;
-    GradRec* grads2;
+    GradRec2* grads2;
     double* loss_out;               // optional: += sum of squared residuals (fused-loss modes only)
 };
 void launch_render_bwd(const RenderBwdArgs& a, cudaStream_t s);
@@ -177,7 +183,7 @@ struct PreprocessBwdArgs {
     const int* radii;
     const uint8_t* clamped;
     GradRec* grads;                 // consumed and cleared
-    GradRec* grads2;                // Trainer mode only: second set (black pass of a fused camera pass), or null
+    GradRec2* grads2;               // Trainer mode only: both passes of a fused camera pass (replaces grads), or null
     const SplatRec* recs;           // the forward's records (conic, opacity)
     int W, H;
     // mode A (Rasterizer::backward): caller arrays, reference semantics

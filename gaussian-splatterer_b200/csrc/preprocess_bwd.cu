@@ -99,7 +99,7 @@ __device__ __forceinline__ V3 dir_grad(const ShDirs& q, V3 dRGB) {
 }
 
 // NS = number of GradRec sets consumed in one pass over the splat: 1 everywhere except the Trainer's
-// fused white+black camera pass (NS = 2: a.grads = white pass, a.grads2 = black pass).  Every gradient
+// fused white+black camera pass (NS = 2: a.grads2 holds the (white, black) pairs of both passes, GradRec2).  Every gradient
 // is linear in a set's moments, so the per-splat geometry (T = W J, Vrk T, the conic Jacobian, the
 // projection Jacobian, the SH direction derivatives) is computed once; only dL/dmean3D is finished
 // per set, because varLocations sums the per-pass norms (src/Trainer.cu:52-54).
@@ -148,20 +148,36 @@ __global__ void __launch_bounds__(GSB_PB_THREADS, GSB_PB_BLOCKS) preprocess_bwd_
     {
         const SplatRec& r = a.recs[idx];
         const float conx = r.a.z, cony = r.a.w, conz = r.b.x, opac = r.b.y;
+        float H[NS][9];
+        const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+        if constexpr (NS == 2) {
+            // fused camera pass: (white, black) pairs of the nine sums in one GradRec2; take and clear
+            float4* gp = reinterpret_cast<float4*>(a.grads2 + idx);
+            float4 q[5];
+#pragma unroll
+            for (int i = 0; i < 5; i++) { q[i] = gp[i]; gp[i] = z; }
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                H[0][2 * i] = q[i].x; H[1][2 * i] = q[i].y; H[0][2 * i + 1] = q[i].z; H[1][2 * i + 1] = q[i].w;
+            }
+            H[0][8] = q[4].x; H[1][8] = q[4].y;
+        } else {
+            GradRec* gp = a.grads + idx;
+            const GradRec g = *gp;
+            gp->a = z; gp->b = z; gp->c = z;                      // take and clear the per-view scratch
+            H[0][0] = g.a.x; H[0][1] = g.a.y; H[0][2] = g.a.z; H[0][3] = g.a.w; H[0][4] = g.b.x; H[0][5] = g.b.y;
+            H[0][6] = g.b.z; H[0][7] = g.b.w; H[0][8] = g.c.x;
+        }
 #pragma unroll
         for (int s = 0; s < NS; s++) {
-            GradRec* gp = (s == 0 ? a.grads : a.grads2) + idx;
-            const GradRec g = *gp;
-            const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
-            gp->a = z; gp->b = z; gp->c = z;                      // take and clear the per-view scratch
-            const float H0 = g.a.x, Hx = g.a.y, Hy = g.a.z, Hxx = g.a.w, Hxy = g.b.x, Hyy = g.b.y;
+            const float H0 = H[s][0], Hx = H[s][1], Hy = H[s][2], Hxx = H[s][3], Hxy = H[s][4], Hyy = H[s][5];
             gop[s] = H0;
             gm2x[s] = -(0.5f * a.W) * opac * (conx * Hx + cony * Hy);
             gm2y[s] = -(0.5f * a.H) * opac * (conz * Hy + cony * Hx);
             gcx[s] = -0.5f * opac * Hxx;
             gcy[s] = -0.5f * opac * Hxy;
             gcw[s] = -0.5f * opac * Hyy;
-            gcol[s] = {g.b.z, g.b.w, g.c.x};
+            gcol[s] = {H[s][6], H[s][7], H[s][8]};
         }
     }
     if (modeA) {

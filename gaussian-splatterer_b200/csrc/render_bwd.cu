@@ -32,7 +32,62 @@
 
 namespace {
 
+#ifndef GSB_BWD_CTAS
+#define GSB_BWD_CTAS 8   // resident CTAs per SM the register budget is cut for (64 registers)
+#endif
+
 constexpr int RED_STRIDE = 36;   // floats per row of the reduction panel: 32 lanes + 4 pad (rows stay 16-byte aligned)
+constexpr int RED_STRIDE2 = 34;  // dual mode: float2 (white, black) per lane, 32 lanes + 2 pad; 34 / 2 odd keeps the
+                                 // readers' 128-bit loads of different rows on different bank groups
+
+// Packed FP32 pairs (sm_100 FFMA2 / FMUL2 / FADD2): one issue slot for two IEEE round-to-nearest operations.  The
+// dual mode keeps every per-residual quantity as a (white, black) pair, so its arithmetic issues half the
+// instructions; a scalar operand is broadcast by the instruction itself (R.F32 operand form), not by a move.
+__device__ __forceinline__ unsigned long long pk(float2 v) {
+    unsigned long long r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(v.x), "f"(v.y));
+    return r;
+}
+__device__ __forceinline__ float2 upk(unsigned long long v) {
+    float2 r;
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(r.x), "=f"(r.y) : "l"(v));
+    return r;
+}
+__device__ __forceinline__ float2 fma2(float2 a, float2 b, float2 c) {
+    unsigned long long r;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(pk(a)), "l"(pk(b)), "l"(pk(c)));
+    return upk(r);
+}
+__device__ __forceinline__ float2 mul2(float2 a, float2 b) {
+    unsigned long long r;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(pk(a)), "l"(pk(b)));
+    return upk(r);
+}
+__device__ __forceinline__ float2 add2(float2 a, float2 b) {
+    unsigned long long r;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(pk(a)), "l"(pk(b)));
+    return upk(r);
+}
+__device__ __forceinline__ float2 dup2(float v) { return make_float2(v, v); }
+// shared-memory accesses through a 32-bit address computed once (kept opaque so it is not re-derived per entry)
+__device__ __forceinline__ void sts64(uint32_t addr, float2 v) {
+    asm volatile("st.shared.v2.f32 [%0], {%1, %2};" ::"r"(addr), "f"(v.x), "f"(v.y) : "memory");
+}
+__device__ __forceinline__ float4 lds128(uint32_t addr) {
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr) : "memory");
+    return v;
+}
+// one RED for a (white, black) pair: REDG.E.ADD.F32x2
+__device__ __forceinline__ void red_add2(float* p, float2 v) {
+    asm volatile("red.global.v2.f32.add [%0], {%1, %2};" ::"l"(p), "f"(v.x), "f"(v.y) : "memory");
+}
+// 1 / x for x in [0.01, 1]: the bare MUFU.RCP (no denormal guard needed in that range)
+__device__ __forceinline__ float rcp_fast(float x) {
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
 
 constexpr int WB = 32;           // list entries per warp-private chunk (one per lane)
 
@@ -44,13 +99,22 @@ struct BwdSmem {
 // MODE 0: dL/dpixel given (Rasterizer::backward).  MODE 1: residual of one truth frame fused.
 // MODE 2: white and black truth frames of one camera fused (two residuals, two GradRec sets).
 template <int MODE>
-__global__ void __launch_bounds__(RENDER_THREADS, 6) render_bwd_kernel(const RenderBwdArgs a) {
+__global__ void __launch_bounds__(RENDER_THREADS, GSB_BWD_CTAS) render_bwd_kernel(const RenderBwdArgs a) {
     constexpr int NS = (MODE == 2) ? 2 : 1;   // residual sets
     __shared__ BwdSmem sm;
-    __shared__ __align__(16) float s_red[RENDER_WARPS][9 * NS * RED_STRIDE];
+    // reduction panel of a warp: NS == 1: [9][RED_STRIDE] floats; NS == 2: [9][RED_STRIDE2] (white, black) pairs
+    __shared__ __align__(16) float s_red[RENDER_WARPS][NS == 2 ? 9 * 2 * RED_STRIDE2 : 9 * RED_STRIDE];
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     float* const red = s_red[warp];
+    // dual mode: lanes r and r + 9 (r < 9) each sum one half of row r of the panel and feed pair r of the splat's
+    // GradRec2; the addresses are computed once and kept opaque so they are not re-derived per entry
+    int role = lane < 9 ? 0 : (lane < 18 ? 1 : 2);          // reader of the first / second half row, or none
+    const int rrow = role == 1 ? lane - 9 : lane;
+    uint32_t col_addr = (uint32_t)__cvta_generic_to_shared(red) + lane * 8;
+    uint32_t row_addr = (uint32_t)__cvta_generic_to_shared(red) + (rrow * RED_STRIDE2 + (role == 1 ? 16 : 0)) * 8;
+    float* gbase = reinterpret_cast<float*>(a.grads2) + rrow * 2;
+    if (NS == 2) asm volatile("" : "+r"(col_addr), "+r"(row_addr), "+l"(gbase), "+r"(role));
     const int tile = blockIdx.y * a.grid_x + blockIdx.x;
     const int start = (int)a.tile_max[tile];       // entries at or beyond this index were blended by no pixel
     if (start == 0 && (MODE == 0 || a.loss_out == nullptr)) return;
@@ -63,9 +127,12 @@ __global__ void __launch_bounds__(RENDER_THREADS, 6) render_bwd_kernel(const Ren
     const float bcx = (float)bx0 + 3.5f, bcy = (float)by0 + 3.5f;
     const size_t plane = (size_t)a.W * a.H;
 
-    float pyf[2], T[2], Tfin[2], last_alpha[2];
-    float lcr[2], lcg[2], lcb[2], arr[2], arg[2], arb[2];
-    float dLr[NS][2], dLg[NS][2], dLb[NS][2], bgdot[2];   // bgdot: set 0 only (set 1 is the black pass)
+    // SD[s][k] = dL_s . (un-normalised colour of everything behind the current entry, background included):
+    // the reference's T_i (c_i - accum_rec_i) . dL - T_final / (1 - alpha_i) bg . dL (backward.cu:489-508) is
+    // T_i (c_i . dL) - SD_i / (1 - alpha_i), and SD_{i-1} = SD_i + alpha_i T_i (c_i . dL) needs one FMA per set
+    // where the normalised colour behind needs a three-channel recurrence.
+    float pyf[2], T[2], SD[NS][2];
+    float dLr[NS][2], dLg[NS][2], dLb[NS][2];
     int ncontrib[2];
 #pragma unroll
     for (int k = 0; k < 2; k++) {
@@ -73,41 +140,41 @@ __global__ void __launch_bounds__(RENDER_THREADS, 6) render_bwd_kernel(const Ren
         pyf[k] = (float)py;
         const bool inside = pix_x < a.W && py < a.H;
         const size_t pid = (size_t)py * a.W + pix_x;
-        Tfin[k] = inside ? a.final_T[pid] : 0.f;
-        T[k] = Tfin[k];
+        const float Tfin = inside ? a.final_T[pid] : 0.f;
+        T[k] = Tfin;
         ncontrib[k] = inside ? (int)a.n_contrib[pid] : 0;
 #pragma unroll
         for (int s = 0; s < NS; s++) dLr[s][k] = dLg[s][k] = dLb[s][k] = 0.f;
-        bgdot[k] = 0.f;
+        float bgdot = 0.f;                      // set 0 only (set 1 of the dual mode is the black pass)
         if (inside) {
             if (MODE == 0) {
                 dLr[0][k] = a.dL_dpix[pid];
                 dLg[0][k] = a.dL_dpix[plane + pid];
                 dLb[0][k] = a.dL_dpix[2 * plane + pid];
-                bgdot[k] = __ldg(a.bg) * dLr[0][k] + __ldg(a.bg + 1) * dLg[0][k] + __ldg(a.bg + 2) * dLb[0][k];
+                bgdot = __ldg(a.bg) * dLr[0][k] + __ldg(a.bg + 1) * dLg[0][k] + __ldg(a.bg + 2) * dLb[0][k];
             } else if (MODE == 1) {
                 // residual = truth/255 - rendered (imageIntToLoss, src/Trainer.cu:38-42)
                 const uint32_t t = a.truth[pid];
                 dLr[0][k] = (float)(t & 0xFF) / 255.0f - a.rendered[pid];
                 dLg[0][k] = (float)((t >> 8) & 0xFF) / 255.0f - a.rendered[plane + pid];
                 dLb[0][k] = (float)((t >> 16) & 0xFF) / 255.0f - a.rendered[2 * plane + pid];
-                bgdot[k] = __ldg(a.bg) * dLr[0][k] + __ldg(a.bg + 1) * dLg[0][k] + __ldg(a.bg + 2) * dLb[0][k];
+                bgdot = __ldg(a.bg) * dLr[0][k] + __ldg(a.bg + 1) * dLg[0][k] + __ldg(a.bg + 2) * dLb[0][k];
             } else {
                 // `rendered` is the black-background image C; the white one is fma(1, T, C) = C + T
                 const float cr = a.rendered[pid], cg = a.rendered[plane + pid], cb = a.rendered[2 * plane + pid];
                 const uint32_t tw = a.truth[pid], tb = a.truth2[pid];
-                dLr[0][k] = (float)(tw & 0xFF) / 255.0f - __fadd_rn(cr, Tfin[k]);
-                dLg[0][k] = (float)((tw >> 8) & 0xFF) / 255.0f - __fadd_rn(cg, Tfin[k]);
-                dLb[0][k] = (float)((tw >> 16) & 0xFF) / 255.0f - __fadd_rn(cb, Tfin[k]);
+                dLr[0][k] = (float)(tw & 0xFF) / 255.0f - __fadd_rn(cr, Tfin);
+                dLg[0][k] = (float)((tw >> 8) & 0xFF) / 255.0f - __fadd_rn(cg, Tfin);
+                dLb[0][k] = (float)((tw >> 16) & 0xFF) / 255.0f - __fadd_rn(cb, Tfin);
                 dLr[NS - 1][k] = (float)(tb & 0xFF) / 255.0f - cr;
                 dLg[NS - 1][k] = (float)((tb >> 8) & 0xFF) / 255.0f - cg;
                 dLb[NS - 1][k] = (float)((tb >> 16) & 0xFF) / 255.0f - cb;
-                bgdot[k] = dLr[0][k] + dLg[0][k] + dLb[0][k];   // white background (1,1,1)
+                bgdot = dLr[0][k] + dLg[0][k] + dLb[0][k];   // white background (1,1,1)
             }
         }
-        last_alpha[k] = 0.f;
-        lcr[k] = lcg[k] = lcb[k] = 0.f;
-        arr[k] = arg[k] = arb[k] = 0.f;
+#pragma unroll
+        for (int s = 0; s < NS; s++) SD[s][k] = 0.f;
+        SD[0][k] = Tfin * bgdot;                // the background is the last, fully opaque layer
     }
     if (MODE != 0 && a.loss_out != nullptr) {
         // monitoring only: sum of squared residuals of the pass(es) this launch serves
@@ -123,6 +190,7 @@ __global__ void __launch_bounds__(RENDER_THREADS, 6) render_bwd_kernel(const Ren
         if (lane == 0) atomicAdd(a.loss_out, acc);
         if (start == 0) return;
     }
+    asm volatile("" : "+f"(pyf[0]), "+f"(pyf[1]));   // keep the pixel rows in registers (not re-derived per entry)
     const int warp_max = __reduce_max_sync(0xffffffffu, max(ncontrib[0], ncontrib[1]));
 
     // Every warp walks the list on its own: no block-wide barrier, a warp whose 64 pixels blended
@@ -177,12 +245,13 @@ __global__ void __launch_bounds__(RENDER_THREADS, 6) render_bwd_kernel(const Ren
                 const float4 ra = buf[j].a;   // x, y, conic.x, conic.y
                 const float4 rb = buf[j].b;   // conic.z, opacity, r, g
                 const float2 rc = *reinterpret_cast<const float2*>(&buf[j].c);   // b, power threshold
+                const uint32_t splat = ids[j];
                 const float dx = __fsub_rn(ra.x, pxf);
                 const float bx = __fmul_rn(dx, ra.z);
                 const float cxy = __fmul_rn(dx, ra.w);
                 // per lane and set: A = sum h, B = sum h dy, C = sum h dy^2 over the lane's two pixels (they
                 // share dx, so the dx factors of the six moments are applied once after the pixel loop) and
-                // the three colour sums
+                // the three colour sums.  NS == 2: every one of them is a (white, black) pair.
                 float mA[NS], mB[NS], mC[NS], vr[NS], vg[NS], vb[NS];
 #pragma unroll
                 for (int s = 0; s < NS; s++) mA[s] = mB[s] = mC[s] = vr[s] = vg[s] = vb[s] = 0.f;
@@ -199,63 +268,94 @@ __global__ void __launch_bounds__(RENDER_THREADS, 6) render_bwd_kernel(const Ren
                     const float alpha = fminf(0.99f, __fmul_rn(rb.y, G));
                     if (alpha < 1.0f / 255.0f) continue;
                     hit = true;
-                    const float inv = __fdividef(1.0f, 1.f - alpha);
-                    T[k] *= inv;
+                    const float inv = rcp_fast(1.f - alpha);      // alpha <= 0.99
+                    T[k] *= inv;                                   // T in front of this entry
                     const float w = alpha * T[k];
-                    // colour behind this splat, reconstructed back to front
-                    arr[k] = fmaf(last_alpha[k], lcr[k] - arr[k], arr[k]);
-                    arg[k] = fmaf(last_alpha[k], lcg[k] - arg[k], arg[k]);
-                    arb[k] = fmaf(last_alpha[k], lcb[k] - arb[k], arb[k]);
-                    lcr[k] = rb.z; lcg[k] = rb.w; lcb[k] = rc.x;
-                    last_alpha[k] = alpha;
-                    const float er = rb.z - arr[k], eg = rb.w - arg[k], eb = rc.x - arb[k];
-                    const float GT = G * T[k];
-#pragma unroll
-                    for (int s = 0; s < NS; s++) {
-                        vr[s] = fmaf(w, dLr[s][k], vr[s]);
-                        vg[s] = fmaf(w, dLg[s][k], vg[s]);
-                        vb[s] = fmaf(w, dLb[s][k], vb[s]);
-                        // h = G * dL/dalpha; the background term (alpha also scales how much of bg shows
-                        // through) exists for a non-black background only
-                        float h = GT * (er * dLr[s][k] + eg * dLg[s][k] + eb * dLb[s][k]);
-                        if (s == 0) h = fmaf(-(G * Tfin[k] * inv), bgdot[k], h);
+                    const float GT = G * T[k], Ginv = G * inv;
+                    if constexpr (NS == 2) {
+                        const float2 w2 = dup2(w), dy2 = dup2(dy);
+                        const float2 dr = make_float2(dLr[0][k], dLr[1][k]), dg = make_float2(dLg[0][k], dLg[1][k]),
+                                     db = make_float2(dLb[0][k], dLb[1][k]);
+                        float2 v;
+                        v = fma2(w2, dr, make_float2(vr[0], vr[1])); vr[0] = v.x; vr[1] = v.y;
+                        v = fma2(w2, dg, make_float2(vg[0], vg[1])); vg[0] = v.x; vg[1] = v.y;
+                        v = fma2(w2, db, make_float2(vb[0], vb[1])); vb[0] = v.x; vb[1] = v.y;
+                        const float2 cd = fma2(dup2(rc.x), db, fma2(dup2(rb.w), dg, mul2(dup2(rb.z), dr)));
+                        const float2 sd = make_float2(SD[0][k], SD[1][k]);
+                        const float2 h = fma2(dup2(GT), cd, mul2(dup2(-Ginv), sd));   // h = G * dL/dalpha
+                        v = fma2(w2, cd, sd); SD[0][k] = v.x; SD[1][k] = v.y;
+                        const float2 hy = mul2(h, dy2);
+                        v = add2(make_float2(mA[0], mA[1]), h); mA[0] = v.x; mA[1] = v.y;
+                        v = add2(make_float2(mB[0], mB[1]), hy); mB[0] = v.x; mB[1] = v.y;
+                        v = fma2(hy, dy2, make_float2(mC[0], mC[1])); mC[0] = v.x; mC[1] = v.y;
+                    } else {
+                        vr[0] = fmaf(w, dLr[0][k], vr[0]);
+                        vg[0] = fmaf(w, dLg[0][k], vg[0]);
+                        vb[0] = fmaf(w, dLb[0][k], vb[0]);
+                        const float cd = fmaf(rc.x, dLb[0][k], fmaf(rb.w, dLg[0][k], rb.z * dLr[0][k]));
+                        const float h = fmaf(GT, cd, -(Ginv * SD[0][k]));              // h = G * dL/dalpha
+                        SD[0][k] = fmaf(w, cd, SD[0][k]);
                         const float hy = h * dy;
-                        mA[s] += h;
-                        mB[s] += hy;
-                        mC[s] = fmaf(hy, dy, mC[s]);
+                        mA[0] += h;
+                        mB[0] += hy;
+                        mC[0] = fmaf(hy, dy, mC[0]);
                     }
                 }
                 if (!__any_sync(0xffffffffu, hit)) continue;
-                // Transposed reduction through shared memory: every lane parks its 9*NS partial sums in
-                // column `lane` of the warp's [9*NS][RED_STRIDE] panel (conflict-free: bank = 4*row + lane),
-                // then lane r adds up row r with eight 128-bit loads and issues the one RED for GradRec
-                // float r.  ~60 warp instructions per (warp, entry) against ~95 for two shuffle butterflies.
+                if constexpr (NS == 2) {
+                    // Transposed reduction through shared memory: every lane parks its nine (white, black) pairs in
+                    // column `lane` of the warp's [9][RED_STRIDE2] panel with 64-bit stores; lanes r and r + 9 add
+                    // up one half of row r each (eight 128-bit loads, a tree of packed adds) and issue one 64-bit
+                    // RED for pair r of the splat's GradRec2 -- one RED instruction per warp and entry.
+                    const float2 dx2 = dup2(dx);
+                    const float2 A2 = make_float2(mA[0], mA[1]), B2 = make_float2(mB[0], mB[1]);
+                    const float2 ax = mul2(A2, dx2);
+                    sts64(col_addr + 0 * RED_STRIDE2 * 8, A2);                                   // H0
+                    sts64(col_addr + 1 * RED_STRIDE2 * 8, ax);                                   // Hx
+                    sts64(col_addr + 2 * RED_STRIDE2 * 8, B2);                                   // Hy
+                    sts64(col_addr + 3 * RED_STRIDE2 * 8, mul2(ax, dx2));                        // Hxx
+                    sts64(col_addr + 4 * RED_STRIDE2 * 8, mul2(B2, dx2));                        // Hxy
+                    sts64(col_addr + 5 * RED_STRIDE2 * 8, make_float2(mC[0], mC[1]));            // Hyy
+                    sts64(col_addr + 6 * RED_STRIDE2 * 8, make_float2(vr[0], vr[1]));
+                    sts64(col_addr + 7 * RED_STRIDE2 * 8, make_float2(vg[0], vg[1]));
+                    sts64(col_addr + 8 * RED_STRIDE2 * 8, make_float2(vb[0], vb[1]));
+                    __syncwarp();
+                    if (role < 2) {
+                        float2 p[8];
 #pragma unroll
-                for (int s = 0; s < NS; s++) {
-                    float* col = red + s * 9 * RED_STRIDE + lane;
-                    const float ax = mA[s] * dx;
-                    col[0 * RED_STRIDE] = mA[s];          // H0
-                    col[1 * RED_STRIDE] = ax;             // Hx
-                    col[2 * RED_STRIDE] = mB[s];          // Hy
-                    col[3 * RED_STRIDE] = ax * dx;        // Hxx
-                    col[4 * RED_STRIDE] = mB[s] * dx;     // Hxy
-                    col[5 * RED_STRIDE] = mC[s];          // Hyy
-                    col[6 * RED_STRIDE] = vr[s];
-                    col[7 * RED_STRIDE] = vg[s];
-                    col[8 * RED_STRIDE] = vb[s];
-                }
-                __syncwarp();
-                if (lane < 9 * NS) {
-                    const float4* row = reinterpret_cast<const float4*>(red + lane * RED_STRIDE);
-                    float4 acc = row[0];
-#pragma unroll
-                    for (int c = 1; c < 8; c++) {
-                        const float4 t = row[c];
-                        acc.x += t.x; acc.y += t.y; acc.z += t.z; acc.w += t.w;
+                        for (int c = 0; c < 8; c++) {
+                            const float4 t = lds128(row_addr + c * 16);
+                            p[c] = add2(make_float2(t.x, t.y), make_float2(t.z, t.w));
+                        }
+                        const float2 sum = add2(add2(add2(p[0], p[1]), add2(p[2], p[3])), add2(add2(p[4], p[5]), add2(p[6], p[7])));
+                        red_add2(gbase + (size_t)splat * (sizeof(GradRec2) / 4), sum);
                     }
-                    const float sum = (acc.x + acc.y) + (acc.z + acc.w);
-                    GradRec* g = ((NS == 1 || lane < 9) ? a.grads : a.grads2) + ids[j];
-                    atomicAdd(reinterpret_cast<float*>(g) + ((NS == 1 || lane < 9) ? lane : lane - 9), sum);
+                } else {
+                    // one set: [9][RED_STRIDE] floats (conflict-free: bank = 4*row + lane), lane r adds up row r
+                    // with eight 128-bit loads and issues the one RED for GradRec float r
+                    float* col = red + lane;
+                    const float ax = mA[0] * dx;
+                    col[0 * RED_STRIDE] = mA[0];          // H0
+                    col[1 * RED_STRIDE] = ax;             // Hx
+                    col[2 * RED_STRIDE] = mB[0];          // Hy
+                    col[3 * RED_STRIDE] = ax * dx;        // Hxx
+                    col[4 * RED_STRIDE] = mB[0] * dx;     // Hxy
+                    col[5 * RED_STRIDE] = mC[0];          // Hyy
+                    col[6 * RED_STRIDE] = vr[0];
+                    col[7 * RED_STRIDE] = vg[0];
+                    col[8 * RED_STRIDE] = vb[0];
+                    __syncwarp();
+                    if (lane < 9) {
+                        const float4* row = reinterpret_cast<const float4*>(red + lane * RED_STRIDE);
+                        float4 acc = row[0];
+#pragma unroll
+                        for (int c = 1; c < 8; c++) {
+                            const float4 t = row[c];
+                            acc.x += t.x; acc.y += t.y; acc.z += t.z; acc.w += t.w;
+                        }
+                        const float sum = (acc.x + acc.y) + (acc.z + acc.w);
+                        atomicAdd(reinterpret_cast<float*>(a.grads + splat) + lane, sum);
+                    }
                 }
                 __syncwarp();
             }

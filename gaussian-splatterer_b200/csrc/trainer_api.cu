@@ -40,7 +40,7 @@ struct gsb_trainer {
 
     // arenas
     char* geom = nullptr; size_t geom_P = 0; GeomWs g;
-    GradRec* grads2 = nullptr;        // second scratch set: black pass of a fused camera pass
+    GradRec2* grads2 = nullptr;       // scratch of a fused camera pass: (white, black) pairs
     bool fuse_wb = true;              // white + black pass of a camera share one forward / one backward walk
     char* bin = nullptr; uint32_t r_cap = 0; BinWs b;
     char* img = nullptr; ImageWs im;
@@ -50,7 +50,7 @@ struct gsb_trainer {
     // the render backward of view pass i (issue-bound); activate() swaps a set into the members before
     // a pass is enqueued (kernel arguments are captured at launch).
     struct ViewSlot {
-        char* geom = nullptr; GeomWs g; GradRec* grads2 = nullptr;
+        char* geom = nullptr; GeomWs g; GradRec2* grads2 = nullptr;
         char* bin = nullptr; BinWs b;
         char* img = nullptr; ImageWs im;
         float* rendered = nullptr;
@@ -119,8 +119,8 @@ int ensure_geom(gsb_trainer* t, size_t P) {
         GSB_CUDA_OK(cudaMemsetAsync(t->geom, 0, bytes, t->stream));   // look-back words and grad scratch start at zero
         t->g.carve(t->geom, cap);
         if (t->grads2) GSB_CUDA_OK(cudaFree(t->grads2));
-        GSB_CUDA_OK(cudaMalloc(&t->grads2, cap * sizeof(GradRec)));
-        GSB_CUDA_OK(cudaMemsetAsync(t->grads2, 0, cap * sizeof(GradRec), t->stream));
+        GSB_CUDA_OK(cudaMalloc(&t->grads2, cap * sizeof(GradRec2)));
+        GSB_CUDA_OK(cudaMemsetAsync(t->grads2, 0, cap * sizeof(GradRec2), t->stream));
         save_slot(t);
     }
     t->geom_P = cap;
@@ -504,7 +504,7 @@ int gsb_trainer_accumulate(gsb_trainer* t) {
         save_slot(t);
         for (int k = 0; k < 2; k++) {
             GSB_CUDA_OK(cudaMemsetAsync(t->slot[k].g.grads, 0, (size_t)t->geom_P * sizeof(GradRec), s));
-            GSB_CUDA_OK(cudaMemsetAsync(t->slot[k].grads2, 0, (size_t)t->geom_P * sizeof(GradRec), s));
+            GSB_CUDA_OK(cudaMemsetAsync(t->slot[k].grads2, 0, (size_t)t->geom_P * sizeof(GradRec2), s));
         }
         if (int e = ensure_bin(t, (uint32_t)std::min<size_t>(0x7FFFFFF0u, (size_t)maxR + maxR / 4 + 4096))) return e;
     }

@@ -185,23 +185,32 @@ def test_iterations_track_reference_replay_over_several_steps():
     rt = refshim.RefTrainer(W, Hh, DEV)
     rt.set_model(cloud, 1000000, 1, 4)
     rt.set_truths(tw, tb, consts)
+    # a second replay of the reference from the same start measures its own run-to-run spread: its atomics are
+    # unordered, and once in a while a rounding difference flips a blend / clamp decision of one splat, after which
+    # two runs of the REFERENCE are further apart (1.4e-3 observed at step 5) than the budget below
+    rt2 = refshim.RefTrainer(W, Hh, DEV)
+    rt2.set_model(cloud, 1000000, 1, 4)
+    rt2.set_truths(tw, tb, consts)
     tr = gsb.Trainer(W, Hh, DEV)
     tr.model = gsb.ModelSplatsDevice(gsb.ModelSplatsHost.from_arrays(*[cloud[k] for k in KEYS]), DEV)
     tr.truthFrameBuffersW, tr.truthFrameBuffersB, tr.truthCameras = tw, tb, cams
     for _ in range(5):
         rt.train(project.params13(), as_shipped=True)
+        rt2.train(project.params13(), as_shipped=True)
         tr.train(project, False)
-    ref = rt.get_model()
+    ref, ref2 = rt.get_model(), rt2.get_model()
     mine = gsb.ModelSplatsHost.from_device(tr.model)
     for k in KEYS:
         # measured against how far the parameters moved: 1e-3 relative L2 (the gradient budget of north_star;
-        # two runs of the reference itself differ by ~2e-5 here), no single parameter off by more than 1 %
+        # two runs of the reference itself usually differ by ~2e-5 here), no single parameter off by more than 1 %;
+        # where the reference's own two runs are further apart than that, twice their spread
         move = ref[k].astype(np.float64) - cloud[k]
         diff = getattr(mine, k).astype(np.float64) - ref[k]
+        spread = ref2[k].astype(np.float64) - ref[k]
         assert np.abs(move).max() > 0
-        assert np.linalg.norm(diff) <= 1e-3 * np.linalg.norm(move), k
-        assert np.abs(diff).max() <= max(1e-2 * np.abs(move).max(), 5e-6), k
-    rt.close(); tr.close()
+        assert np.linalg.norm(diff) <= max(1e-3 * np.linalg.norm(move), 2 * np.linalg.norm(spread)), k
+        assert np.abs(diff).max() <= max(1e-2 * np.abs(move).max(), 5e-6, 2 * np.abs(spread).max()), k
+    rt.close(); rt2.close(); tr.close()
 
 
 def test_overlapped_pipeline_equals_serial_execution():
