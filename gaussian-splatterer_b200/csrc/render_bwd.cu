@@ -17,15 +17,23 @@
 // For every surviving list entry the nine partial sums are added over the lane's two pixels in
 // registers and reduced across the warp (skipped when no lane blended the entry) by a transposed
 // pass through a per-warp shared-memory panel; the lanes that end up holding a total issue one
-// red.global.add each into the packed GradRec scratch (one RED instruction per warp and entry).
+// red.global.add each into the packed scratch (one RED instruction per warp and entry).
 // On the measured scenes 1.2 warps blend a given (tile, splat) duplicate, so a further cross-warp
-// stage would save almost nothing.  (Round-1 ncu: the earlier shuffle butterfly was 48 % of the
-// kernel's warp instructions, profiles/r01_render_bwd_source.txt.)
+// stage would save almost nothing.
+//
+// The colour behind an entry is not tracked as the reference's normalised three-channel recurrence
+// (accum_rec / last_alpha / last_color, backward.cu:489-500) but as SD = dL . (un-normalised colour
+// behind, background included), one FMA per residual: T_i (c_i - accum_rec_i) . dL equals
+// T_i (c_i . dL) - SD_i / (1 - alpha_i).
 //
 // DUAL mode serves Trainer::train's white and black pass of one camera (src/Trainer.cu:311-314) in
 // a single walk: both passes blend the same splats with the same alpha and T (the background only
-// enters through out = C + T * bg, forward.cu:372), so power / exp / T / colour-behind are computed
-// once and only the two residuals' sums are kept apart (two GradRec sets).
+// enters through out = C + T * bg, forward.cu:372), so power / exp / T are computed once and every
+// per-residual quantity is a (white, black) pair: the arithmetic is issued as packed FP32 pairs
+// (FFMA2 / FMUL2 / FADD2), the panel holds float2 and the scratch is GradRec2 (interleaved pairs),
+// so one 64-bit RED per reader lane adds both passes' sums.  Round-1 ncu history
+// (profiles/r01_render_bwd_source.txt): shuffle butterflies 48 % of the warp instructions ->
+// transposed scalar panel 30 % -> packed panel 22 %; 622 M -> 421 M warp instructions per launch.
 
 #include "common.cuh"
 #include "render_common.cuh"
@@ -109,12 +117,11 @@ __global__ void __launch_bounds__(RENDER_THREADS, GSB_BWD_CTAS) render_bwd_kerne
     float* const red = s_red[warp];
     // dual mode: lanes r and r + 9 (r < 9) each sum one half of row r of the panel and feed pair r of the splat's
     // GradRec2; the addresses are computed once and kept opaque so they are not re-derived per entry
-    int role = lane < 9 ? 0 : (lane < 18 ? 1 : 2);          // reader of the first / second half row, or none
-    const int rrow = role == 1 ? lane - 9 : lane;
+    const int rrow = lane < 9 ? lane : lane - 9;
     uint32_t col_addr = (uint32_t)__cvta_generic_to_shared(red) + lane * 8;
-    uint32_t row_addr = (uint32_t)__cvta_generic_to_shared(red) + (rrow * RED_STRIDE2 + (role == 1 ? 16 : 0)) * 8;
-    float* gbase = reinterpret_cast<float*>(a.grads2) + rrow * 2;
-    if (NS == 2) asm volatile("" : "+r"(col_addr), "+r"(row_addr), "+l"(gbase), "+r"(role));
+    uint32_t row_addr = (uint32_t)__cvta_generic_to_shared(red) + (rrow * RED_STRIDE2 + (lane < 9 ? 0 : 16)) * 8;
+    float* gbase = lane < 18 ? reinterpret_cast<float*>(a.grads2) + rrow * 2 : nullptr;   // null: not a reader lane
+    if (NS == 2) asm volatile("" : "+r"(col_addr), "+r"(row_addr), "+l"(gbase));
     const int tile = blockIdx.y * a.grid_x + blockIdx.x;
     const int start = (int)a.tile_max[tile];       // entries at or beyond this index were blended by no pixel
     if (start == 0 && (MODE == 0 || a.loss_out == nullptr)) return;
@@ -320,7 +327,7 @@ __global__ void __launch_bounds__(RENDER_THREADS, GSB_BWD_CTAS) render_bwd_kerne
                     sts64(col_addr + 7 * RED_STRIDE2 * 8, make_float2(vg[0], vg[1]));
                     sts64(col_addr + 8 * RED_STRIDE2 * 8, make_float2(vb[0], vb[1]));
                     __syncwarp();
-                    if (role < 2) {
+                    if (gbase != nullptr) {
                         float2 p[8];
 #pragma unroll
                         for (int c = 0; c < 8; c++) {
