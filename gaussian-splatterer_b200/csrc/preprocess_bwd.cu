@@ -106,6 +106,19 @@ __device__ __forceinline__ V3 dir_grad(const ShDirs& q, V3 dRGB) {
 // M4 = the application's shape (SH degree 1, 4 coefficients, src/Config.h:19-20): the 24 running-mean
 // floats of the splat are loaded up front into registers (independent loads in flight together, hidden
 // behind the arithmetic) and stored once at the end, instead of 24 dependent read-modify-writes.
+// GSB_PB_RED: the Trainer shape adds grad/S to the running means with fire-and-forget REDs (vector REDs for the 16-byte
+// aligned SH and rotation records) instead of loading the 24 floats up front and storing them back: no load latency on
+// the critical path and 24 registers fewer.  Every element is touched by exactly one thread per launch, so the sums
+// (and their order across launches of one stream) are those of the load / add / store form.
+#ifndef GSB_PB_RED
+#define GSB_PB_RED 1
+#endif
+__device__ __forceinline__ void pb_red(float* p, float v) {
+    asm volatile("red.global.add.f32 [%0], %1;" ::"l"(p), "f"(v) : "memory");
+}
+__device__ __forceinline__ void pb_red4(float* p, float x, float y, float z, float w) {
+    asm volatile("red.global.v4.f32.add [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(x), "f"(y), "f"(z), "f"(w) : "memory");
+}
 #ifndef GSB_PB_THREADS
 #define GSB_PB_THREADS 256
 #define GSB_PB_BLOCKS 1
@@ -124,7 +137,11 @@ __global__ void __launch_bounds__(GSB_PB_THREADS, GSB_PB_BLOCKS) preprocess_bwd_
     float* avg_rot = modeA ? nullptr : avg_op + P;
     float o_var = 0.f, o_loc[3] = {0.f, 0.f, 0.f}, o_op = 0.f, o_scale[3] = {0.f, 0.f, 0.f}, o_rot[4] = {0.f, 0.f, 0.f, 0.f};
     float o_sh[12];
-    if (!modeA) {
+    constexpr bool RED = M4 && (GSB_PB_RED != 0);   // o_* start at zero and are added with REDs at the end
+    if (RED) {
+#pragma unroll
+        for (int k = 0; k < 12; k++) o_sh[k] = 0.f;
+    } else if (!modeA) {
         o_var = a.avg[idx];
         o_op = avg_op[idx];
 #pragma unroll
@@ -305,7 +322,10 @@ __global__ void __launch_bounds__(GSB_PB_THREADS, GSB_PB_BLOCKS) preprocess_bwd_
             });
             float4* p = reinterpret_cast<float4*>(avg_sh + 12 * (size_t)idx);
 #pragma unroll
-            for (int k = 0; k < 3; k++) p[k] = make_float4(o_sh[4 * k], o_sh[4 * k + 1], o_sh[4 * k + 2], o_sh[4 * k + 3]);
+            for (int k = 0; k < 3; k++) {
+                if (RED) pb_red4(reinterpret_cast<float*>(p + k), o_sh[4 * k], o_sh[4 * k + 1], o_sh[4 * k + 2], o_sh[4 * k + 3]);
+                else p[k] = make_float4(o_sh[4 * k], o_sh[4 * k + 1], o_sh[4 * k + 2], o_sh[4 * k + 3]);
+            }
         } else {
             float* out = avg_sh + (size_t)idx * M * 3;
             dirs = sh_backward(a.D, mx, my, mz, a.cam_pos, sh, dsum, [&](int c, V3 v) {
@@ -328,9 +348,15 @@ __global__ void __launch_bounds__(GSB_PB_THREADS, GSB_PB_BLOCKS) preprocess_bwd_
             var += sqrtf(gmean[s].x * gmean[s].x + gmean[s].y * gmean[s].y + gmean[s].z * gmean[s].z) / S;
             gs_.x += gmean[s].x / S; gs_.y += gmean[s].y / S; gs_.z += gmean[s].z / S;
         }
-        a.avg[idx] = o_var + var;
-        avg_loc[3 * idx] = o_loc[0] + gs_.x; avg_loc[3 * idx + 1] = o_loc[1] + gs_.y; avg_loc[3 * idx + 2] = o_loc[2] + gs_.z;
-        avg_op[idx] = o_op + sop * invS;
+        if (RED) {
+            pb_red(a.avg + idx, var);
+            pb_red(avg_loc + 3 * idx, gs_.x); pb_red(avg_loc + 3 * idx + 1, gs_.y); pb_red(avg_loc + 3 * idx + 2, gs_.z);
+            pb_red(avg_op + idx, sop * invS);
+        } else {
+            a.avg[idx] = o_var + var;
+            avg_loc[3 * idx] = o_loc[0] + gs_.x; avg_loc[3 * idx + 1] = o_loc[1] + gs_.y; avg_loc[3 * idx + 2] = o_loc[2] + gs_.z;
+            avg_op[idx] = o_op + sop * invS;
+        }
     }
 
     // ---- cov3D -> scale, rotation ----
@@ -369,6 +395,10 @@ __global__ void __launch_bounds__(GSB_PB_THREADS, GSB_PB_BLOCKS) preprocess_bwd_
             for (int c = 0; c < 3; c++) a.dL_dscale[3 * idx + c] = gs[c];
 #pragma unroll
             for (int c = 0; c < 4; c++) a.dL_drot[4 * idx + c] = gq[c];
+        } else if (RED) {
+#pragma unroll
+            for (int c = 0; c < 3; c++) pb_red(avg_scale + 3 * idx + c, gs[c] / S);
+            pb_red4(avg_rot + 4 * idx, gq[0] / S, gq[1] / S, gq[2] / S, gq[3] / S);
         } else {
 #pragma unroll
             for (int c = 0; c < 3; c++) avg_scale[3 * idx + c] = o_scale[c] + gs[c] / S;
