@@ -40,6 +40,9 @@
 
 namespace {
 
+#ifndef GSB_BWD_CONV
+#define GSB_BWD_CONV 1   // fused mode: straight-line evaluation of both pixels of a lane
+#endif
 #ifndef GSB_BWD_CTAS
 #define GSB_BWD_CTAS 8   // resident CTAs per SM the register budget is cut for (64 registers)
 #endif
@@ -260,6 +263,63 @@ __global__ void __launch_bounds__(RENDER_THREADS, GSB_BWD_CTAS) render_bwd_kerne
                 // share dx, so the dx factors of the six moments are applied once after the pixel loop) and
                 // the three colour sums.  NS == 2: every one of them is a (white, black) pair.
                 float mA[NS], mB[NS], mC[NS], vr[NS], vg[NS], vb[NS];
+#if GSB_BWD_CONV
+                if constexpr (NS == 2) {
+                    // Both pixels of the lane in one straight-line pass (no divergent per-pixel blocks: the two
+                    // dependency chains interleave).  A pixel that does not blend the entry runs with alpha = G = 0,
+                    // which leaves T and SD bit for bit unchanged (1 / (1 - 0) = 1, w = 0) and contributes zero sums.
+                    float pw[2], dyv[2];
+                    bool pass[2];
+#pragma unroll
+                    for (int k = 0; k < 2; k++) {
+                        const float dy = __fsub_rn(ra.y, pyf[k]);
+                        const float ay = __fmul_rn(dy, __fmul_rn(dy, rb.x));
+                        const float power = __fmaf_rn(__fmaf_rn(dx, bx, ay), -0.5f, -__fmul_rn(dy, cxy));
+                        pass[k] = (idx < ncontrib[k]) && !(power < rc.y) && !(power > 0.0f);
+                        pw[k] = power;
+                        dyv[k] = dy;
+                    }
+                    if (!__any_sync(0xffffffffu, pass[0] || pass[1])) continue;
+                    float G[2], alpha[2];
+                    bool hit = false;
+#pragma unroll
+                    for (int k = 0; k < 2; k++) {
+                        const float g = expf(pw[k]);
+                        const float al = fminf(0.99f, __fmul_rn(rb.y, g));
+                        const bool h = pass[k] && !(al < 1.0f / 255.0f);
+                        G[k] = h ? g : 0.f;
+                        alpha[k] = h ? al : 0.f;
+                        hit = hit || h;
+                    }
+                    if (!__any_sync(0xffffffffu, hit)) continue;
+                    float2 sA, sB, sC, sr, sg, sb;
+#pragma unroll
+                    for (int k = 0; k < 2; k++) {
+                        const float inv = rcp_fast(1.f - alpha[k]);
+                        T[k] *= inv;
+                        const float w = alpha[k] * T[k];
+                        const float GT = G[k] * T[k], Ginv = G[k] * inv;
+                        const float2 w2 = dup2(w), dy2 = dup2(dyv[k]);
+                        const float2 dr = make_float2(dLr[0][k], dLr[1][k]), dg = make_float2(dLg[0][k], dLg[1][k]),
+                                     db = make_float2(dLb[0][k], dLb[1][k]);
+                        const float2 cd = fma2(dup2(rc.x), db, fma2(dup2(rb.w), dg, mul2(dup2(rb.z), dr)));
+                        const float2 sd = make_float2(SD[0][k], SD[1][k]);
+                        const float2 h = fma2(dup2(GT), cd, mul2(dup2(-Ginv), sd));   // h = G * dL/dalpha
+                        const float2 v = fma2(w2, cd, sd); SD[0][k] = v.x; SD[1][k] = v.y;
+                        const float2 hy = mul2(h, dy2);
+                        if (k == 0) {
+                            sr = mul2(w2, dr); sg = mul2(w2, dg); sb = mul2(w2, db);
+                            sA = h; sB = hy; sC = mul2(hy, dy2);
+                        } else {
+                            sr = fma2(w2, dr, sr); sg = fma2(w2, dg, sg); sb = fma2(w2, db, sb);
+                            sA = add2(sA, h); sB = add2(sB, hy); sC = fma2(hy, dy2, sC);
+                        }
+                    }
+                    mA[0] = sA.x; mA[1] = sA.y; mB[0] = sB.x; mB[1] = sB.y; mC[0] = sC.x; mC[1] = sC.y;
+                    vr[0] = sr.x; vr[1] = sr.y; vg[0] = sg.x; vg[1] = sg.y; vb[0] = sb.x; vb[1] = sb.y;
+                } else
+#endif
+                {
 #pragma unroll
                 for (int s = 0; s < NS; s++) mA[s] = mB[s] = mC[s] = vr[s] = vg[s] = vb[s] = 0.f;
                 bool hit = false;
@@ -309,6 +369,7 @@ __global__ void __launch_bounds__(RENDER_THREADS, GSB_BWD_CTAS) render_bwd_kerne
                     }
                 }
                 if (!__any_sync(0xffffffffu, hit)) continue;
+                }
                 if constexpr (NS == 2) {
                     // Transposed reduction through shared memory: every lane parks its nine (white, black) pairs in
                     // column `lane` of the warp's [9][RED_STRIDE2] panel with 64-bit stores; lanes r and r + 9 add
