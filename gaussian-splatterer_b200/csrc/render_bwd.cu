@@ -48,8 +48,9 @@ namespace {
 #endif
 
 constexpr int RED_STRIDE = 36;   // floats per row of the reduction panel: 32 lanes + 4 pad (rows stay 16-byte aligned)
-constexpr int RED_STRIDE2 = 34;  // dual mode: float2 (white, black) per lane, 32 lanes + 2 pad; 34 / 2 odd keeps the
-                                 // readers' 128-bit loads of different rows on different bank groups
+constexpr int RED_STRIDE2 = 38;  // dual mode: float2 (white, black) per lane: 32 lanes + 4 zero slots (18 chunks of 16 B) + 2 pad; the row
+                                 // stride of 304 B = 48 mod 128 keeps the three readers of consecutive rows (48 contiguous bytes per row
+                                 // and load) on different banks
 
 // Packed FP32 pairs (sm_100 FFMA2 / FMUL2 / FADD2): one issue slot for two IEEE round-to-nearest operations.  The
 // dual mode keeps every per-residual quantity as a (white, black) pair, so its arithmetic issues half the
@@ -120,11 +121,19 @@ __global__ void __launch_bounds__(RENDER_THREADS, GSB_BWD_CTAS) render_bwd_kerne
     float* const red = s_red[warp];
     // dual mode: lanes r and r + 9 (r < 9) each sum one half of row r of the panel and feed pair r of the splat's
     // GradRec2; the addresses are computed once and kept opaque so they are not re-derived per entry
-    const int rrow = lane < 9 ? lane : lane - 9;
+    // lane = 3 * row + third (< 27) reads chunks third, third + 3, ..., third + 15 of its row (six 128-bit loads in flight
+    // together: one shared-memory round trip; slots 32..35 of a row stay zero); the lanes with third == 0 collect the
+    // other two partial pairs with two shuffles and issue the RED for pair `row` of the GradRec2
+    const int rrow = lane / 3, third = lane - 3 * rrow;
     uint32_t col_addr = (uint32_t)__cvta_generic_to_shared(red) + lane * 8;
-    uint32_t row_addr = (uint32_t)__cvta_generic_to_shared(red) + (rrow * RED_STRIDE2 + (lane < 9 ? 0 : 16)) * 8;
-    float* gbase = lane < 18 ? reinterpret_cast<float*>(a.grads2) + rrow * 2 : nullptr;   // null: not a reader lane
-    if (NS == 2) asm volatile("" : "+r"(col_addr), "+r"(row_addr), "+l"(gbase));
+    uint32_t row_addr = lane < 27 ? (uint32_t)__cvta_generic_to_shared(red) + rrow * RED_STRIDE2 * 8 + third * 16 : 0u;
+    float* gbase = (lane < 27 && third == 0) ? reinterpret_cast<float*>(a.grads2) + rrow * 2 : nullptr;
+    if (NS == 2) {
+        for (int r = 0; r < 9; r++)
+            if (lane < 6) sts64((uint32_t)__cvta_generic_to_shared(red) + (r * RED_STRIDE2 + 32 + lane) * 8, make_float2(0.f, 0.f));
+        __syncwarp();
+        asm volatile("" : "+r"(col_addr), "+r"(row_addr), "+l"(gbase));
+    }
     const int tile = blockIdx.y * a.grid_x + blockIdx.x;
     const int start = (int)a.tile_max[tile];       // entries at or beyond this index were blended by no pixel
     if (start == 0 && (MODE == 0 || a.loss_out == nullptr)) return;
@@ -372,9 +381,10 @@ __global__ void __launch_bounds__(RENDER_THREADS, GSB_BWD_CTAS) render_bwd_kerne
                 }
                 if constexpr (NS == 2) {
                     // Transposed reduction through shared memory: every lane parks its nine (white, black) pairs in
-                    // column `lane` of the warp's [9][RED_STRIDE2] panel with 64-bit stores; lanes r and r + 9 add
-                    // up one half of row r each (eight 128-bit loads, a tree of packed adds) and issue one 64-bit
-                    // RED for pair r of the splat's GradRec2 -- one RED instruction per warp and entry.
+                    // column `lane` of the warp's [9][RED_STRIDE2] panel with 64-bit stores; lanes 3r, 3r + 1, 3r + 2
+                    // add up a third of row r each (six 128-bit loads, a tree of packed adds), lane 3r collects the
+                    // three partial pairs with two shuffles and issues one 64-bit RED for pair r of the splat's
+                    // GradRec2 -- nine distinct addresses, one RED instruction per warp and entry.
                     const float2 dx2 = dup2(dx);
                     const float2 A2 = make_float2(mA[0], mA[1]), B2 = make_float2(mB[0], mB[1]);
                     const float2 ax = mul2(A2, dx2);
@@ -388,15 +398,20 @@ __global__ void __launch_bounds__(RENDER_THREADS, GSB_BWD_CTAS) render_bwd_kerne
                     sts64(col_addr + 7 * RED_STRIDE2 * 8, make_float2(vg[0], vg[1]));
                     sts64(col_addr + 8 * RED_STRIDE2 * 8, make_float2(vb[0], vb[1]));
                     __syncwarp();
-                    if (gbase != nullptr) {
-                        float2 p[8];
+                    {
+                        float2 part = make_float2(0.f, 0.f);
+                        if (row_addr != 0u) {
+                            float2 p[6];
 #pragma unroll
-                        for (int c = 0; c < 8; c++) {
-                            const float4 t = lds128(row_addr + c * 16);
-                            p[c] = add2(make_float2(t.x, t.y), make_float2(t.z, t.w));
+                            for (int c = 0; c < 6; c++) {
+                                const float4 t = lds128(row_addr + c * 48);
+                                p[c] = add2(make_float2(t.x, t.y), make_float2(t.z, t.w));
+                            }
+                            part = add2(add2(add2(p[0], p[1]), add2(p[2], p[3])), add2(p[4], p[5]));
                         }
-                        const float2 sum = add2(add2(add2(p[0], p[1]), add2(p[2], p[3])), add2(add2(p[4], p[5]), add2(p[6], p[7])));
-                        red_add2(gbase + (size_t)splat * (sizeof(GradRec2) / 4), sum);
+                        const float2 d1 = make_float2(__shfl_down_sync(0xffffffffu, part.x, 1), __shfl_down_sync(0xffffffffu, part.y, 1));
+                        const float2 d2 = make_float2(__shfl_down_sync(0xffffffffu, part.x, 2), __shfl_down_sync(0xffffffffu, part.y, 2));
+                        if (gbase != nullptr) red_add2(gbase + (size_t)splat * (sizeof(GradRec2) / 4), add2(part, add2(d1, d2)));
                     }
                 } else {
                     // one set: [9][RED_STRIDE] floats (conflict-free: bank = 4*row + lane), lane r adds up row r
