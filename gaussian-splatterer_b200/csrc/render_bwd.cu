@@ -52,35 +52,6 @@ constexpr int RED_STRIDE2 = 38;  // dual mode: float2 (white, black) per lane: 3
                                  // stride of 304 B = 48 mod 128 keeps the three readers of consecutive rows (48 contiguous bytes per row
                                  // and load) on different banks
 
-// Packed FP32 pairs (sm_100 FFMA2 / FMUL2 / FADD2): one issue slot for two IEEE round-to-nearest operations.  The
-// dual mode keeps every per-residual quantity as a (white, black) pair, so its arithmetic issues half the
-// instructions; a scalar operand is broadcast by the instruction itself (R.F32 operand form), not by a move.
-__device__ __forceinline__ unsigned long long pk(float2 v) {
-    unsigned long long r;
-    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(v.x), "f"(v.y));
-    return r;
-}
-__device__ __forceinline__ float2 upk(unsigned long long v) {
-    float2 r;
-    asm("mov.b64 {%0, %1}, %2;" : "=f"(r.x), "=f"(r.y) : "l"(v));
-    return r;
-}
-__device__ __forceinline__ float2 fma2(float2 a, float2 b, float2 c) {
-    unsigned long long r;
-    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(pk(a)), "l"(pk(b)), "l"(pk(c)));
-    return upk(r);
-}
-__device__ __forceinline__ float2 mul2(float2 a, float2 b) {
-    unsigned long long r;
-    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(pk(a)), "l"(pk(b)));
-    return upk(r);
-}
-__device__ __forceinline__ float2 add2(float2 a, float2 b) {
-    unsigned long long r;
-    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(pk(a)), "l"(pk(b)));
-    return upk(r);
-}
-__device__ __forceinline__ float2 dup2(float v) { return make_float2(v, v); }
 // shared-memory accesses through a 32-bit address computed once (kept opaque so it is not re-derived per entry)
 __device__ __forceinline__ void sts64(uint32_t addr, float2 v) {
     asm volatile("st.shared.v2.f32 [%0], {%1, %2};" ::"r"(addr), "f"(v.x), "f"(v.y) : "memory");

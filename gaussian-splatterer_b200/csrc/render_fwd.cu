@@ -26,6 +26,13 @@ namespace {
 
 constexpr int WB = 32;   // list entries per warp-private chunk (one per lane)
 
+// 1: both pixels of a lane are evaluated in one straight-line pass with packed FP32 pairs (FFMA2 / FMUL2 / FADD2, IEEE
+// round-to-nearest like the scalar intrinsics, so every bit of T / colour / n_contrib is unchanged); a pixel that does
+// not blend the entry runs with alpha = 0, which leaves T (T * 1) and the colour (C + T * 0) bit for bit unchanged.
+#ifndef GSB_FWD_CONV
+#define GSB_FWD_CONV 1
+#endif
+
 __global__ void __launch_bounds__(RENDER_THREADS) render_fwd_kernel(const RenderFwdArgs a) {
     __shared__ SplatRec s_rec[RENDER_WARPS][2][WB];
     __shared__ uint32_t s_max;
@@ -38,6 +45,7 @@ __global__ void __launch_bounds__(RENDER_THREADS) render_fwd_kernel(const Render
     const int pix_y[2] = {by0 + (lane >> 3), by0 + (lane >> 3) + 4};
     const float pxf = (float)pix_x;
     const float pyf[2] = {(float)pix_y[0], (float)pix_y[1]};
+    const float2 npy2 = make_float2(-pyf[0], -pyf[1]);
     const float bcx = (float)bx0 + 3.5f, bcy = (float)by0 + 3.5f;   // sub-block centre
     bool done[2];
     float T[2] = {1.0f, 1.0f}, Cr[2] = {0.f, 0.f}, Cg[2] = {0.f, 0.f}, Cb[2] = {0.f, 0.f};
@@ -100,6 +108,33 @@ __global__ void __launch_bounds__(RENDER_THREADS) render_fwd_kernel(const Render
                 const float dx = __fsub_rn(ra.x, pxf);
                 const float bx = __fmul_rn(dx, ra.z);
                 const float cxy = __fmul_rn(dx, ra.w);
+#if GSB_FWD_CONV
+                // power = -0.5 (cx dx^2 + cz dy^2) - cy dx dy for both pixels, in the reference's evaluation order
+                const float2 dy2 = add2(dup2(ra.y), npy2);                      // ra.y - py
+                const float2 ay2 = mul2(dy2, mul2(dy2, dup2(rb.x)));
+                const float2 pw2 = fma2(fma2(dup2(dx), dup2(bx), ay2), dup2(-0.5f), mul2(dy2, dup2(-cxy)));
+                const bool pass0 = !done[0] && !(pw2.x < rc.y) && !(pw2.x > 0.0f);
+                const bool pass1 = !done[1] && !(pw2.y < rc.y) && !(pw2.y > 0.0f);
+                if (!__any_sync(0xffffffffu, pass0 || pass1)) continue;
+                const float a0 = fminf(0.99f, __fmul_rn(rb.y, expf(pw2.x)));
+                const float a1 = fminf(0.99f, __fmul_rn(rb.y, expf(pw2.y)));
+                const bool hit0 = pass0 && !(a0 < 1.0f / 255.0f), hit1 = pass1 && !(a1 < 1.0f / 255.0f);
+                if (!__any_sync(0xffffffffu, hit0 || hit1)) continue;
+                const float2 T2 = make_float2(T[0], T[1]);
+                const float2 test2 = mul2(T2, add2(dup2(1.0f), make_float2(hit0 ? -a0 : -0.0f, hit1 ? -a1 : -0.0f)));
+                const bool stop0 = hit0 && test2.x < 0.0001f, stop1 = hit1 && test2.y < 0.0001f;
+                const bool do0 = hit0 && !stop0, do1 = hit1 && !stop1;
+                const float2 al2 = make_float2(do0 ? a0 : 0.0f, do1 ? a1 : 0.0f);
+                float2 c2;
+                c2 = fma2(T2, mul2(al2, dup2(rb.z)), make_float2(Cr[0], Cr[1])); Cr[0] = c2.x; Cr[1] = c2.y;
+                c2 = fma2(T2, mul2(al2, dup2(rb.w)), make_float2(Cg[0], Cg[1])); Cg[0] = c2.x; Cg[1] = c2.y;
+                c2 = fma2(T2, mul2(al2, dup2(rc.x)), make_float2(Cb[0], Cb[1])); Cb[0] = c2.x; Cb[1] = c2.y;
+                const uint32_t pos = (uint32_t)(i * WB + j + 1);
+                if (do0) { T[0] = test2.x; last[0] = pos; }
+                if (do1) { T[1] = test2.y; last[1] = pos; }
+                done[0] = done[0] || stop0;
+                done[1] = done[1] || stop1;
+#else
 #pragma unroll
                 for (int k = 0; k < 2; k++) {
                     if (done[k]) continue;
@@ -122,6 +157,7 @@ __global__ void __launch_bounds__(RENDER_THREADS) render_fwd_kernel(const Render
                     T[k] = test_T;
                     last[k] = (uint32_t)(i * WB + j + 1);
                 }
+#endif
             }
         }
     }
