@@ -250,14 +250,14 @@ __global__ void __launch_bounds__(RENDER_THREADS, GSB_BWD_CTAS) render_bwd_kerne
                     // which leaves T and SD bit for bit unchanged (1 / (1 - 0) = 1, w = 0) and contributes zero sums.
                     float pw[2], dyv[2];
                     bool pass[2];
+                    {
+                        // power of both pixels with packed pairs, in the forward's evaluation order (bit-identical)
+                        const float2 dy2 = add2(dup2(ra.y), make_float2(-pyf[0], -pyf[1]));
+                        const float2 ay2 = mul2(dy2, mul2(dy2, dup2(rb.x)));
+                        const float2 pw2 = fma2(fma2(dup2(dx), dup2(bx), ay2), dup2(-0.5f), mul2(dy2, dup2(-cxy)));
+                        pw[0] = pw2.x; pw[1] = pw2.y; dyv[0] = dy2.x; dyv[1] = dy2.y;
 #pragma unroll
-                    for (int k = 0; k < 2; k++) {
-                        const float dy = __fsub_rn(ra.y, pyf[k]);
-                        const float ay = __fmul_rn(dy, __fmul_rn(dy, rb.x));
-                        const float power = __fmaf_rn(__fmaf_rn(dx, bx, ay), -0.5f, -__fmul_rn(dy, cxy));
-                        pass[k] = (idx < ncontrib[k]) && !(power < rc.y) && !(power > 0.0f);
-                        pw[k] = power;
-                        dyv[k] = dy;
+                        for (int k = 0; k < 2; k++) pass[k] = (idx < ncontrib[k]) && !(pw[k] < rc.y) && !(pw[k] > 0.0f);
                     }
                     if (!__any_sync(0xffffffffu, pass[0] || pass[1])) continue;
                     float G[2], alpha[2];
