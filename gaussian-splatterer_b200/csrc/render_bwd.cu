@@ -40,6 +40,9 @@
 
 namespace {
 
+#ifndef GSB_BWD_VOTE2
+#define GSB_BWD_VOTE2 0   // second vote after the alpha test (exits in < 1 % of the cases; without it such an entry adds zeros)
+#endif
 #ifndef GSB_BWD_CONV
 #define GSB_BWD_CONV 1   // fused mode: straight-line evaluation of both pixels of a lane
 #endif
@@ -271,7 +274,9 @@ __global__ void __launch_bounds__(RENDER_THREADS, GSB_BWD_CTAS) render_bwd_kerne
                         alpha[k] = h ? al : 0.f;
                         hit = hit || h;
                     }
+#if GSB_BWD_VOTE2
                     if (!__any_sync(0xffffffffu, hit)) continue;
+#endif
                     float2 sA, sB, sC, sr, sg, sb;
 #pragma unroll
                     for (int k = 0; k < 2; k++) {
