@@ -187,9 +187,15 @@ class Trainer:
             return
         arr_w = (C.c_void_p * max(n, 1))(*[t.data_ptr() for t in self.truthFrameBuffersW])
         arr_b = (C.c_void_p * max(n, 1))(*[t.data_ptr() for t in self.truthFrameBuffersB])
-        cams = (CameraC * max(n, 1))()
-        for k, cam in enumerate(self.truthCameras):
-            cams[k] = camera_struct(cam.view_constants(self.width, self.height, self.square_fov))
+        # the camera constants depend on the camera objects only: when a caller just swaps frame buffers (double-buffered
+        # uploads) they are not recomputed
+        cam_sig = (sig[2], self.width, self.height, self.square_fov)
+        if getattr(self, "_cam_sig", None) != cam_sig:
+            cams = (CameraC * max(n, 1))()
+            for k, cam in enumerate(self.truthCameras):
+                cams[k] = camera_struct(cam.view_constants(self.width, self.height, self.square_fov))
+            self._cam_sig, self._cam_structs = cam_sig, cams
+        cams = self._cam_structs
         check(lib().gsb_trainer_set_truths(self._h, n, arr_w, arr_b, cams, self._total_cameras or n))
         self._truth_sig = sig
 
