@@ -120,7 +120,7 @@ __device__ __forceinline__ void pb_red4(float* p, float x, float y, float z, flo
     asm volatile("red.global.v4.f32.add [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(x), "f"(y), "f"(z), "f"(w) : "memory");
 }
 #ifndef GSB_PB_THREADS
-#define GSB_PB_THREADS 256
+#define GSB_PB_THREADS 128   // 95 registers: five 128-thread blocks per SM against two of 256
 #define GSB_PB_BLOCKS 1
 #endif
 template <int NS, bool M4>
