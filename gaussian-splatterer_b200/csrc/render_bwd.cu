@@ -43,6 +43,9 @@ namespace {
 #ifndef GSB_BWD_VOTE2
 #define GSB_BWD_VOTE2 0   // second vote after the alpha test (exits in < 1 % of the cases; without it such an entry adds zeros)
 #endif
+#ifndef GSB_BWD_DIRECT
+#define GSB_BWD_DIRECT 4   // measured: 4 - 6 best (-1.5 %), 12 loses 8 % (same-address REDs serialise in L2)
+#endif
 #ifndef GSB_BWD_CONV
 #define GSB_BWD_CONV 1   // fused mode: straight-line evaluation of both pixels of a lane
 #endif
@@ -246,6 +249,7 @@ __global__ void __launch_bounds__(RENDER_THREADS, GSB_BWD_CTAS) render_bwd_kerne
                 // share dx, so the dx factors of the six moments are applied once after the pixel loop) and
                 // the three colour sums.  NS == 2: every one of them is a (white, black) pair.
                 float mA[NS], mB[NS], mC[NS], vr[NS], vg[NS], vb[NS];
+                bool lane_hit = false;
 #if GSB_BWD_CONV
                 if constexpr (NS == 2) {
                     // Both pixels of the lane in one straight-line pass (no divergent per-pixel blocks: the two
@@ -274,6 +278,7 @@ __global__ void __launch_bounds__(RENDER_THREADS, GSB_BWD_CTAS) render_bwd_kerne
                         alpha[k] = h ? al : 0.f;
                         hit = hit || h;
                     }
+                    lane_hit = hit;
 #if GSB_BWD_VOTE2
                     if (!__any_sync(0xffffffffu, hit)) continue;
 #endif
@@ -355,6 +360,31 @@ __global__ void __launch_bounds__(RENDER_THREADS, GSB_BWD_CTAS) render_bwd_kerne
                 }
                 if (!__any_sync(0xffffffffu, hit)) continue;
                 }
+#if GSB_BWD_DIRECT > 0
+                if constexpr (NS == 2) {
+                    // entries at most GSB_BWD_DIRECT lanes blended: those lanes add their nine pairs themselves (nine 64-bit REDs,
+                    // no shared-memory round trip: the shared-memory data pipe bounds this kernel)
+                    const uint32_t hits = __ballot_sync(0xffffffffu, lane_hit);
+                    if (__popc(hits) <= GSB_BWD_DIRECT) {
+                        if (lane_hit) {
+                            float* g = reinterpret_cast<float*>(a.grads2 + splat);
+                            const float2 dx2 = dup2(dx);
+                            const float2 A2 = make_float2(mA[0], mA[1]), B2 = make_float2(mB[0], mB[1]);
+                            const float2 ax = mul2(A2, dx2);
+                            red_add2(g + 0, A2);
+                            red_add2(g + 2, ax);
+                            red_add2(g + 4, B2);
+                            red_add2(g + 6, mul2(ax, dx2));
+                            red_add2(g + 8, mul2(B2, dx2));
+                            red_add2(g + 10, make_float2(mC[0], mC[1]));
+                            red_add2(g + 12, make_float2(vr[0], vr[1]));
+                            red_add2(g + 14, make_float2(vg[0], vg[1]));
+                            red_add2(g + 16, make_float2(vb[0], vb[1]));
+                        }
+                        continue;
+                    }
+                }
+#endif
                 if constexpr (NS == 2) {
                     // Transposed reduction through shared memory: every lane parks its nine (white, black) pairs in
                     // column `lane` of the warp's [9][RED_STRIDE2] panel with 64-bit stores; lanes 3r, 3r + 1, 3r + 2
