@@ -24,6 +24,7 @@ cpu_baseline  the scalar C++ oracle (oracle/liboracle.so, one host thread) on ON
         no CPU path, its own code for this path is CUDA (north_star).
 """
 import argparse
+import ctypes as C
 import importlib
 import json
 import os
@@ -61,6 +62,9 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-fuse", action="store_true", help="one full pass per (camera, background) like the reference")
+    ap.add_argument("--torch-allreduce", action="store_true", help="A/B: torch.distributed.all_reduce through the hook instead of gsb_comm_*")
+    ap.add_argument("--no-mgpu-check", action="store_true", help="skip the N > 1 correctness job (tests/mgpu_check.py)")
+    ap.add_argument("--densify-every", type=int, default=0, help="densify every k-th step inside the timed loop (C5 as written)")
     return ap.parse_args()
 
 
@@ -143,15 +147,21 @@ def init_dist(args):
 
 
 # ---------------------------------------------------------------------------------------------
-def build_scene(gsb, args, rank, world):
-    """Student cloud, teacher cloud and the camera set of the config; cameras sharded by rank."""
+def build_scene(gsb, args, rank, world, reference_cameras=False):
+    """Student cloud, teacher cloud and the camera set of the config; cameras sharded by rank.
+    reference_cameras: the camera set comes from the reference's own Camera.cpp (oracle/_ref/libgsrefcam.so) instead of the
+    product's host code, so the reference arm never loads libgsb200.so (the two agree bit for bit: tests/test_host_logic.py)."""
     cfg = args.config
     W, H, P = gsb.synth.CONFIGS[cfg]
     project = gsb.synth.project_for(cfg)
     if args.cameras > 0:
         project.sphere1.count = args.cameras
         project.sphere2.count = args.cameras if project.sphere2.count > 0 else 0
-    cams = gsb.Camera.getCameras(project)
+    if reference_cameras:
+        from oracle import refshim
+        cams = [gsb.Camera(loc, (0.0, 0.0, 0.0), fov) for loc, fov in refshim.ref_cameras(project)]
+    else:
+        cams = gsb.Camera.getCameras(project)
     seed = 0x5EED0000 + int(cfg[1])
     cloud = gsb.synth.splat_cloud(P, seed)
     teacher = gsb.synth.splat_cloud(P // 2, seed + 1)
@@ -205,6 +215,12 @@ STREAM_BYTES = {  # algorithmic bytes per view pass and stage group, SURVEY.md 8
     "binning": lambda c: 8 * c["P"] + 20 * c["P"] + 12 * c["R"] + 152 * c["R"] + 8 * c["R"] + 16 * c["tiles"],
     "preprocess_bwd": lambda c: (92 + 243) * c["Pv"] + 284 * c["P"],
 }
+
+
+def workload_text(cfg, n_total, views_per_step, W, Hh, P):
+    """config.workload, identical in both arms (the driver compares the strings)."""
+    return (f"{cfg}: {n_total} cameras x 2 backgrounds = {views_per_step} view passes per step, {W}x{Hh}, {P} splats, "
+            f"SH degree 1")
 
 
 def fused_step_bytes(c):
@@ -314,6 +330,8 @@ def run_gsb(args):
     cloud = scene["cloud"]
     host = gsb.ModelSplatsHost.from_arrays(*[cloud[k] for k in ("locations", "shs", "scales", "opacities", "rotations")])
 
+    comm = gsb.Comm.from_torch_distributed(dist, dev) if (world > 1 and not args.torch_allreduce) else None
+
     def new_trainer():
         tr = gsb.Trainer(W, Hh, dev)
         tr.set_fuse_backgrounds(not args.no_fuse)
@@ -321,22 +339,49 @@ def run_gsb(args):
         tr.model = gsb.ModelSplatsDevice(host, dev)
         tr.truthFrameBuffersW, tr.truthFrameBuffersB, tr.truthCameras = list(tw), list(tb), mine
         if world > 1:
-            tr.set_allreduce(lambda t: dist.all_reduce(t, op=dist.ReduceOp.SUM))
+            if args.torch_allreduce:
+                tr.set_allreduce(lambda t: dist.all_reduce(t, op=dist.ReduceOp.SUM))
+            else:
+                tr.set_comm(comm)                  # the library's own NCCL communicator
         return tr
 
     # ---- value: inputs resident in HBM ------------------------------------------------------
     tr = new_trainer()
     for _ in range(args.warmup):
         tr.train(project, False)
+    densify_info = None
+    if args.densify_every > 0:
+        # "densify/split/cull compaction enabled" (BASELINE config 5): thresholds at quantiles of the current decision
+        # variables so that every densify splits / clones ~2 % and culls ~2 % of the splats.  Every rank holds the same
+        # all-reduced means and the same parameters, so every rank derives the same thresholds.
+        torch.cuda.synchronize()
+        a = tr.grad_tensor().cpu().numpy()
+        Pn = tr.model.count
+        score = a[:Pn].astype(np.float64) - np.linalg.norm(a[Pn:4 * Pn].astype(np.float64).reshape(-1, 3), axis=1)
+        project.paramDensifyVariance = float(np.quantile(score, 0.98))
+        project.paramCullOpacity = float(np.quantile(tr.model.devOpacities.cpu().numpy(), 0.02))
+        project.paramSplitSize = float(np.median(np.linalg.norm(tr.model.devScales.cpu().numpy().reshape(-1, 3), axis=1)))
+        densify_info = {"every": args.densify_every, "count_before": int(Pn),
+                        "thresholds": [project.paramDensifyVariance, project.paramCullOpacity, project.paramSplitSize]}
+    do_densify = (lambda k: (k + 1) % args.densify_every == 0) if args.densify_every > 0 else (lambda k: False)
     launches0 = tr.stats()["kernel_launches"]
     sampler = ClockSampler(gpu_identifier(torch, local))
     if rank == 0:
         sampler.start()
-    ms = timed_steps(torch, dist, lambda k: tr.train(project, False), args.steps)
+    ms = timed_steps(torch, dist, lambda k: tr.train(project, do_densify(k)), args.steps)
     clocks = sampler.stop() if rank == 0 else None
     stats = tr.stats()
     launches = stats["kernel_launches"] - launches0
     value = views_per_step * args.steps / (ms / 1000.0)
+    if densify_info is not None:
+        densify_info["count_after"] = int(tr.model.count)
+        if world > 1:       # replicas must still be bit-identical after densifying inside the timed loop
+            import mgpu_check
+            cs = torch.tensor(mgpu_check._checksum(torch, tr.model), dtype=torch.int64, device=dev)
+            gathered = [torch.zeros_like(cs) for _ in range(world)]
+            dist.all_gather(gathered, cs)
+            densify_info["replicas_identical_after_run"] = all(bool(torch.equal(g, gathered[0])) for g in gathered)
+        P = int(tr.model.count)
 
     # ---- per-kernel launch times, live: the same K steps again with every stage of every view pass
     # bracketed by CUDA events on the launching stream.  Stage timing serialises the kernels (in the
@@ -356,7 +401,30 @@ def run_gsb(args):
     fused = not args.no_fuse
     units = 2 if fused else 1                     # view passes one launch of a stage serves
     per_launch = {k: v / max(passes, 1) for k, v in stage_ms.items()}
+    fp32_meas = (C.c_double * 2)()
+    if L.gsb_measure_fp32_peak(fp32_meas, None) != 0:
+        fp32_meas[0] = fp32_meas[1] = 0.0
     tr.close()
+
+    # ---- the same steps with one full pass per (camera, background), the reference's order ----
+    unfused = None
+    if fused and not args.no_e2e and args.densify_every == 0:
+        tr = new_trainer()
+        tr.set_fuse_backgrounds(False)
+        for _ in range(args.warmup):
+            tr.train(project, False)
+        k_u = max(2, args.steps // 2)
+        ms_u = timed_steps(torch, dist, lambda k: tr.train(project, False), k_u)
+        unfused = {"value": views_per_step * k_u / (ms_u / 1000.0), "unit": UNIT, "ms_per_step": ms_u / k_u, "steps": k_u,
+                   "what": "one forward + one backward walk per (camera, background) in the reference's order "
+                           "(gsb_trainer_set_fuse_backgrounds(0)); `value` above shares them between a camera's two passes"}
+        tr.close()
+
+    # ---- N > 1: the correctness job (bit-identical replicas, equal to N = 1, with a densify) ----------------
+    mgpu = None
+    if world > 1 and not args.no_mgpu_check and not args.torch_allreduce:
+        import mgpu_check
+        mgpu = mgpu_check.run_check(torch, dist, rank, world, local, config="C4", cameras=8)
 
     # ---- e2e: truth frames in pinned host memory, uploaded every step, loss read back --------
     e2e = None
@@ -416,7 +484,8 @@ def run_gsb(args):
     hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
     hbm_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650 GB/s"
     sm_max = float((clocks or {}).get("sm_max_mhz") or peaks.get("sm_max_mhz", 1965.0))
-    fp32_peak = 2 * 128 * 148 * sm_max * 1e6 / 1e12
+    fp32_nominal = 2 * 128 * 148 * sm_max * 1e6 / 1e12
+    fp32_peak = float(fp32_meas[0]) if fp32_meas[0] > 0 else fp32_nominal    # measured FFMA issue peak (csrc/measure.cu)
     traffic = None
     try:
         traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
@@ -446,10 +515,11 @@ def run_gsb(args):
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"{args.config}: {n_total} cameras x 2 backgrounds = {views_per_step} view passes per step, "
-                               f"{W}x{Hh}, {P} splats, SH degree 1; cameras partitioned over {world} GPU(s), splats replicated",
+        "config": {"workload": workload_text(args.config, n_total, views_per_step, W, Hh, P),
                    "views_per_step": views_per_step, "cameras_per_rank": n_local,
-                   "fused_white_black": fused, "parallelism": f"camera-sharded x{world}, NCCL all-reduce of 24 floats/splat",
+                   "fused_white_black": fused,
+                   "parallelism": f"cameras partitioned over {world} GPU(s), splats replicated; one NCCL all-reduce of 24 "
+                                  f"floats/splat per iteration issued by libgsb200.so itself (gsb_comm_*)",
                    "l2": "inputs larger than L2: every step streams > 1 GB of truth frames, parameters and per-view state "
                          "through the 126 MB L2; no explicit flush"},
         "gpu_launches": int(launches),
@@ -461,14 +531,28 @@ def run_gsb(args):
                      "traffic": traffic.get("render_bwd"),
                      "flops_per_launch": bwd_fl, "ms_per_launch": bwd_ms, "share_of_step": stages["render_bwd"]["share"],
                      "view_passes_per_launch": units,
-                     "peak_source": f"FP32 SIMT issue peak 2 x 128 lanes x 148 SMs x clocks.max.sm ({sm_max:.0f} MHz); no stage "
-                                    "is HBM- or tensor-bound at the top (SURVEY.md 8d), MEASURED_PEAKS.json holds no FP32 figure",
+                     "peak_source": "measured on this GPU in this run: FFMA-only kernel, 8 independent chains per thread "
+                                    "(gsb_measure_fp32_peak, csrc/measure.cu); MEASURED_PEAKS.json holds no FP32 SIMT figure and no "
+                                    "stage is HBM- or tensor-bound at the top (SURVEY.md 8d)" if fp32_meas[0] > 0 else "nominal",
+                     "fp32_peak_measured": float(fp32_meas[0]), "fp32x2_peak_measured": float(fp32_meas[1]),
+                     "fp32_peak_nominal": fp32_nominal,
+                     "fp32_peak_nominal_how": f"2 x 128 lanes x 148 SMs x clocks.max.sm ({sm_max:.0f} MHz)",
+                     "frac_is": "effective: the numerator counts the REFERENCE algorithm's FLOPs (SURVEY 8d) for the pairs it "
+                                "evaluates; this kernel culls most of them with bounding boxes and never executes them",
                      "step_hbm": {"bound": "hbm", "achieved": step_gbs, "peak": hbm_peak, "unit": "GB/s",
                                   "frac": step_gbs / hbm_peak, "bytes_per_step_per_rank": step_bytes, "peak_source": hbm_src}},
         "stages": stages,
         "stats": {"rendered_per_step": stats["rendered_total"], "retries": stats["retries"],
                   "ms_per_step_serialised_with_stage_events": ms_serial / args.steps},
     }
+    if unfused is not None:
+        out["unfused"] = unfused
+    if mgpu is not None:
+        out["replicas_identical"] = bool(mgpu.get("replicas_identical")) and bool(mgpu.get("rendered_match"))
+        out["vs_n1_rel"] = mgpu.get("vs_n1_rel")
+        out["mgpu_check"] = mgpu
+    if densify_info is not None:
+        out["densify"] = densify_info
     if e2e is not None:
         out["e2e"] = e2e
     if render_stats is not None:
@@ -494,12 +578,12 @@ def run_reference(args):
     torch.cuda.set_device(local)
     import helpers as H
     from oracle import refshim
-    gsb = H.gsb                                    # host-side scene / camera generation only
+    gsb = H.gsb                                    # pure-Python scene generation only: libgsb200.so is never loaded here
     if not refshim.available():
         emit({"impl": "reference", "unavailable": "oracle/_ref/libgsref.so was not built (needs /root/reference)"})
         return
     dev = f"cuda:{local}"
-    scene = build_scene(gsb, args, 0, 1)
+    scene = build_scene(gsb, args, 0, 1, reference_cameras=os.path.exists(refshim.REF_CAM_LIB))
     W, Hh, P = scene["W"], scene["H"], scene["P"]
     project = scene["project"]
     n_total = len(scene["cams"])
@@ -541,9 +625,9 @@ def run_reference(args):
         "impl": "reference", "metric": METRIC, "value": best["views_per_s"], "unit": UNIT, "n_gpus": 1,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": best["ms_per_step"], "higher_is_better": True,
         "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"{args.config}: {n_total} cameras x 2 backgrounds = {views_per_step} view passes per step, "
-                               f"{W}x{Hh}, {P} splats, SH degree 1; single GPU (the reference has no multi-GPU path)",
+        "config": {"workload": workload_text(args.config, n_total, views_per_step, W, Hh, P),
                    "views_per_step": views_per_step,
+                   "parallelism": "single GPU (the reference has no multi-GPU path)",
                    "variant": "best case for the reference: debug=false, pooled workspaces, no per-view cudaMalloc/cudaFree; "
                               "the as-shipped call sequence (debug=true, per-view malloc/free) is in `as_shipped`",
                    "l2": "inputs larger than L2"},

@@ -37,7 +37,8 @@ class StateView(C.Structure):
 class TrainerStats(C.Structure):
     """gsb_trainer_stats."""
     _fields_ = [("rendered_total", C.c_longlong), ("visible_total", C.c_longlong), ("views", C.c_int),
-                ("retries", C.c_int), ("kernel_launches", C.c_longlong), ("sum_sq_residual", C.c_double)]
+                ("retries", C.c_int), ("kernel_launches", C.c_longlong), ("sum_sq_residual", C.c_double),
+                ("epoch_wraps", C.c_longlong)]
 
 
 _lib = None
@@ -112,6 +113,25 @@ def lib():
     L.gsb_trainer_get_stage_times.restype = i
     L.gsb_trainer_count_pairs.argtypes = [vp, i, C.POINTER(C.c_ulonglong)]
     L.gsb_trainer_count_pairs.restype = i
+    L.gsb_comm_nccl_version.argtypes = [C.POINTER(i)]
+    L.gsb_comm_get_unique_id.argtypes = [vp]
+    L.gsb_comm_init.argtypes = [C.POINTER(vp), vp, i, i]
+    L.gsb_comm_init_all.argtypes = [C.POINTER(vp), i, C.POINTER(i)]
+    L.gsb_comm_destroy.argtypes = [vp]
+    L.gsb_comm_rank.argtypes = [vp]
+    L.gsb_comm_world.argtypes = [vp]
+    L.gsb_comm_device.argtypes = [vp]
+    L.gsb_comm_allreduce_sum.argtypes = [vp, vp, sz, vp]
+    L.gsb_comm_broadcast.argtypes = [vp, vp, sz, i, vp]
+    L.gsb_trainer_set_comm.argtypes = [vp, vp]
+    for _n in ("nccl_version", "get_unique_id", "init", "init_all", "destroy", "rank", "world", "device", "allreduce_sum",
+               "broadcast"):
+        getattr(L, "gsb_comm_" + _n).restype = i
+    L.gsb_trainer_set_comm.restype = i
+    L.gsb_measure_fp32_peak.argtypes = [C.POINTER(C.c_double), vp]
+    L.gsb_measure_fp32_peak.restype = i
+    L.gsb_trainer_debug_set_epoch.argtypes = [vp, C.c_uint]
+    L.gsb_trainer_debug_set_epoch.restype = i
     L.gsb_image_float_to_int.argtypes = [vp, vp, i, i, vp]
     L.gsb_image_float_to_int.restype = i
     L.gsb_image_int_to_loss.argtypes = [vp, vp, vp, i, i, vp]
@@ -126,6 +146,10 @@ EXPORTED_SYMBOLS = [
     "gsb_rasterizer_mark_visible", "gsb_rasterizer_state", "gsb_rasterizer_sorted_keys",
     "gsb_trainer_enable_loss", "gsb_trainer_set_fuse_backgrounds", "gsb_trainer_profile_pass",
     "gsb_trainer_set_stage_timing", "gsb_trainer_get_stage_times", "gsb_trainer_count_pairs", "gsb_trainer_set_overlap",
+    "gsb_trainer_debug_set_epoch", "gsb_measure_fp32_peak",
+    "gsb_comm_nccl_version", "gsb_comm_get_unique_id", "gsb_comm_init", "gsb_comm_init_all", "gsb_comm_destroy",
+    "gsb_comm_rank", "gsb_comm_world", "gsb_comm_device", "gsb_comm_allreduce_sum", "gsb_comm_broadcast",
+    "gsb_trainer_set_comm",
     "gsb_image_float_to_int", "gsb_image_int_to_loss",
     "gsb_trainer_create", "gsb_trainer_destroy", "gsb_trainer_bind_model", "gsb_trainer_set_truths",
     "gsb_trainer_set_grad_buffer", "gsb_trainer_grad_floats", "gsb_trainer_grad_buffer",

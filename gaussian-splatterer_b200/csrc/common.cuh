@@ -164,6 +164,7 @@ void launch_render_bwd(const RenderBwdArgs& a, cudaStream_t s);
 // algorithm defines them, for the FLOP side of the roofline.
 // out[6] += { E_eval_f, E_exp_f, E_blend_f, E_eval_b, E_exp_b, E_blend_b }
 void launch_count_pairs(const RenderFwdArgs& a, unsigned long long* out, cudaStream_t s);
+int gsb_measure_fp32_peak_impl(double* out2, cudaStream_t s);
 
 // preprocess_bwd.cu
 struct PreprocessBwdArgs {

@@ -57,7 +57,81 @@ __global__ void __launch_bounds__(256) count_pairs_kernel(const RenderFwdArgs a,
     }
 }
 
+// FP32 issue peak, measured: every thread runs 8 independent FFMA chains (scalar) or 8 independent packed FFMA2
+// chains (fma.rn.f32x2: two FMAs per issue slot) long enough for the launch overhead to vanish.  The render kernels'
+// roofline denominator is the scalar figure; the packed one shows what the f32x2 path could add on top.
+template <bool PACKED>
+__global__ void __launch_bounds__(256) ffma_peak_kernel(float* out, float a, float b, int iters) {
+    if constexpr (PACKED) {
+        unsigned long long x[8];
+        unsigned long long a2, b2;
+        asm("mov.b64 %0, {%1, %1};" : "=l"(a2) : "f"(a));
+        asm("mov.b64 %0, {%1, %1};" : "=l"(b2) : "f"(b));
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+            const float v = (float)(threadIdx.x + k) * 1e-3f;
+            asm("mov.b64 %0, {%1, %1};" : "=l"(x[k]) : "f"(v));
+        }
+        for (int i = 0; i < iters; i++) {
+#pragma unroll
+            for (int u = 0; u < 4; u++)
+#pragma unroll
+                for (int k = 0; k < 8; k++) asm volatile("fma.rn.f32x2 %0, %0, %1, %2;" : "+l"(x[k]) : "l"(a2), "l"(b2));
+        }
+        unsigned long long acc = 0;
+#pragma unroll
+        for (int k = 0; k < 8; k++) acc ^= x[k];
+        if (acc == 0x123456789abcdef0ull) out[0] = 1.0f;
+    } else {
+        float x[8];
+#pragma unroll
+        for (int k = 0; k < 8; k++) x[k] = (float)(threadIdx.x + k) * 1e-3f;
+        for (int i = 0; i < iters; i++) {
+#pragma unroll
+            for (int u = 0; u < 4; u++)
+#pragma unroll
+                for (int k = 0; k < 8; k++) asm volatile("fma.rn.f32 %0, %0, %1, %2;" : "+f"(x[k]) : "f"(a), "f"(b));
+        }
+        float acc = 0.f;
+#pragma unroll
+        for (int k = 0; k < 8; k++) acc += x[k];
+        if (acc == 12345.678f) out[0] = acc;
+    }
+}
+
 }  // namespace
+
+// out2[0] = scalar FFMA TFLOP/s, out2[1] = packed FFMA2 TFLOP/s (2 FLOP per FMA), best of `reps` timed launches each.
+int gsb_measure_fp32_peak_impl(double* out2, cudaStream_t s) {
+    int dev = 0, sms = 0;
+    GSB_CUDA_OK(cudaGetDevice(&dev));
+    GSB_CUDA_OK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    float* d_out = nullptr;
+    GSB_CUDA_OK(cudaMalloc(&d_out, sizeof(float)));
+    cudaEvent_t e0, e1;
+    GSB_CUDA_OK(cudaEventCreate(&e0));
+    GSB_CUDA_OK(cudaEventCreate(&e1));
+    const int blocks = sms * 8, threads = 256, iters = 4096, reps = 5;
+    for (int mode = 0; mode < 2; mode++) {
+        double best = 0.0;
+        for (int r = 0; r < reps + 1; r++) {                      // first launch is the warm-up
+            GSB_CUDA_OK(cudaEventRecord(e0, s));
+            if (mode == 0) ffma_peak_kernel<false><<<blocks, threads, 0, s>>>(d_out, 0.999f, 1e-3f, iters);
+            else ffma_peak_kernel<true><<<blocks, threads, 0, s>>>(d_out, 0.999f, 1e-3f, iters);
+            GSB_CUDA_OK(cudaEventRecord(e1, s));
+            GSB_CUDA_OK(cudaEventSynchronize(e1));
+            float ms = 0.f;
+            GSB_CUDA_OK(cudaEventElapsedTime(&ms, e0, e1));
+            const double fma = (double)blocks * threads * (double)iters * 32.0 * (mode == 0 ? 1.0 : 2.0);
+            const double tf = 2.0 * fma / (ms * 1e-3) / 1e12;
+            if (r > 0 && tf > best) best = tf;
+        }
+        out2[mode] = best;
+    }
+    cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(d_out);
+    GSB_CUDA_OK(cudaGetLastError());
+    return 0;
+}
 
 void launch_count_pairs(const RenderFwdArgs& a, unsigned long long* out, cudaStream_t s) {
     count_pairs_kernel<<<dim3(a.grid_x, a.grid_y), 256, 0, s>>>(a, out);

@@ -131,6 +131,7 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(const PreprocessArg
 
     float cov[6];
     float ix = 0.f, iy = 0.f, conx = 0.f, cony = 0.f, conz = 0.f, covx = 0.f, covy = 0.f;
+    bool pos_def = true;
     if (alive) {
         const float hx = affine_row(px, py, pz, __ldg(Pm + 0), __ldg(Pm + 4), __ldg(Pm + 8), __ldg(Pm + 12));
         const float hy = affine_row(px, py, pz, __ldg(Pm + 1), __ldg(Pm + 5), __ldg(Pm + 9), __ldg(Pm + 13));
@@ -186,6 +187,7 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(const PreprocessArg
             cony = mul_(cxy, -det_inv);
             conz = mul_(cxx, det_inv);
             covx = cxx; covy = cyy;
+            pos_def = det > 0.0f && cxx > 0.0f && cyy > 0.0f;
             const float mid = mul_(add_(cxx, cyy), 0.5f);
             const float sq = __fsqrt_rn(fmaxf(fma_(mid, mid, -det), 0.1f));
             const float lam = fmaxf(add_(mid, sq), sub_(mid, sq));
@@ -234,7 +236,9 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(const PreprocessArg
         const float k = -2.0f * (lim - 0.05f);
         ex = sqrtf(fmaxf(k * covx, 0.f)) * 1.001f + 0.01f;
         ey = sqrtf(fmaxf(k * covy, 0.f)) * 1.001f + 0.01f;
-        if (!(ex == ex) || !(ey == ey)) { ex = 1e30f; ey = 1e30f; }     // NaN covariance: never cull
+        // NaN covariance, or a conic that is not positive definite (a caller's cov3D_precomp can produce det < 0:
+        // { power >= lim } is then unbounded): never cull by the box, only by the exact threshold on power
+        if (!(ex == ex) || !(ey == ey) || !pos_def) { ex = 1e30f; ey = 1e30f; }
     }
     SplatRec rec;
     rec.a = make_float4(ix, iy, conx, cony);

@@ -249,6 +249,11 @@ int gsb_rasterizer_sorted_keys(int P, int width, int height, int R, char* geom_b
     return GSB_OK;
 }
 
+int gsb_measure_fp32_peak(double* out2, void* stream) {
+    if (!out2) return gsb_fail_msg("gsb_measure_fp32_peak: null argument");
+    return gsb_measure_fp32_peak_impl(out2, (cudaStream_t)stream);
+}
+
 int gsb_image_float_to_int(const float* dev_src, uint32_t* dev_fb, int w, int h, void* stream) {
     launch_image_float_to_int(dev_src, dev_fb, w, h, (cudaStream_t)stream);
     GSB_CUDA_OK(cudaGetLastError());

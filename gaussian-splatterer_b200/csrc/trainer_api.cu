@@ -76,6 +76,7 @@ struct gsb_trainer {
     uint32_t n_keep = 0, n_split_done = 0, n_clone_done = 0;
 
     gsb_allreduce_fn allreduce = nullptr; void* allreduce_user = nullptr;
+    gsb_comm* comm = nullptr;         // gsb_trainer_set_comm: native NCCL exchange, takes precedence over the hook
     bool loss_on = false; double* d_loss = nullptr;
     gsb_trainer_stats stats;
 
@@ -155,6 +156,28 @@ int ensure_avg(gsb_trainer* t) {
     return GSB_OK;
 }
 
+// Look-back status words carry a 30-bit epoch tag (binning.cu lb_pack) so the status arrays never need clearing
+// between launches.  Before the tag would wrap, every stream is drained, all look-back arrays are cleared and the
+// counter restarts (one view pass consumes at most 9 epochs, a densify 1).
+constexpr uint32_t GSB_EPOCH_LIMIT = 0x3FFFFFFFu - 64u;
+
+int epoch_guard(gsb_trainer* t) {
+    if (t->epoch < GSB_EPOCH_LIMIT) return GSB_OK;
+    GSB_CUDA_OK(cudaStreamSynchronize(t->stream));
+    if (t->sF) GSB_CUDA_OK(cudaStreamSynchronize(t->sF));
+    if (t->sB) GSB_CUDA_OK(cudaStreamSynchronize(t->sB));
+    save_slot(t);
+    for (int k = 0; k < 2; k++) {
+        const gsb_trainer::ViewSlot& v = t->slot[k];
+        if (v.geom) GSB_CUDA_OK(cudaMemset(v.g.lookback, 0, GeomWs::lookback_tiles(t->geom_P) * 256 * sizeof(unsigned long long)));
+        if (v.bin) GSB_CUDA_OK(cudaMemset(v.b.lookback, 0, BinWs::lookback_tiles(t->r_cap) * 256 * sizeof(unsigned long long)));
+    }
+    if (t->dens_lb) GSB_CUDA_OK(cudaMemset(t->dens_lb, 0, ((t->dens_P + 1023) / 1024 + 1) * 4 * sizeof(unsigned long long)));
+    t->epoch = 0;
+    t->stats.epoch_wraps++;
+    return GSB_OK;
+}
+
 // Stage boundaries of one view pass (gsb_trainer_profile_pass reports the time between them).
 enum { ST_CLEAR = 0, ST_PREPROCESS, ST_DEPTH_SORT, ST_SCAN, ST_EMIT, ST_TILE_SORT, ST_RANGES, ST_RENDER_FWD,
        ST_RENDER_BWD, ST_PREPROCESS_BWD, ST_COUNT };
@@ -171,6 +194,7 @@ int forward_pass(gsb_trainer* t, const float* view, const float* projview, const
     const int grid_x = (W + GSB_TILE - 1) / GSB_TILE, grid_y = (H + GSB_TILE - 1) / GSB_TILE;
     const int tiles = grid_x * grid_y;
     const int P = t->count;
+    if (int e = epoch_guard(t)) return e;
     mark(ev, ST_CLEAR, s);
     GSB_CUDA_OK(cudaMemsetAsync(t->g.ctrl, 0, sizeof(GsbCtrl), s));
     GSB_CUDA_OK(cudaMemsetAsync(im.ranges, 0, (size_t)tiles * sizeof(uint2), s));
@@ -366,6 +390,10 @@ int gsb_trainer_set_truths(gsb_trainer* t, int n, const uint32_t* const* devW, c
     if (!t || n < 0 || (n > 0 && (!devW || !devB || !cameras))) return gsb_fail_msg("gsb_trainer_set_truths: invalid argument");
     t->truthW.assign(devW, devW + n);
     t->truthB.assign(devB, devB + n);
+    // Trainer::train hands the same cameras over on every iteration (compat/Trainer.cpp, app_driver.cpp): the device
+    // copy and its synchronisation are skipped when nothing changed
+    const bool same_cams = t->d_cams && (size_t)n == t->cams.size() && (size_t)n <= t->d_cams_cap &&
+                           (n == 0 || memcmp(t->cams.data(), cameras, (size_t)n * sizeof(gsb_camera)) == 0);
     t->cams.assign(cameras, cameras + n);
     t->total_cameras = total_cameras > 0 ? total_cameras : n;
     if ((size_t)n > t->d_cams_cap) {
@@ -373,7 +401,7 @@ int gsb_trainer_set_truths(gsb_trainer* t, int n, const uint32_t* const* devW, c
         GSB_CUDA_OK(cudaMalloc(&t->d_cams, (size_t)n * sizeof(gsb_camera)));
         t->d_cams_cap = (size_t)n;
     }
-    if (n > 0) {
+    if (n > 0 && !same_cams) {
         GSB_CUDA_OK(cudaMemcpyAsync(t->d_cams, cameras, (size_t)n * sizeof(gsb_camera), cudaMemcpyHostToDevice, t->stream));
         GSB_CUDA_OK(cudaStreamSynchronize(t->stream));   // `cameras` may be a temporary
     }
@@ -400,6 +428,12 @@ int gsb_trainer_set_allreduce(gsb_trainer* t, gsb_allreduce_fn fn, void* user) {
 }
 
 
+int gsb_trainer_set_comm(gsb_trainer* t, gsb_comm* comm) {
+    if (!t) return gsb_fail_msg("gsb_trainer_set_comm: null trainer");
+    t->comm = comm;
+    return GSB_OK;
+}
+
 int gsb_trainer_set_fuse_backgrounds(gsb_trainer* t, int on) {
     if (!t) return gsb_fail_msg("gsb_trainer_set_fuse_backgrounds: null trainer");
     t->fuse_wb = on != 0;
@@ -424,9 +458,18 @@ int gsb_trainer_accumulate(gsb_trainer* t) {
         gsb_fail_msg("Can't run training iteration, no truth data available!");   // src/Trainer.cu:253
         return GSB_ERR_STATE;
     }
-    if (t->count <= 0 || !t->loc) { gsb_fail_msg("gsb_trainer_accumulate: no model bound"); return GSB_ERR_STATE; }
+    if (t->count < 0 || (t->count > 0 && !t->loc)) { gsb_fail_msg("gsb_trainer_accumulate: no model bound"); return GSB_ERR_STATE; }
     cudaStream_t s = t->stream;
     const int n = (int)t->truthW.size();
+    if (t->count == 0) {
+        // the reference's temporary 0-splat model (src/Trainer.cu:112) or a densify that culled everything: every
+        // kernel of the iteration runs over zero splats, i.e. nothing happens
+        t->stats.retries = 0;
+        t->stats.rendered_total = 0;
+        t->stats.views = 2 * n;
+        t->stats.sum_sq_residual = 0.0;
+        return GSB_OK;
+    }
     const int P = t->count;
     if (int e = ensure_geom(t, (size_t)P)) return e;
     if (int e = ensure_avg(t)) return e;
@@ -534,6 +577,12 @@ int gsb_trainer_profile_pass(gsb_trainer* t, int pass_index, float* stage_ms, un
     return GSB_OK;
 }
 
+int gsb_trainer_debug_set_epoch(gsb_trainer* t, unsigned int epoch) {
+    if (!t) return gsb_fail_msg("gsb_trainer_debug_set_epoch: null trainer");
+    t->epoch = epoch;
+    return GSB_OK;
+}
+
 int gsb_trainer_set_overlap(gsb_trainer* t, int on) {
     if (!t) return gsb_fail_msg("gsb_trainer_set_overlap: null trainer");
     t->overlap = on != 0;
@@ -611,6 +660,7 @@ int gsb_trainer_densify_plan(gsb_trainer* t, const gsb_project_params* p, int* n
         GSB_CUDA_OK(cudaMemsetAsync(t->dens_lb, 0, lbw * sizeof(unsigned long long), s));
         t->dens_P = cap;
     }
+    if (int e = epoch_guard(t)) return e;
     GSB_CUDA_OK(cudaMemsetAsync(t->dens_ticket, 0, sizeof(uint32_t), s));
     GSB_CUDA_OK(cudaMemsetAsync(t->totals, 0, 4 * sizeof(uint32_t), s));
     DensifyArgs a;
@@ -666,7 +716,9 @@ int gsb_trainer_densify_commit(gsb_trainer* t, float* devLocations, float* devSh
 int gsb_trainer_train(gsb_trainer* t, const gsb_project_params* p, int densify, int* new_count) {
     if (!t || !p) return gsb_fail_msg("gsb_trainer_train: invalid argument");
     if (int e = gsb_trainer_accumulate(t)) return e;
-    if (t->allreduce) {
+    if (t->comm) {
+        if (int e = gsb_comm_allreduce_sum(t->comm, avg_ptr(t), grad_floats(t), t->stream)) return e;
+    } else if (t->allreduce) {
         if (int e = t->allreduce(avg_ptr(t), grad_floats(t), t->stream, t->allreduce_user)) {
             gsb_fail_msg("gsb_trainer_train: all-reduce hook failed");
             return e;
@@ -688,7 +740,7 @@ int gsb_trainer_render(gsb_trainer* t, uint32_t* dev_frame_buffer, int width, in
     const int tiles = ((width + GSB_TILE - 1) / GSB_TILE) * ((height + GSB_TILE - 1) / GSB_TILE);
     if (int e = ensure_geom(t, (size_t)std::max(t->count, 1))) return e;
     if (t->r_cap == 0) {
-        if (int e = ensure_bin(t, (uint32_t)std::max<size_t>((size_t)1 << 20, (size_t)t->count * 6))) return e;
+        if (int e = ensure_bin(t, (uint32_t)std::min<size_t>(0x7FFFFFF0u, std::max<size_t>((size_t)1 << 20, (size_t)t->count * 6)))) return e;
     }
     // preview arena: the training image workspace is reused when the size matches (T:159-167)
     ImageWs im;

@@ -121,6 +121,10 @@ def _params_struct(project):
     return p
 
 
+def _camera_key(cam):
+    return (cam.location.tobytes(), cam.target.tobytes(), float(cam.fovDegY))
+
+
 def camera_struct(consts):
     c = CameraC()
     c.view[:] = [float(x) for x in consts["view"]]
@@ -128,6 +132,45 @@ def camera_struct(consts):
     c.location[:] = [float(x) for x in consts["location"]]
     c.tan_fovx, c.tan_fovy = float(consts["tan_fovx"]), float(consts["tan_fovy"])
     return c
+
+
+class Comm:
+    """gsb_comm: the library's own NCCL communicator (include/gsb.h).  One process per GPU: rank 0 creates the NCCL
+    unique id, `exchange(bytes) -> bytes` ships it to the other ranks (any out-of-band channel)."""
+
+    def __init__(self, handle, rank, world):
+        self._h, self.rank, self.world = handle, rank, world
+
+    @classmethod
+    def init(cls, rank, world, exchange):
+        uid = (C.c_ubyte * 128)()
+        if rank == 0:
+            check(lib().gsb_comm_get_unique_id(uid))
+        raw = exchange(bytes(uid))
+        buf = (C.c_ubyte * 128).from_buffer_copy(raw)
+        h = C.c_void_p()
+        check(lib().gsb_comm_init(C.byref(h), buf, rank, world))
+        return cls(h, rank, world)
+
+    @classmethod
+    def from_torch_distributed(cls, dist, device):
+        """Bootstrap over an initialised torch.distributed group (any backend): broadcast of the 128-byte id."""
+        rank, world = dist.get_rank(), dist.get_world_size()
+
+        def exchange(raw):
+            on = device if dist.get_backend() == "nccl" else "cpu"
+            t = torch.tensor(list(raw), dtype=torch.uint8, device=on)
+            dist.broadcast(t, src=0)
+            return bytes(t.cpu().tolist())
+        return cls.init(rank, world, exchange)
+
+    def allreduce_sum(self, tensor):
+        check(lib().gsb_comm_allreduce_sum(self._h, tensor.data_ptr(), tensor.numel(), None))
+
+    def close(self):
+        if self._h:
+            lib().gsb_comm_destroy(self._h)
+            self._h = None
 
 
 class Trainer:
@@ -149,6 +192,7 @@ class Trainer:
         self._total_cameras = None
         self._allreduce_cb = None
         self._avg = None
+        self._render_cams = {}
 
     def close(self):
         if getattr(self, "_h", None):
@@ -181,8 +225,9 @@ class Trainer:
 
     def _sync_truths(self):
         n = len(self.truthFrameBuffersW)
+        # keyed on the camera VALUES (a Camera mutated in place, or a rebuilt list that re-uses CPython ids, must be seen)
         sig = (tuple(t.data_ptr() for t in self.truthFrameBuffersW), tuple(t.data_ptr() for t in self.truthFrameBuffersB),
-               tuple(id(c) for c in self.truthCameras), self._total_cameras)
+               tuple(_camera_key(c) for c in self.truthCameras), self._total_cameras)
         if sig == self._truth_sig:
             return
         arr_w = (C.c_void_p * max(n, 1))(*[t.data_ptr() for t in self.truthFrameBuffersW])
@@ -228,6 +273,11 @@ class Trainer:
                 return 1
         self._allreduce_cb = ALLREDUCE_FN(hook)
         check(lib().gsb_trainer_set_allreduce(self._h, self._allreduce_cb, None))
+
+    def set_comm(self, comm):
+        """Native exchange: train() all-reduces the running means over `comm` (a Comm) inside libgsb200.so."""
+        self._comm = comm
+        check(lib().gsb_trainer_set_comm(self._h, comm._h if comm is not None else None))
 
     def set_fuse_backgrounds(self, on=True):
         """White + black pass of a camera in one forward / one backward walk (default on)."""
@@ -278,7 +328,12 @@ class Trainer:
     def render(self, frameBuffer, sizeX, sizeY, splatScale, camera):
         """Trainer::render (src/Trainer.cu:148-216): RGBA8 preview into `frameBuffer` (int32/uint32 tensor)."""
         self._bind()
-        cs = camera_struct(camera.view_constants(sizeX, sizeY, square_fov=False))
+        key = (_camera_key(camera), int(sizeX), int(sizeY))
+        cs = self._render_cams.get(key)
+        if cs is None:                      # the float32 glm-order matrix maths runs in Python: once per camera and size
+            if len(self._render_cams) > 4096:
+                self._render_cams.clear()
+            cs = self._render_cams[key] = camera_struct(camera.view_constants(sizeX, sizeY, square_fov=False))
         check(lib().gsb_trainer_render(self._h, frameBuffer.data_ptr(), sizeX, sizeY, float(splatScale), C.byref(cs)))
 
     def accumulate(self):

@@ -23,6 +23,13 @@ private:
     gsb_trainer* impl = nullptr;     // gsb_trainer_create(RENDER_RESOLUTION_X, RENDER_RESOLUTION_Y)
     int lastTruthCount = -1;         // as src/Trainer.cuh:16: re-allocate truth frames when the camera count changes
 
+    // GSB_COMPAT_DEVICES=G (environment, read by the constructor): the truth cameras are sharded over G GPUs of this
+    // process -- one replica trainer, one host thread and one NCCL communicator per extra device; `model`, the truth
+    // frames and render() stay on the application's device exactly as before.  Null on a single GPU.
+    struct Multi;
+    Multi* multi = nullptr;
+    void trainMulti(Project& project, bool densify);
+
 public:
     ModelSplatsDevice* model;
 

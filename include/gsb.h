@@ -151,6 +151,31 @@ float* gsb_trainer_grad_buffer(gsb_trainer* t);
 typedef int (*gsb_allreduce_fn)(float* dev, size_t count, void* stream, void* user);
 int gsb_trainer_set_allreduce(gsb_trainer* t, gsb_allreduce_fn fn, void* user);
 
+/* Native exchange step: NCCL communicators owned by the library, so a C++ caller of this ABI
+ * (or of include/compat/Trainer.cuh) can shard the truth cameras over several GPUs without any Python.  NCCL is bound
+ * at run time (libnccl.so.2); single-GPU callers never load it.
+ *   one process per GPU:  rank 0 calls gsb_comm_get_unique_id, ships the 128 bytes to the other ranks out of band
+ *                         (file, socket, MPI, torch.distributed), every rank calls gsb_comm_init on ITS current device
+ *   one process, G GPUs:  gsb_comm_init_all fills out[0..ndev) (devices = NULL means 0..ndev-1); each communicator is
+ *                         then driven from its own host thread with its device current
+ * gsb_trainer_set_comm makes gsb_trainer_train sum the running means over the communicator (on the trainer's stream)
+ * between accumulate and apply; it takes precedence over the gsb_trainer_set_allreduce hook.  Every rank must call
+ * train() the same number of times.  NCCL returns bit-identical sums on all ranks and apply / densify are
+ * deterministic, so the replicas stay bit-identical without a parameter broadcast. */
+#define GSB_COMM_UNIQUE_ID_BYTES 128
+typedef struct gsb_comm gsb_comm;
+int gsb_comm_nccl_version(int* version);
+int gsb_comm_get_unique_id(void* id_out);
+int gsb_comm_init(gsb_comm** out, const void* nccl_unique_id, int rank, int world);
+int gsb_comm_init_all(gsb_comm** out, int ndev, const int* devices);
+int gsb_comm_destroy(gsb_comm* c);
+int gsb_comm_rank(const gsb_comm* c);
+int gsb_comm_world(const gsb_comm* c);
+int gsb_comm_device(const gsb_comm* c);
+int gsb_comm_allreduce_sum(gsb_comm* c, float* dev, size_t count, void* stream);
+int gsb_comm_broadcast(gsb_comm* c, void* dev, size_t bytes, int root, void* stream);
+int gsb_trainer_set_comm(gsb_trainer* t, gsb_comm* comm);
+
 /* Trainer::train (T:252-543) split at the point where ranks exchange gradients:
  *   accumulate = zero the means, then forward + loss + backward + accumulate of every local view
  *   apply      = applyGradients (T:428-431)
@@ -177,6 +202,7 @@ typedef struct gsb_trainer_stats {
     int retries;                   /* accumulate re-runs caused by binning-capacity growth */
     long long kernel_launches;     /* kernels launched by this trainer since creation */
     double sum_sq_residual;        /* sum over views of sum(residual^2), if enabled */
+    long long epoch_wraps;         /* look-back epoch counter restarts (every ~2^30 look-back launches) */
 } gsb_trainer_stats;
 int gsb_trainer_get_stats(gsb_trainer* t, gsb_trainer_stats* out);
 int gsb_trainer_enable_loss(gsb_trainer* t, int on);
@@ -209,6 +235,15 @@ int gsb_trainer_get_stage_times(gsb_trainer* t, double* stage_ms, long long* pas
  * control flow: out8 = { E_eval_f, E_exp_f, E_blend_f, E_eval_b, E_exp_b, E_blend_b, R, visible }
  * (forward.cu:310-357, backward.cu:476-503).  Needs one prior gsb_trainer_accumulate. */
 int gsb_trainer_count_pairs(gsb_trainer* t, int camera_index, unsigned long long* out8);
+
+/* Measurement: FP32 issue peak of the current device from an FFMA-only kernel (8 independent chains per thread,
+ * 8 x 256 threads per SM): out2[0] = scalar FFMA TFLOP/s, out2[1] = packed fma.rn.f32x2 TFLOP/s.  The measured
+ * denominator of the render kernels' roofline (MEASURED_PEAKS.json has no FP32 SIMT figure). */
+int gsb_measure_fp32_peak(double* out2, void* stream);
+
+/* Testing: preset the look-back epoch counter (30-bit tags in the chained-scan status words) so the wrap
+ * path can be exercised without running 2^30 launches. */
+int gsb_trainer_debug_set_epoch(gsb_trainer* t, unsigned int epoch);
 
 /* Image helpers: imageFloatToInt / imageIntToLoss (T:19-44). */
 int gsb_image_float_to_int(const float* dev_src, uint32_t* dev_fb, int w, int h, void* stream);

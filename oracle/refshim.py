@@ -66,6 +66,23 @@ def lib():
     return _lib
 
 
+REF_CAM_LIB = os.path.join(_HERE, "_ref", "libgsrefcam.so")
+
+
+def ref_cameras(project):
+    """Camera::getCameras of the reference's own src/Camera.cpp (oracle/_ref/libgsrefcam.so) for a Project-like object
+    with sphere1 / sphere2 (count, distance, fovDeg, rotX, rotY).  Returns [(location xyz float32[3], fovDegY)]."""
+    L = C.CDLL(REF_CAM_LIB)
+    L.gsrefcam_get_cameras.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
+    L.gsrefcam_get_cameras.restype = C.c_int
+    sp = [np.array([s.count, s.distance, s.fovDeg, s.rotX, s.rotY], np.float32) for s in (project.sphere1, project.sphere2)]
+    cap = int(project.sphere1.count + project.sphere2.count) + 1
+    out = np.zeros(4 * cap, np.float32)
+    n = L.gsrefcam_get_cameras(sp[0].ctypes.data_as(C.c_void_p), sp[1].ctypes.data_as(C.c_void_p),
+                               out.ctypes.data_as(C.c_void_p), cap)
+    return [(out[4 * i:4 * i + 3].copy(), float(out[4 * i + 3])) for i in range(n)]
+
+
 def _p(t):
     return None if t is None else C.c_void_p(t.data_ptr())
 

@@ -3,10 +3,24 @@
 // It proves the drop-in boundary: `Trainer`, `CudaRasterizer::Rasterizer` and the model containers
 // are used through the reference's signatures only.  Plain host C++ (g++), no nvcc.
 //
-// Prints one JSON line; exit code 0 only if training reduced the image error and densify grew the model.
+// Two builds (tests/compat/Makefile):
+//   GSB_DEMO_REAL_APP  the application headers are the REFERENCE'S OWN src/Camera.h, src/Camera.cpp, src/Project.h,
+//                      src/Config.h, src/ModelSplatsDevice.h, src/ModelSplatsHost.h, read in place from the reference
+//                      tree (with its in-tree glm and nlohmann); only the bodies of ModelSplats*.cpp are restated
+//                      (app_impl/ModelSplatsImpl.cpp) because the originals include ui/UiPanelViewInput.h (wxWidgets)
+//   otherwise          the hand-written look-alikes in tests/compat/app/ (where the reference tree is absent)
+//
+//   compat_demo               single GPU: training must reduce the image error, densify must grow the model
+//   compat_demo --devices G   the same job twice, once on one GPU and once with GSB_COMPAT_DEVICES=G (camera-sharded,
+//                             native NCCL all-reduce inside libgsb200.so): parameters after k iterations incl. a densify
+//                             must agree ("G in {1,2,4,8} produce parameters equal to G = 1")
+// Prints one JSON line; exit code 0 on success.
 #include <cmath>
 #include <cstdint>
 #include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <stdexcept>
 #include <vector>
 
 #include <cuda_runtime.h>
@@ -19,16 +33,20 @@
 #include "Trainer.cuh"
 #include "rasterizer.h"
 
+#ifndef GSB_DEMO_REAL_APP
 int Camera::getCamerasCount(const Project& project) { return project.sphere1.count + project.sphere2.count; }
 std::vector<Camera> Camera::getCameras(const Project& project) {
     std::vector<Camera> out;
-    for (int i = 0; i < project.sphere1.count; i++) {
-        const float a = 6.2831853f * (float)i / (float)project.sphere1.count;
-        out.push_back(Camera({project.sphere1.distance * std::sin(a), 2.0f, project.sphere1.distance * std::cos(a)}, {0, 0, 0},
-                             project.sphere1.fovDeg));
+    for (int s = 0; s < 2; s++) {
+        const auto& sphere = s == 0 ? project.sphere1 : project.sphere2;
+        for (int i = 0; i < sphere.count; i++) {
+            const float a = 6.2831853f * ((float)i + 0.37f * (float)s) / (float)sphere.count;
+            out.push_back(Camera({sphere.distance * std::sin(a), 2.0f + (float)s, sphere.distance * std::cos(a)}, {0, 0, 0}, sphere.fovDeg));
+        }
     }
     return out;
 }
+#endif
 
 static uint32_t lcg_state = 12345u;
 static float rnd() { lcg_state = lcg_state * 1664525u + 1013904223u; return (float)(lcg_state >> 8) * (1.0f / 16777216.0f); }
@@ -63,19 +81,13 @@ static double image_error(Trainer& trainer, const std::vector<Camera>& cams, std
     return err / ((double)cams.size() * N * 3);
 }
 
-int main() {
+// "truth capture": a teacher model rendered on black through Trainer::render and on white through
+// CudaRasterizer::Rasterizer::forward called the way src/Trainer.cu:175-201 calls it
+static int capture_truths(Trainer& trainer, const std::vector<Camera>& cams, int teacherSplats) {
     const int W = RENDER_RESOLUTION_X, H = RENDER_RESOLUTION_Y, N = W * H;
-    Project project;
-    project.sphere1.count = 4;
-    project.sphere2.count = 0;
-    const std::vector<Camera> cams = Camera::getCameras(project);
-
-    Trainer trainer;
-
-    // "truth capture": a teacher model rendered on black through Trainer::render and on white through
-    // CudaRasterizer::Rasterizer::forward called the way src/Trainer.cu:175-201 calls it
     ModelSplatsHost teacher(SPLATS_LIMIT, SPLATS_SH_DEGREE, SPLATS_SH_COEF);
-    fill(teacher, 2000, 2.0f);
+    lcg_state = 12345u;
+    fill(teacher, teacherSplats, 2.0f);
     delete trainer.model;
     trainer.model = new ModelSplatsDevice(teacher);
     float *devBg, *devView, *devProjView, *devCamLoc, *devColor;
@@ -109,6 +121,32 @@ int main() {
         trainer.truthFrameBuffersB.push_back(fbB);
         trainer.truthCameras.push_back(camera);
     }
+    cudaFree(devBg); cudaFree(devView); cudaFree(devProjView); cudaFree(devCamLoc); cudaFree(devColor);
+    return rendered;
+}
+
+static void set_student(Trainer& trainer, int splats) {
+    // what UiFrame::initField* does -- delete trainer->model, assign a new one
+    ModelSplatsHost student(SPLATS_LIMIT, SPLATS_SH_DEGREE, SPLATS_SH_COEF);
+    lcg_state = 777u;
+    fill(student, splats, 2.0f);
+    delete trainer.model;
+    trainer.model = new ModelSplatsDevice(student);
+}
+
+static void set_rates(Project& project) {
+    project.lrLocation = 0.02f; project.lrSh = 0.1f; project.lrScale = 0.002f; project.lrOpacity = 0.05f; project.lrRotation = 0.002f;
+}
+
+static int single_device_demo() {
+    const int N = RENDER_RESOLUTION_X * RENDER_RESOLUTION_Y;
+    Project project;
+    project.sphere1.count = 4;
+    project.sphere2.count = 0;
+    const std::vector<Camera> cams = Camera::getCameras(project);
+
+    Trainer trainer;
+    const int rendered = capture_truths(trainer, cams, 2000);
 
     // train() with no truths must throw the reference's message: check on a second trainer
     bool threw = false;
@@ -117,17 +155,12 @@ int main() {
         try { empty.train(project, false); } catch (const std::runtime_error&) { threw = true; }
     }
 
-    // the student: what UiFrame::initField* does -- delete trainer->model, assign a new one
-    ModelSplatsHost student(SPLATS_LIMIT, SPLATS_SH_DEGREE, SPLATS_SH_COEF);
-    fill(student, 3000, 2.0f);
-    delete trainer.model;
-    trainer.model = new ModelSplatsDevice(student);
-
+    set_student(trainer, 3000);
     std::vector<uint32_t> scratch(N);
     uint32_t* devFb;
     cudaMalloc(&devFb, N * sizeof(uint32_t));
     const double err0 = image_error(trainer, cams, scratch, devFb);
-    project.lrLocation = 0.02f; project.lrSh = 0.1f; project.lrScale = 0.002f; project.lrOpacity = 0.05f; project.lrRotation = 0.002f;
+    set_rates(project);
     for (int it = 0; it < 60; it++) trainer.train(project, false);
     const double err1 = image_error(trainer, cams, scratch, devFb);
     const int count0 = trainer.model->count;
@@ -139,9 +172,90 @@ int main() {
     for (int i = 0; i < back.count * 3; i++) finite = finite && std::isfinite(back.scales[i]);
     trainer.train(project, false);             // the iteration after a densify re-binds the new arrays
 
+#ifdef GSB_DEMO_REAL_APP
+    const char* app = "reference headers (src/Camera.h, Camera.cpp, Project.h, Config.h, ModelSplats*.h)";
+#else
+    const char* app = "stand-in headers (tests/compat/app)";
+#endif
     printf("{\"rendered_last_truth\": %d, \"err0\": %.4f, \"err1\": %.4f, \"count0\": %d, \"count1\": %d, \"iterations\": %d, "
-           "\"threw_without_truths\": %s, \"finite\": %s}\n",
-           rendered, err0, err1, count0, count1, project.iterations, threw ? "true" : "false", finite ? "true" : "false");
+           "\"threw_without_truths\": %s, \"finite\": %s, \"resolution\": %d, \"app\": \"%s\"}\n",
+           rendered, err0, err1, count0, count1, project.iterations, threw ? "true" : "false", finite ? "true" : "false",
+           RENDER_RESOLUTION_X, app);
     const bool ok = rendered > 0 && err1 < 0.8 * err0 && count1 > count0 && threw && finite && project.iterations == 62;
     return ok ? 0 : 1;
+}
+
+struct RunResult {
+    int count = 0;
+    std::vector<float> loc, shs, scales, opac, rot;
+};
+
+// k iterations of the same job (6 + 6 cameras, densify on iteration 3 of 5) on `devices` GPUs
+static RunResult run_job(int devices) {
+    if (devices > 1) setenv("GSB_COMPAT_DEVICES", std::to_string(devices).c_str(), 1);
+    else unsetenv("GSB_COMPAT_DEVICES");
+    Project project;
+    project.sphere1.count = 6;
+    project.sphere2.count = 6;
+    project.sphere2.fovDeg = 30.0f;
+    const std::vector<Camera> cams = Camera::getCameras(project);
+    Trainer trainer;
+    capture_truths(trainer, cams, 2000);
+    set_student(trainer, 3000);
+    set_rates(project);
+    // every surviving splat densifies (no near-tie on the variance threshold), large ones split, small ones clone, faint
+    // ones are culled: all three branches of src/Trainer.cu:448-499 on the all-reduced means
+    project.paramDensifyVariance = -1.0f;
+    project.paramCullOpacity = 0.35f;
+    project.paramSplitSize = 0.2f;
+    for (int it = 0; it < 5; it++) trainer.train(project, it == 2);
+    ModelSplatsHost back(*trainer.model);
+    RunResult r;
+    r.count = back.count;
+    r.loc.assign(back.locations, back.locations + 3 * back.count);
+    r.shs.assign(back.shs, back.shs + 3 * back.shCoeffs * back.count);
+    r.scales.assign(back.scales, back.scales + 3 * back.count);
+    r.opac.assign(back.opacities, back.opacities + back.count);
+    r.rot.assign(back.rotations, back.rotations + 4 * back.count);
+    return r;
+}
+
+static double rel_diff(const std::vector<float>& a, const std::vector<float>& b) {
+    if (a.size() != b.size()) return 1e30;
+    double num = 0.0, den = 0.0;
+    for (size_t i = 0; i < a.size(); i++) {
+        const double d = (double)a[i] - (double)b[i];
+        num += d * d; den += (double)b[i] * (double)b[i];
+    }
+    return std::sqrt(num / (den > 0.0 ? den : 1.0));
+}
+
+static int multi_device_demo(int devices) {
+    int have = 0;
+    cudaGetDeviceCount(&have);
+    if (have < devices) {
+        printf("{\"skipped\": \"needs %d GPUs, %d visible\"}\n", devices, have);
+        return 77;
+    }
+    const RunResult one = run_job(1);
+    const RunResult many = run_job(devices);
+    const double d[5] = {rel_diff(many.loc, one.loc), rel_diff(many.shs, one.shs), rel_diff(many.scales, one.scales),
+                         rel_diff(many.opac, one.opac), rel_diff(many.rot, one.rot)};
+    double worst = 0.0;
+    for (double x : d) worst = std::max(worst, x);
+    printf("{\"devices\": %d, \"count_1\": %d, \"count_G\": %d, \"rel_loc\": %.3e, \"rel_sh\": %.3e, \"rel_scale\": %.3e, "
+           "\"rel_opacity\": %.3e, \"rel_rot\": %.3e}\n", devices, one.count, many.count, d[0], d[1], d[2], d[3], d[4]);
+    return (one.count == many.count && one.count != 3000 && worst <= 1e-5) ? 0 : 1;
+}
+
+int main(int argc, char** argv) {
+    int devices = 1;
+    for (int i = 1; i + 1 < argc; i++)
+        if (!strcmp(argv[i], "--devices")) devices = std::atoi(argv[i + 1]);
+    try {
+        return devices > 1 ? multi_device_demo(devices) : single_device_demo();
+    } catch (const std::exception& e) {
+        fprintf(stderr, "compat_demo: %s\n", e.what());
+        return 2;
+    }
 }

@@ -1,0 +1,167 @@
+"""Multi-GPU correctness of the CUDA path (SURVEY.md 7.4 last row; reference linearity src/Trainer.cu:47-77 and the
+densify block :437-542).  Run under torchrun, one rank per GPU; also called by bench.py for every N > 1.
+
+The job: k = 3 iterations of a camera-sharded trainer with the library's own NCCL exchange (gsb_comm_*), the second one
+densifying (cull + split + clone all occur).  Checked:
+  (i)   a 64-bit checksum of count + all five parameter arrays is bit-identical on every rank  -> replicas_identical
+  (ii)  every parameter array is within 1e-5 relative L2 of the N = 1 run of the same job (same canonical densify
+        order)                                                                                 -> vs_n1_rel
+  (iii) R summed over the ranks' view passes equals the N = 1 value                           -> rendered_match
+
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29533 \
+        tests/mgpu_check.py [--config C3] [--cameras 4]
+"""
+import argparse
+import json
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+for p in (ROOT, os.path.join(ROOT, "tests"), os.path.join(ROOT, "tools")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+KEYS = ("locations", "shs", "scales", "opacities", "rotations")
+DEVKEYS = ("devLocations", "devShs", "devScales", "devOpacities", "devRotations")
+
+
+def _checksum(torch, model):
+    """Position-weighted 64-bit sum of the raw float bits of every array, plus the count."""
+    out = [int(model.count)]
+    for k in DEVKEYS:
+        v = getattr(model, k).view(torch.int32).to(torch.int64)
+        w = (torch.arange(v.numel(), device=v.device, dtype=torch.int64) % 65521) + 1
+        out.append(int((v * w).sum().item()))
+    return out
+
+
+def _gap_threshold(values, q):
+    v = np.sort(np.asarray(values, dtype=np.float64))
+    k = int(q * (len(v) - 1))
+    lo, hi = max(1, k - 200), min(len(v) - 1, k + 200)
+    j = lo + int(np.argmax(v[lo + 1:hi + 1] - v[lo:hi]))
+    return float(0.5 * (v[j] + v[j + 1]))
+
+
+def run_check(torch, dist, rank, world, local, config="C4", cameras=8, iterations=3, densify_at=1):
+    import helpers as H
+    from gpu_stage_probe import make_truths
+    gsb = H.gsb
+    dev = f"cuda:{local}"
+    W, Hh, P = gsb.synth.CONFIGS[config]
+    project = gsb.synth.project_for(config)
+    project.sphere1.count = cameras
+    project.sphere2.count = cameras if project.sphere2.count > 0 else 0
+    # learning rates large enough for three iterations to move the parameters visibly in float32
+    project.lrLocation, project.lrSh, project.lrScale, project.lrOpacity, project.lrRotation = 0.002, 0.01, 0.0005, 0.01, 0.0005
+    cams = gsb.Camera.getCameras(project)
+    n1 = project.sphere1.count
+    seed = 0x5EED0000 + int(config[1])
+    cloud = gsb.synth.splat_cloud(P, seed)
+    teacher = gsb.synth.splat_cloud(P // 2, seed + 1)
+    mine = gsb.synth.shard_cameras(cams, n1, rank, world)
+    sq = (W == Hh)
+
+    def trainer_for(camset, tw, tb, comm):
+        tr = gsb.Trainer(W, Hh, dev, square_fov=sq)
+        tr.set_total_cameras(len(cams))
+        host = gsb.ModelSplatsHost.from_arrays(*[cloud[k] for k in KEYS])
+        tr.model = gsb.ModelSplatsDevice(host, dev)
+        tr.truthFrameBuffersW, tr.truthFrameBuffersB, tr.truthCameras = tw, tb, camset
+        if comm is not None:
+            tr.set_comm(comm)
+        return tr
+
+    import copy
+    thr = torch.zeros(3, dtype=torch.float64, device=dev)
+    all_tw = all_tb = None
+    if rank == 0:
+        # thresholds in gaps of the decision variables, taken from an N = 1 pre-run up to the densifying iteration
+        all_tw, all_tb, _ = make_truths(teacher, cams, W, Hh, dev)
+        pre = trainer_for(cams, all_tw, all_tb, None)
+        avg = pre.grad_tensor()
+        pj = copy.deepcopy(project)
+        for _ in range(densify_at + 1):
+            pre.train(pj, False)
+        torch.cuda.synchronize()
+        a = avg.cpu().numpy()
+        m = gsb.ModelSplatsHost.from_device(pre.model)
+        score = a[:P].astype(np.float64) - np.linalg.norm(a[P:4 * P].astype(np.float64).reshape(-1, 3), axis=1)
+        thr[0] = _gap_threshold(score, 0.85)
+        thr[1] = _gap_threshold(m.opacities, 0.08)
+        thr[2] = _gap_threshold(np.linalg.norm(m.scales.reshape(-1, 3), axis=1), 0.5)
+        pre.close()
+    dist.broadcast(thr, src=0)
+    project.paramDensifyVariance, project.paramCullOpacity, project.paramSplitSize = [float(x) for x in thr.cpu()]
+
+    # ---- the N-rank job: camera shards, native NCCL exchange -------------------------------------------------
+    comm = gsb.Comm.from_torch_distributed(dist, dev)
+    if rank == 0:
+        idx = [cams.index(c) for c in mine]
+        tw, tb = [all_tw[i] for i in idx], [all_tb[i] for i in idx]
+    else:
+        tw, tb, _ = make_truths(teacher, mine, W, Hh, dev)
+    tr = trainer_for(mine, tw, tb, comm)
+    pj = copy.deepcopy(project)
+    counts = []
+    for it in range(iterations):
+        tr.train(pj, it == densify_at)
+        counts.append(int(tr.model.count))
+    torch.cuda.synchronize()
+    rendered = torch.tensor([tr.stats()["rendered_total"]], dtype=torch.int64, device=dev)
+    dist.all_reduce(rendered)
+    cs = torch.tensor(_checksum(torch, tr.model), dtype=torch.int64, device=dev)
+    gathered = [torch.zeros_like(cs) for _ in range(world)]
+    dist.all_gather(gathered, cs)
+    identical = all(bool(torch.equal(g, gathered[0])) for g in gathered)
+
+    res = {"world": world, "config": config, "cameras_total": len(cams), "iterations": iterations,
+           "densify_iteration": densify_at, "counts": counts, "replicas_identical": identical,
+           "checksums": [[int(x) for x in g.cpu().tolist()] for g in gathered]}
+    if rank == 0:
+        # ---- the same job on ONE GPU --------------------------------------------------------------------------
+        one = trainer_for(cams, all_tw, all_tb, None)
+        pj1 = copy.deepcopy(project)
+        counts1 = []
+        for it in range(iterations):
+            one.train(pj1, it == densify_at)
+            counts1.append(int(one.model.count))
+        torch.cuda.synchronize()
+        rel = {}
+        if counts1 == counts:
+            for k, dk in zip(KEYS, DEVKEYS):
+                a, b = getattr(tr.model, dk).double(), getattr(one.model, dk).double()
+                rel[k] = float(torch.linalg.norm(a - b) / torch.linalg.norm(b))
+        res.update({"counts_n1": counts1, "vs_n1_rel": max(rel.values()) if rel else None, "vs_n1_rel_per_array": rel,
+                    "rendered_total": int(rendered.item()), "rendered_total_n1": int(one.stats()["rendered_total"]),
+                    "rendered_match": int(rendered.item()) == int(one.stats()["rendered_total"]),
+                    "densify_changed_count": counts[densify_at] != P,
+                    "thresholds": [float(x) for x in thr.cpu()]})
+        one.close()
+    tr.close()
+    comm.close()
+    return res
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--config", default="C3")
+    ap.add_argument("--cameras", type=int, default=4)
+    args = ap.parse_args()
+    import torch
+    import torch.distributed as dist
+    rank, world, local = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("LOCAL_RANK", "0"))
+    os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", local))
+    res = run_check(torch, dist, rank, world, local, args.config, args.cameras)
+    if rank == 0:
+        print("MGPU_CHECK " + json.dumps(res), flush=True)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,262 @@
+"""GPU: the BASELINE.json configurations that had no trainer-level comparison with the compiled reference
+(oracle/_ref/libgsref.so = the reference's own kernels + the replay of Trainer::train / its CPU densify block):
+
+  C3  mid-stage: 16+16 cameras (cut to 2+2), 1024x1024, 50 k splats, lrSh = lrOpacity = 0.01 (reference README presets)
+  C2  early-stage WITH periodic densify: 8 cameras 512x512, 10 k splats, densify whenever iterations % interval == 0,
+      evaluated before the increment as UiFrame::update does (src/ui/UiFrame.cpp:283-292), both sides densifying
+  C4  late-stage at trainer level: the running means of one accumulate over 2+2 cameras at 1920x1080 / 500 k splats
+      against the reference replay (not just fused-vs-unfused of the product against itself)
+plus the round-1 advisor findings that needed a device to test (look-back epoch wrap, 0-splat model, in-place camera
+mutation, indefinite cov3D_precomp)."""
+import os
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+import golden_cases as GC
+import helpers as H
+from oracle import refshim
+
+sys.path.insert(0, os.path.join(GC.ROOT, "tools"))
+from gpu_stage_probe import make_truths  # noqa: E402
+
+gsb = GC.gsb
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+KEYS = ("locations", "shs", "scales", "opacities", "rotations")
+needs_ref = pytest.mark.skipif(not refshim.available(), reason="oracle/_ref/libgsref.so not present")
+
+
+def _new_trainer(W, Hh, cloud, cams, tw, tb, **kw):
+    tr = gsb.Trainer(W, Hh, DEV, **kw)
+    tr.model = gsb.ModelSplatsDevice(gsb.ModelSplatsHost.from_arrays(*[cloud[k] for k in KEYS]), DEV)
+    tr.truthFrameBuffersW, tr.truthFrameBuffersB, tr.truthCameras = tw, tb, cams
+    return tr
+
+
+def _new_ref(W, Hh, cloud, tw, tb, consts, capacity=1000000):
+    rt = refshim.RefTrainer(W, Hh, DEV)
+    rt.set_model(cloud, capacity, 1, 4)
+    rt.set_truths(tw, tb, consts)
+    return rt
+
+
+def _assert_tracks(mine, ref, ref2, start, label):
+    """Parameters within 1e-3 relative L2 of the distance moved (north_star's gradient budget); where two runs of the
+    REFERENCE are further apart than that (unordered atomics), twice their spread."""
+    for k in KEYS:
+        move = ref[k].astype(np.float64) - start[k]
+        diff = np.asarray(mine[k], np.float64) - ref[k]
+        spread = ref2[k].astype(np.float64) - ref[k]
+        assert np.abs(move).max() > 0, (label, k)
+        assert np.linalg.norm(diff) <= max(1e-3 * np.linalg.norm(move), 2 * np.linalg.norm(spread)), (label, k)
+        assert np.abs(diff).max() <= max(1e-2 * np.abs(move).max(), 5e-6, 2 * np.abs(spread).max()), (label, k)
+
+
+@needs_ref
+def test_config_c3_iterations_track_reference():
+    W, Hh, P = gsb.synth.CONFIGS["C3"]
+    project = gsb.synth.project_for("C3")
+    assert (W, Hh, P) == (1024, 1024, 50000) and project.lrSh == project.lrOpacity == 0.01
+    project.sphere1.count = project.sphere2.count = 2          # 16+16 cut to 2+2: both FOVs (60 / 20 close-ups)
+    cams = gsb.Camera.getCameras(project)
+    cloud = gsb.synth.splat_cloud(P, 0x5EED0003)
+    tw, tb, consts = make_truths(gsb.synth.splat_cloud(P // 2, 0x5EED0004), cams, W, Hh, DEV)
+    rt, rt2 = _new_ref(W, Hh, cloud, tw, tb, consts), _new_ref(W, Hh, cloud, tw, tb, consts)
+    tr = _new_trainer(W, Hh, cloud, cams, tw, tb)
+    for it in range(5):
+        rt.train(project.params13(), as_shipped=True)
+        rt2.train(project.params13(), as_shipped=True)
+        tr.train(project, False)
+        if it == 0:      # identical parameters going in: the duplicate count must be identical, not just close
+            assert tr.stats()["rendered_total"] == rt.rendered_total()
+    mine = gsb.ModelSplatsHost.from_device(tr.model)
+    _assert_tracks({k: getattr(mine, k) for k in KEYS}, rt.get_model(), rt2.get_model(), cloud, "C3")
+    rt.close(); rt2.close(); tr.close()
+
+
+def _match_rows(a, b, M=4):
+    """Bijection between two splat sets by nearest neighbour in the 11 geometric dimensions; returns the largest
+    distance over all 11 + 3M columns of matched rows."""
+    from scipy.spatial import cKDTree
+
+    def rows(m):
+        n = m["opacities"].shape[0]
+        geo = np.concatenate([m["locations"].reshape(n, 3), m["scales"].reshape(n, 3), m["opacities"].reshape(n, 1),
+                              m["rotations"].reshape(n, 4)], axis=1).astype(np.float64)
+        return geo, m["shs"].reshape(n, 3 * M).astype(np.float64)
+    ga, sa = rows(a)
+    gb, sb = rows(b)
+    assert ga.shape == gb.shape
+    d, idx = cKDTree(gb).query(ga)
+    assert len(np.unique(idx)) == len(idx), "not a bijection"
+    return max(float(d.max()), float(np.abs(sa - sb[idx]).max()))
+
+
+@needs_ref
+def test_config_c2_with_periodic_densify_tracks_reference():
+    W, Hh, P = gsb.synth.CONFIGS["C2"]
+    project = gsb.synth.project_for("C2")
+    assert (W, Hh, P) == (512, 512, 10000) and project.sphere1.count == 8
+    project.intervalDensify = 2
+    project.lrLocation, project.lrSh, project.lrScale, project.lrOpacity, project.lrRotation = 0.002, 0.01, 0.0005, 0.01, 0.0005
+    cams = gsb.Camera.getCameras(project)
+    cloud = gsb.synth.splat_cloud(P, 0x5EED0002)
+    tw, tb, consts = make_truths(gsb.synth.splat_cloud(P // 2, 0x5EED0003), cams, W, Hh, DEV)
+    rt = _new_ref(W, Hh, cloud, tw, tb, consts)
+    tr = _new_trainer(W, Hh, cloud, cams, tw, tb)
+    avg = tr.grad_tensor()
+    counts = []
+    for it in range(5):
+        densify = project.iterations % project.intervalDensify == 0        # before the increment inside train()
+        rt.train(project.params13(), as_shipped=True)
+        tr.train(project, False)
+        if densify:
+            # thresholds in gaps of the decision variables (no splat within rounding distance of a boundary, so both
+            # implementations take the same decisions), then the densify block on this iteration's means on both sides:
+            # exactly what train(project, true) runs after applyGradients (src/Trainer.cu:437-542)
+            torch.cuda.synchronize()
+            n = tr.model.count
+            a = avg.cpu().numpy()
+            m = gsb.ModelSplatsHost.from_device(tr.model)
+            GC.densify_thresholds(project, {"opacities": m.opacities, "scales": m.scales}, a[:n], a[n:4 * n])
+            tr.densify(project)
+            rt.densify(project.params13())
+            avg = tr.grad_tensor()
+            assert tr.model.count == rt.count() != n, (it, tr.model.count, rt.count(), n)
+            mine = gsb.ModelSplatsHost.from_device(tr.model)
+            worst = _match_rows({k: getattr(mine, k) for k in KEYS}, rt.get_model())
+            assert worst <= 5e-5, (it, worst)
+            counts.append(tr.model.count)
+    assert len(counts) == 3                      # iterations 0, 2, 4
+    # and the genuine fused call once more: train(project, true) with everything densifying (no threshold near-ties)
+    project.paramDensifyVariance = -1.0
+    n = tr.model.count
+    rt.train(project.params13(), as_shipped=True)
+    rt.densify(project.params13())
+    tr.train(project, True)
+    assert tr.model.count == rt.count() > n
+    mine = gsb.ModelSplatsHost.from_device(tr.model)
+    assert _match_rows({k: getattr(mine, k) for k in KEYS}, rt.get_model()) <= 5e-5
+    rt.close(); tr.close()
+
+
+@needs_ref
+def test_config_c4_running_means_match_reference_replay():
+    W, Hh, P = gsb.synth.CONFIGS["C4"]
+    project = gsb.synth.project_for("C4")
+    project.sphere1.count = project.sphere2.count = 2
+    cams = gsb.Camera.getCameras(project)
+    cloud = gsb.synth.splat_cloud(P, 0x5EED0004)
+    tw, tb, consts = make_truths(gsb.synth.splat_cloud(P // 2, 0x5EED0005), cams, W, Hh, DEV)
+    rt = _new_ref(W, Hh, cloud, tw, tb, consts)
+    rt.train(project.params13(), as_shipped=False, apply=False)
+    ref = [b.cpu() for b in rt.buffers()]
+    for fuse in (True, False):
+        tr = _new_trainer(W, Hh, cloud, cams, tw, tb, square_fov=True)     # Trainer::train's tan_fovx = tan_fovy (T:355-356)
+        tr.set_fuse_backgrounds(fuse)
+        avg = tr.grad_tensor()
+        tr.accumulate()
+        torch.cuda.synchronize()
+        a, o = avg.cpu(), 0
+        for name, size, r in zip(("var", "loc", "sh", "scale", "opacity", "rot"), (P, 3 * P, 12 * P, 3 * P, P, 4 * P), ref):
+            assert H.rel_l2(a[o:o + size], r) <= 1e-3, (fuse, name, H.rel_l2(a[o:o + size], r))
+            o += size
+        assert tr.stats()["rendered_total"] == rt.rendered_total()
+        tr.close()
+    rt.close()
+
+
+# ---- advisor findings -------------------------------------------------------------------------------------------
+def _small_job(seed=41):
+    W, Hh, P = 200, 136, 4000
+    project = gsb.synth.project_for("C2")
+    project.sphere1.count = 3
+    cams = gsb.Camera.getCameras(project)
+    cloud = gsb.synth.splat_cloud(P, seed, scale_hi=0.12)
+    tw, tb, _ = make_truths(gsb.synth.splat_cloud(P // 2, seed + 1, scale_hi=0.12), cams, W, Hh, DEV)
+    return W, Hh, P, project, cams, cloud, tw, tb
+
+
+def test_lookback_epoch_wrap_is_survived():
+    """The chained-scan status words keep a 30-bit epoch: preset the counter just below the limit so that one
+    accumulate crosses it; results must equal those of a fresh trainer and the wrap must have been taken."""
+    W, Hh, P, project, cams, cloud, tw, tb = _small_job()
+    ref = _new_trainer(W, Hh, cloud, cams, tw, tb, square_fov=False)
+    a0 = ref.grad_tensor()
+    ref.accumulate()
+    tr = _new_trainer(W, Hh, cloud, cams, tw, tb, square_fov=False)
+    a1 = tr.grad_tensor()
+    tr.accumulate()                                                   # arenas sized, look-back words carry small epochs
+    gsb.lib().gsb_trainer_debug_set_epoch(tr._h, 0x3FFFFFFF - 64 - 2)
+    for _ in range(3):
+        tr.accumulate()
+    torch.cuda.synchronize()
+    assert tr.stats()["epoch_wraps"] >= 1
+    assert H.rel_l2(a1, a0) <= 1e-5
+    project.paramDensifyVariance = -1.0
+    gsb.lib().gsb_trainer_debug_set_epoch(tr._h, 0x3FFFFFFF - 64)    # the densify scan takes the wrap itself
+    tr.train(project, True)
+    assert tr.model.count > P and tr.stats()["epoch_wraps"] >= 2
+    ref.close(); tr.close()
+
+
+def test_zero_splat_model_is_a_no_op_like_the_reference():
+    W, Hh, P, project, cams, cloud, tw, tb = _small_job()
+    tr = gsb.Trainer(W, Hh, DEV)
+    host = gsb.ModelSplatsHost(1000000, 1, 4)                          # the constructor's temporary model (T:112)
+    tr.model = gsb.ModelSplatsDevice(host, DEV)
+    tr.truthFrameBuffersW, tr.truthFrameBuffersB, tr.truthCameras = tw, tb, cams
+    tr.train(project, False)                                           # every kernel runs over zero splats
+    tr.train(project, True)
+    assert tr.model.count == 0 and tr.stats()["views"] == 2 * len(cams)
+    fb = torch.zeros(W * Hh, dtype=torch.int32, device=DEV)
+    tr.render(fb, W, Hh, 1.0, cams[0])
+    assert int((fb.view(torch.uint8).view(-1, 4)[:, :3] != 0).sum()) == 0   # black background, nothing drawn
+    tr.close()
+
+
+def test_camera_mutated_in_place_is_seen():
+    W, Hh, P, project, cams, cloud, tw, tb = _small_job()
+    import copy
+    cams_a = [copy.deepcopy(c) for c in cams]
+    tr = _new_trainer(W, Hh, cloud, cams_a, tw, tb, square_fov=False)
+    avg = tr.grad_tensor()
+    tr.accumulate()
+    first = avg.clone()
+    cams_a[0].location[:] = cams_a[0].location * np.float32(0.8)      # same objects, new values
+    tr.accumulate()
+    moved = avg.clone()
+    fresh = _new_trainer(W, Hh, cloud, [copy.deepcopy(c) for c in cams_a], tw, tb, square_fov=False)
+    a2 = fresh.grad_tensor()
+    fresh.accumulate()
+    assert H.rel_l2(moved, first) > 1e-3 and H.rel_l2(moved, a2) <= 1e-5
+    tr.close(); fresh.close()
+
+
+@needs_ref
+def test_indefinite_precomputed_covariance_is_not_culled():
+    """cov3D_precomp may project to a conic that is not positive definite (det < 0): the set the reference blends is then
+    unbounded, so the bounding-box pre-cull must stand down (advisor finding on render_fwd.cu)."""
+    W, Hh, P = 160, 112, 600
+    cloud = gsb.synth.splat_cloud(P, 123, scale_hi=0.3)
+    cam = gsb.Camera((0.0, 0.0, 9.0), (0, 0, 0), 50.0)
+    consts = cam.view_constants(W, Hh)
+    sc = H.scene_tensors(cloud, DEV)
+    vw = H.view_tensors(consts, (0, 0, 0), DEV)
+    ws, _, R = H.run_forward_gsb(sc, vw, P, 1, 4, W, Hh)
+    cov = gsb.state(ws, P, W, Hh, R)["cov3D"].cpu().numpy().copy()
+    cov[::7, 1] *= -40.0                     # strong off-diagonal terms: indefinite 3D "covariances"
+    cov[::11, 0] = -np.abs(cov[::11, 0]) * 5
+    covt = torch.from_numpy(cov.reshape(-1).astype(np.float32)).to(DEV)
+    ref_out, R_ref = H.run_forward_ref(sc, vw, P, 1, 4, W, Hh, cov3D_precomp=covt)
+    ref = refshim.state(P, W, Hh, R_ref, DEV)
+    ws2, out, R2 = H.run_forward_gsb(sc, vw, P, 1, 4, W, Hh, cov3D_precomp=covt)
+    st = gsb.state(ws2, P, W, Hh, R2)
+    assert R2 == R_ref and torch.equal(st["point_list"], ref["point_list"])
+    assert torch.equal(st["n_contrib"], ref["n_contrib"])
+    finite = torch.isfinite(ref_out) & torch.isfinite(out)
+    assert float((out - ref_out)[finite].abs().max()) <= 1e-4
+    assert bool((torch.isfinite(ref_out) == torch.isfinite(out)).all())

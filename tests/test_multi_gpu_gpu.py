@@ -1,0 +1,42 @@
+"""GPU, world size 2 (skipped with fewer devices): the N > 1 CUDA path -- camera shards, the library's own NCCL
+exchange (gsb_comm_*), densify on the reduced means -- gives bit-identical replicas that equal the N = 1 run
+(tests/mgpu_check.py has the protocol).  The C++ flavour of the same statement: compat_demo --devices 2 drives two
+GPUs from one process through include/compat/Trainer.cuh with GSB_COMPAT_DEVICES."""
+import json
+import os
+import subprocess
+import sys
+
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+pytestmark = pytest.mark.gpu
+needs2 = pytest.mark.skipif(not torch.cuda.is_available() or torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+
+
+@needs2
+@pytest.mark.parametrize("config,cameras", [("C3", 4), ("C2", 4)])
+def test_two_ranks_bit_identical_and_equal_to_one_rank(config, cameras):
+    port = 29600 + (os.getpid() % 300)
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
+           "--master-port", str(port), os.path.join(ROOT, "tests", "mgpu_check.py"), "--config", config, "--cameras", str(cameras)]
+    r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=900, cwd=ROOT)
+    lines = [l for l in r.stdout.splitlines() if l.startswith("MGPU_CHECK ")]
+    assert r.returncode == 0 and lines, r.stdout[-4000:]
+    res = json.loads(lines[-1][len("MGPU_CHECK "):])
+    assert res["replicas_identical"], res
+    assert res["counts"] == res["counts_n1"] and res["densify_changed_count"], res
+    assert res["vs_n1_rel"] is not None and res["vs_n1_rel"] <= 1e-5, res
+    assert res["rendered_match"], res
+
+
+@needs2
+def test_compat_trainer_two_devices_in_one_process():
+    demo = os.path.join(ROOT, "tests", "compat", "compat_demo")
+    if not os.path.exists(demo):
+        subprocess.check_call(["make", "-C", os.path.join(ROOT, "tests", "compat")], stdout=subprocess.DEVNULL)
+    r = subprocess.run([demo, "--devices", "2"], stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout + r.stderr
+    out = json.loads(r.stdout.strip().splitlines()[-1])
+    assert out["count_1"] == out["count_G"] and max(out[k] for k in out if k.startswith("rel_")) <= 1e-5, out

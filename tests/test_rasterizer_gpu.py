@@ -99,7 +99,7 @@ def test_forward_backward_match_cpu_oracle_on_fresh_scene():
 needs_ref = pytest.mark.skipif(not refshim.available(), reason="oracle/_ref/libgsref.so not present")
 
 
-def _compare_with_reference(cloud, consts, bg, W, Hh, D, M, backward=True, grad_tol={}, skip_grads=(), **kw):
+def _compare_with_reference(cloud, consts, bg, W, Hh, D, M, backward=True, grad_tol={}, skip_grads=(), spread_aware=(), **kw):
     sc = H.scene_tensors(cloud, DEV)
     vw = H.view_tensors(consts, bg, DEV)
     P = cloud["opacities"].shape[0]
@@ -130,10 +130,27 @@ def _compare_with_reference(cloud, consts, bg, W, Hh, D, M, backward=True, grad_
         sm = kw.get("scale_modifier", 1.0)
         g_ref = H.run_backward_ref(sc, vw, P, D, M, R_ref, W, Hh, dL, scale_modifier=sm)
         g = H.run_backward_gsb(ws, sc, vw, P, D, M, R, W, Hh, dL, scale_modifier=sm)
+        if spread_aware:
+            # ill-conditioned tensors: the bar is what the REFERENCE itself achieves, measured here and asserted --
+            # its run-to-run spread (unordered atomics, backward.cu:523-554; largest over three more runs) and its own
+            # distance from the double-precision CPU oracle
+            more = [H.run_backward_ref(sc, vw, P, D, M, R_ref, W, Hh, dL, scale_modifier=sm) for _ in range(3)]
+            _, v = pyoracle.forward(P, D, M, bg, W, Hh, cloud["locations"], cloud["shs"], None, cloud["opacities"], cloud["scales"],
+                                    sm, cloud["rotations"], None, consts["view"], consts["projview"], consts["location"],
+                                    consts["tan_fovx"], consts["tan_fovy"])
+            exact = v.backward(dL.cpu().numpy(), M)
+            v.close()
         for k in H.GRAD_NAMES:
             if k in skip_grads:
                 continue
-            assert H.rel_l2(g[k], g_ref[k]) <= grad_tol.get(k, 1e-3), k
+            tol = grad_tol.get(k, 1e-3)
+            if k in spread_aware:
+                spread = max(H.rel_l2(m[k], g_ref[k]) for m in more)
+                ex = torch.from_numpy(exact[k].reshape(-1)).to(g[k].device)
+                ref_err, my_err = H.rel_l2(g_ref[k], ex), H.rel_l2(g[k], ex)
+                assert my_err <= max(1e-3, 1.5 * ref_err), (k, my_err, ref_err)      # as close to exact as the reference is
+                tol = max(1e-3, 2.0 * spread, 2.0 * ref_err)
+            assert H.rel_l2(g[k], g_ref[k]) <= tol, (k, H.rel_l2(g[k], g_ref[k]), tol)
     return st, out
 
 
@@ -180,15 +197,15 @@ def test_degenerate_and_extreme_splats_against_compiled_reference():
     sc[320:360] = (0.3, 0.004, 0.004)      # needle: strongest anisotropy the trainer's clamps allow
     cam = gsb.Camera((0.0, 0.0, 10.0), (0, 0, 0), 60.0)
     # The needle and scale-40 splats make the covariance-path gradients ill-conditioned in float32: two runs
-    # of the REFERENCE differ by 3e-3 (dL_drot) / 1e-3 (dL_dcov3D) here because its atomics sum in a different
-    # order each time (backward.cu:523-554; measured with tools/gpu_diag.py, against the double-precision
-    # oracle the reference is 3.2e-3 off and this library 1.9e-3).  Those three tensors get 1e-2 on this
-    # scene; every other tensor keeps 1e-3.
-    loose = {"dL_drot": 1e-2, "dL_dcov3D": 1e-2, "dL_dscale": 1e-2}
-    _compare_with_reference(cloud, cam.view_constants(W, Hh), (1.0, 1.0, 1.0), W, Hh, 1, 4, grad_tol=loose)
+    # of the REFERENCE differ by ~3e-3 (dL_drot) / ~1e-3 (dL_dcov3D) here because its atomics sum in a different
+    # order each time (backward.cu:523-554).  For those three tensors the bar is therefore measured inside the test
+    # (spread_aware): no further from the double-precision oracle than 1.5 x the reference is, and within twice the
+    # reference's own spread / oracle distance of the reference.  Every other tensor keeps 1e-3.
+    loose = ("dL_drot", "dL_dcov3D", "dL_dscale")
+    _compare_with_reference(cloud, cam.view_constants(W, Hh), (1.0, 1.0, 1.0), W, Hh, 1, 4, spread_aware=loose)
     # splats far outside the 1.3 tan(fov) clamp of computeCov2D (forward.cu:82-87)
     cam2 = gsb.Camera((0.0, 0.0, 4.5), (0, 0, 0), 25.0)
-    _compare_with_reference(cloud, cam2.view_constants(W, Hh), (0.0, 0.0, 0.0), W, Hh, 1, 4, grad_tol=loose)
+    _compare_with_reference(cloud, cam2.view_constants(W, Hh), (0.0, 0.0, 0.0), W, Hh, 1, 4, spread_aware=loose)
 
 
 @needs_ref

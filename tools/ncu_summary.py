@@ -4,6 +4,7 @@ usage:
   python tools/ncu_summary.py launches gpurun_out/launches.csv            > profiles/rNN_launches.txt
   python tools/ncu_summary.py raw      gpurun_out/prof_render.ncu-rep     > profiles/rNN_render_raw.txt
   python tools/ncu_summary.py source   gpurun_out/prof_render.ncu-rep render_bwd [top]  > profiles/rNN_render_bwd_source.txt
+  python tools/ncu_summary.py traffic  gpurun_out/prof_render.ncu-rep gpurun_out/prof_render.cmd   (rewrites profiles/traffic.json)
 """
 import collections
 import csv
@@ -69,6 +70,38 @@ def raw(rep):
                 print(f"  {m:84s} {r[idx[m]]:>18s} {units[idx[m]]}")
 
 
+def traffic(rep, cmd_file):
+    """profiles/traffic.json = dram__bytes_read.sum + dram__bytes_write.sum of the captured launches, per kernel (mean
+    over the launches in the report), with the ncu command line that produced the report.  bench.py reads
+    `render_bwd` / `render_fwd` from it for roofline.traffic; nothing in it is typed by hand."""
+    import json
+    import os
+    rows = list(csv.reader(io.StringIO(_ncu(rep, "raw"))))
+    hdr, units = rows[0], rows[1]
+    idx = {h: i for i, h in enumerate(hdr)}
+    scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    per = collections.OrderedDict()
+    for r in rows[2:]:
+        name = r[idx["Kernel Name"]]
+        key = next((k for k in ("render_bwd", "render_fwd", "preprocess_bwd", "preprocess_fwd", "tile_sort", "emit") if k in name), name[:40])
+        rd = float(r[idx["dram__bytes_read.sum"]].replace(",", "")) * scale.get(units[idx["dram__bytes_read.sum"]], 1.0)
+        wr = float(r[idx["dram__bytes_write.sum"]].replace(",", "")) * scale.get(units[idx["dram__bytes_write.sum"]], 1.0)
+        per.setdefault(key, []).append((rd, wr, name))
+    out = {}
+    detail = {}
+    for k, v in per.items():
+        out[k] = int(sum(a + b for a, b, _ in v) / len(v))
+        detail[k] = {"kernel": v[0][2], "launches": len(v), "read_bytes": [int(a) for a, _, _ in v], "write_bytes": [int(b) for _, b, _ in v]}
+    out["_detail"] = detail
+    out["_command"] = open(cmd_file).read().strip() if cmd_file and os.path.exists(cmd_file) else None
+    out["_report"] = os.path.basename(rep)
+    out["_source"] = "generated by tools/ncu_summary.py traffic from the ncu --set full report of the command above; bytes per launch"
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    with open(os.path.join(root, "profiles", "traffic.json"), "w") as f:
+        json.dump(out, f, indent=1)
+    print(json.dumps({k: v for k, v in out.items() if not k.startswith("_")}))
+
+
 def source(rep, kernel, top=40):
     txt = _ncu(rep, "source", ("--kernel-name", "regex:" + kernel))
     # the report holds one block per captured launch; keep the first
@@ -97,5 +130,7 @@ if __name__ == "__main__":
         launches(sys.argv[2])
     elif mode == "raw":
         raw(sys.argv[2])
+    elif mode == "traffic":
+        traffic(sys.argv[2], sys.argv[3] if len(sys.argv) > 3 else None)
     else:
         source(sys.argv[2], sys.argv[3], int(sys.argv[4]) if len(sys.argv) > 4 else 40)
