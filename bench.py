@@ -390,6 +390,11 @@ def run_gsb(args):
     tr.set_stage_timing(True)
     ms_serial = timed_steps(torch, dist, lambda k: tr.train(project, False), args.steps)
     stage_ms, passes = tr.stage_times()
+    st_x = tr.stats()
+    iteration_tail = {"exchange_ms": st_x["exchange_ms"] / max(st_x["timed_iterations"], 1),
+                      "apply_ms": st_x["apply_ms"] / max(st_x["timed_iterations"], 1),
+                      "what": "per iteration: all-reduce of the running means (NCCL, on the trainer's stream) and applyGradients; "
+                              "with the first forward chain (nothing to overlap with) they are the serial section of a step"}
     tr.set_stage_timing(False)
 
     # ---- counters for the roofline (after the timed region) ----------------------------------
@@ -434,7 +439,14 @@ def run_gsb(args):
         # one pinned host block and one device block per buffer set: the step's 2n frames travel as ONE cudaMemcpyAsync
         # (128 separate copies cost ~2 ms of host enqueue time per step, during which the compute stream sat idle)
         n_fr = len(tw) + len(tb)
-        host_all = torch.stack([t.cpu() for t in list(tw) + list(tb)]).pin_memory()
+        numa = importlib.import_module("gaussian-splatterer_b200.numa")
+        props = torch.cuda.get_device_properties(local)
+        try:
+            bus = "%08x:%02x:%02x.0" % (props.pci_domain_id, props.pci_bus_id, props.pci_device_id)
+        except Exception:
+            bus = None
+        with numa.local_to_gpu(bus) as placement:         # the pinned block lives on the GPU's own NUMA node
+            host_all = torch.stack([t.cpu() for t in list(tw) + list(tb)]).pin_memory()
         dev_all = [torch.stack(list(tw) + list(tb)), torch.empty((n_fr,) + tuple(tw[0].shape), dtype=tw[0].dtype, device=tw[0].device)]
         dset = [([dev_all[w][i] for i in range(len(tw))], [dev_all[w][len(tw) + i] for i in range(len(tb))]) for w in (0, 1)]
         copy_stream = torch.cuda.Stream()
@@ -446,24 +458,28 @@ def run_gsb(args):
                 dev_all[which].copy_(host_all, non_blocking=True)
                 up_ev[which].record(copy_stream)
 
-        def step(k):
+        def step(k, last=False):
             cur = k & 1
             torch.cuda.current_stream().wait_event(up_ev[cur])    # this step's inputs have landed
             upload(cur ^ 1)                                       # next step's inputs, overlapped
             tr.truthFrameBuffersW, tr.truthFrameBuffersB = dset[cur]
             tr.train(project, False)
-            losses.append(tr.stats()["sum_sq_residual"])          # device -> host read of the step's result
+            # device -> host read of a step's result, every step: the scalar of step k-1 is read while step k runs (the
+            # library copies it to pinned memory at the end of each iteration), the last step's own before the clock stops
+            losses.append(tr.loss(1 if not last else 0) if (len(losses) or last) else tr.loss(0))
 
         upload(0)
         for k in range(2 * ((args.warmup + 1) // 2)):             # even count: the timed loop starts on set 0
             step(k)
-        ms_e = timed_steps(torch, dist, step, args.steps)
+        ms_e = timed_steps(torch, dist, lambda k: step(k, last=(k == args.steps - 1)), args.steps)
         h2d = n_local * 2 * W * Hh * 4 + n_local * 148
         e2e = {"value": views_per_step * args.steps / (ms_e / 1000.0), "unit": UNIT, "h2d_bytes_per_step": h2d,
                "d2h_bytes_per_step": 8 + 4 * 2 * n_local, "ms_per_step": ms_e / args.steps,
                "result": "sum of squared residuals", "last_loss": losses[-1],
-               "how": "Trainer.train with RGBA8 truth frames in pinned host memory; one cudaMemcpyAsync of the next step's "
-                      "frames on a copy stream overlaps the current step; per rank"}
+               "how": "Trainer.train with RGBA8 truth frames in pinned host memory (allocated on the GPU's NUMA node); one "
+                      "cudaMemcpyAsync of the next step's frames on a copy stream overlaps the current step; the loss scalar of "
+                      "step k-1 is read from pinned memory while step k runs, the last step's before the clock stops; per rank",
+               "host_placement": placement.info}
         tr.close()
 
     render_stats = truth_stats = None
@@ -501,7 +517,7 @@ def run_gsb(args):
         stages[k] = {"ms_per_launch": round(v, 4), "share": round(v / total_stage_ms, 4) if total_stage_ms else None}
     stages["render_fwd"].update({"tflops": fwd_flops(pair) / (fwd_ms * 1e-3) / 1e12 if fwd_ms else None,
                                  "frac_fp32": fwd_flops(pair) / (fwd_ms * 1e-3) / 1e12 / fp32_peak if fwd_ms else None})
-    bin_ms = sum(per_launch[k] for k in ("depth_sort", "scan", "emit", "tile_sort", "ranges"))
+    bin_ms = sum(per_launch[k] for k in ("tile_scan", "emit", "tile_sort"))
     for name, ms_k in (("preprocess", per_launch["preprocess"]), ("binning", bin_ms),
                        ("preprocess_bwd", per_launch["preprocess_bwd"])):
         by = STREAM_BYTES[name](cnt) * (units if name == "preprocess_bwd" else 1)
@@ -542,6 +558,7 @@ def run_gsb(args):
                      "step_hbm": {"bound": "hbm", "achieved": step_gbs, "peak": hbm_peak, "unit": "GB/s",
                                   "frac": step_gbs / hbm_peak, "bytes_per_step_per_rank": step_bytes, "peak_source": hbm_src}},
         "stages": stages,
+        "iteration_tail": iteration_tail,
         "stats": {"rendered_per_step": stats["rendered_total"], "retries": stats["retries"],
                   "ms_per_step_serialised_with_stage_events": ms_serial / args.steps},
     }

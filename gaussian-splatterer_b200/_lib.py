@@ -30,15 +30,16 @@ class CameraC(C.Structure):
 class StateView(C.Structure):
     """gsb_state_view."""
     _fields_ = [(n, C.c_void_p) for n in (
-        "radii", "depths", "tiles_touched", "recs", "cov3D", "clamped", "depth_order", "point_list",
-        "point_list_tiles", "ranges", "n_contrib", "final_T", "tile_max", "counters")]
+        "radii", "depths", "tiles_touched", "recs", "cov3D", "clamped", "point_list",
+        "ranges", "n_contrib", "final_T", "tile_max", "counters")]
 
 
 class TrainerStats(C.Structure):
     """gsb_trainer_stats."""
     _fields_ = [("rendered_total", C.c_longlong), ("visible_total", C.c_longlong), ("views", C.c_int),
                 ("retries", C.c_int), ("kernel_launches", C.c_longlong), ("sum_sq_residual", C.c_double),
-                ("epoch_wraps", C.c_longlong)]
+                ("epoch_wraps", C.c_longlong), ("exchange_ms", C.c_double), ("apply_ms", C.c_double),
+                ("timed_iterations", C.c_longlong)]
 
 
 _lib = None
@@ -67,7 +68,7 @@ def lib():
     L.gsb_rasterizer_mark_visible.restype = i
     L.gsb_rasterizer_state.argtypes = [i, i, i, i, vp, vp, vp, C.POINTER(StateView)]
     L.gsb_rasterizer_state.restype = i
-    L.gsb_rasterizer_sorted_keys.argtypes = [i, i, i, i, vp, vp, vp, vp]
+    L.gsb_rasterizer_sorted_keys.argtypes = [i, i, i, i, vp, vp, vp, vp, vp]
     L.gsb_rasterizer_sorted_keys.restype = i
     L.gsb_trainer_create.argtypes = [C.POINTER(vp), i, i, vp]
     L.gsb_trainer_create.restype = i
@@ -99,6 +100,8 @@ def lib():
     L.gsb_trainer_render.restype = i
     L.gsb_trainer_get_stats.argtypes = [vp, C.POINTER(TrainerStats)]
     L.gsb_trainer_get_stats.restype = i
+    L.gsb_trainer_get_loss.argtypes = [vp, i, C.POINTER(C.c_double)]
+    L.gsb_trainer_get_loss.restype = i
     L.gsb_trainer_enable_loss.argtypes = [vp, i]
     L.gsb_trainer_enable_loss.restype = i
     L.gsb_trainer_set_fuse_backgrounds.argtypes = [vp, i]
@@ -144,7 +147,7 @@ def lib():
 EXPORTED_SYMBOLS = [
     "gsb_last_error", "gsb_version", "gsb_rasterizer_forward", "gsb_rasterizer_backward",
     "gsb_rasterizer_mark_visible", "gsb_rasterizer_state", "gsb_rasterizer_sorted_keys",
-    "gsb_trainer_enable_loss", "gsb_trainer_set_fuse_backgrounds", "gsb_trainer_profile_pass",
+    "gsb_trainer_enable_loss", "gsb_trainer_get_loss", "gsb_trainer_set_fuse_backgrounds", "gsb_trainer_profile_pass",
     "gsb_trainer_set_stage_timing", "gsb_trainer_get_stage_times", "gsb_trainer_count_pairs", "gsb_trainer_set_overlap",
     "gsb_trainer_debug_set_epoch", "gsb_measure_fp32_peak",
     "gsb_comm_nccl_version", "gsb_comm_get_unique_id", "gsb_comm_init", "gsb_comm_init_all", "gsb_comm_destroy",

@@ -34,14 +34,12 @@ struct __align__(16) GradRec2 {
     float2 v[12];   // v[0..5] = H0, Hx, Hy, Hxx, Hxy, Hyy; v[6..8] = dL/dr, dL/dg, dL/db; v[9..11] unused
 };
 
-// Device-resident control block, cleared by one memset per view.
+// Device-resident control block, cleared by one (16-byte) memset per view.
 struct GsbCtrl {
     uint32_t num_rendered;          // R: total duplicates (device copy; host copy is optional)
     uint32_t num_visible;           // splats with radius > 0
     uint32_t overflow;              // 1 if R exceeded the binning capacity
-    uint32_t pad0;
-    uint32_t tickets[16];           // dynamic tile ids of the look-back kernels (one per launch)
-    uint32_t hist[8][256];          // digit histograms: [0..3] depth sort, [4..7] tile sort
+    uint32_t ticket;                // dynamic scan-tile ids of tile_scan_kernel
 };
 
 #define GSB_CUDA_OK(expr)                                                              \
@@ -54,6 +52,20 @@ int gsb_fail(cudaError_t e, const char* what, const char* file, int line);
 int gsb_fail_msg(const char* msg);
 
 static inline int gsb_div_up(long long a, long long b) { return (int)((a + b - 1) / b); }
+
+// NVTX ranges around the host-side stages: compiled in with `make EXTRA=-DGSB_NVTX`.
+#ifdef GSB_NVTX
+#include <nvtx3/nvToolsExt.h>
+struct GsbNvtxRange {
+    explicit GsbNvtxRange(const char* name) { nvtxRangePushA(name); }
+    ~GsbNvtxRange() { nvtxRangePop(); }
+};
+#define GSB_NVTX_CAT2(a, b) a##b
+#define GSB_NVTX_CAT(a, b) GSB_NVTX_CAT2(a, b)
+#define GSB_NVTX(name) GsbNvtxRange GSB_NVTX_CAT(gsb_nvtx_, __LINE__)(name)
+#else
+#define GSB_NVTX(name) do { } while (0)
+#endif
 
 // ------------------------------------------------------------------------------------------
 // Kernel launchers (defined in the .cu files of this directory).  All take a stream and never
@@ -85,8 +97,8 @@ struct PreprocessArgs {
     SplatRec* recs;                 // [P]
     float* cov3D;                   // [P][6]
     uint8_t* clamped;               // [P] bit c set if channel c was clamped at 0
-    uint32_t* sort_keys;            // [P] depth bits (0xFFFFFFFF for culled splats)
-    uint32_t* sort_vals;            // [P] splat index
+    uint32_t* tile_count;           // [tiles] += 1 for every tile of a visible splat's rectangle (zero on entry)
+    GsbCtrl* ctrl;                  // num_visible += visible splats
 };
 void launch_preprocess_fwd(const PreprocessArgs& a, cudaStream_t s);
 void launch_mark_visible(int P, const float* means3D, const float* viewmatrix, bool* present, cudaStream_t s);
@@ -96,33 +108,26 @@ struct BinningArgs {
     int P;
     uint32_t r_cap;                 // capacity of the duplicate arrays
     int grid_x, grid_y;
-    int tile_bits;                  // getHigherMsb(tiles)
     const int* radii;
     const uint32_t* tiles_touched;
+    const float* depths;
     const SplatRec* recs;
-    uint32_t* pkeys[2];             // [P] depth-sort ping-pong (pkeys[0] holds the input)
-    uint32_t* pvals[2];             // [P]
-    uint32_t* offsets;              // [P] exclusive offsets in depth order
-    uint32_t* rkeys[2];             // [r_cap] tile-id ping-pong
-    uint32_t* rvals[2];             // [r_cap] splat-id ping-pong
-    uint2* ranges;                  // [tiles], zeroed by the caller
-    unsigned long long* lookback;   // [lookback_tiles][256]
-    uint32_t lookback_tiles;
+    uint32_t* tile_count;           // [tiles] per-tile duplicate counts from preprocess; cursors after the scan; zero after the sort
+    uint2* ranges;                  // [tiles] written for every tile by the scan
+    uint32_t* tile_max;             // [tiles] zeroed by the sort (render forward takes atomicMax into it)
+    unsigned long long* pairs;      // [r_cap] depth_bits << 32 | splat, bucketed by tile, sorted in place for long lists
+    uint32_t* point_list;           // [r_cap] splat ids sorted by (tile, depth, splat)
+    unsigned long long* lookback;   // [scan tiles] chained-scan status words
     uint32_t* epoch;                // host counter, bumped per look-back launch
     GsbCtrl* ctrl;
     uint32_t* num_rendered_host;    // pinned host mirror of R, or null
 };
-// The stages, in order.  launch_tile_sort returns the index (0/1) of the rkeys/rvals buffer that
-// holds the sorted list; a.lookback must cover P items for the first two and r_cap for the sort.
-void launch_depth_sort(const BinningArgs& a, cudaStream_t s);
-void launch_scan_offsets(const BinningArgs& a, cudaStream_t s);
+// The stages, in order (preprocess has filled tile_count).
+void launch_tile_scan(const BinningArgs& a, cudaStream_t s);
 void launch_emit(const BinningArgs& a, cudaStream_t s);
-int launch_tile_sort(const BinningArgs& a, cudaStream_t s);
-void launch_tile_ranges(const BinningArgs& a, int fin, cudaStream_t s);
-int gsb_tile_sort_passes(int tile_bits);
-// Convenience: depth sort + scan (everything before R is known) and emit + sort + ranges.
-void launch_binning_depth_and_scan(const BinningArgs& a, cudaStream_t s);
-int launch_binning_emit_and_sort(const BinningArgs& a, cudaStream_t s);
+void launch_tile_sort(const BinningArgs& a, cudaStream_t s);
+void launch_sorted_keys(const uint2* ranges, const uint32_t* point_list, const float* depths, uint32_t tiles, uint64_t* out,
+                        cudaStream_t s);
 
 // render_fwd.cu
 struct RenderFwdArgs {

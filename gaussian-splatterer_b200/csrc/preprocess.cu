@@ -111,11 +111,11 @@ __device__ F3 sh_to_rgb(int deg, int M, float px, float py, float pz, const floa
 __global__ void __launch_bounds__(256) preprocess_fwd_kernel(const PreprocessArgs a) {
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= a.P) return;
+    const unsigned live = __activemask();   // lanes of this warp that own a splat (only the last warp is partial)
 
     // Culled unless proven visible (forward.cu:189-190).
     int radius = 0;
     uint32_t tiles = 0;
-    uint32_t key = 0xFFFFFFFFu;
 
     const float px = a.means3D[3 * idx], py = a.means3D[3 * idx + 1], pz = a.means3D[3 * idx + 2];
     const float* V = a.viewmatrix;
@@ -205,15 +205,22 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(const PreprocessArg
             const uint32_t rx1 = min(gx, (uint32_t)max(0, x1)), ry1 = min(gy, (uint32_t)max(0, y1));
             const uint32_t t = (rx1 - rx0) * (ry1 - ry0);
             alive = (t != 0);
-            if (alive) { radius = r; tiles = t; key = __float_as_uint(depth); }
+            if (alive) {
+                radius = r; tiles = t;
+                // first half of the binning (binning.cu): how many splats cover each tile
+                for (uint32_t y = ry0; y < ry1; y++)
+                    for (uint32_t x = rx0; x < rx1; x++) atomicAdd(&a.tile_count[y * gx + x], 1u);
+            }
         }
     }
 
     a.radii[idx] = radius;
     if (a.radii_user) a.radii_user[idx] = radius;
     a.tiles_touched[idx] = tiles;
-    a.sort_keys[idx] = key;
-    a.sort_vals[idx] = (uint32_t)idx;
+    {
+        const unsigned vis = __ballot_sync(live, alive);
+        if (vis && (threadIdx.x & 31) == (__ffs(live) - 1)) atomicAdd(&a.ctrl->num_visible, (uint32_t)__popc(vis));
+    }
     if (!alive) return;
 
     F3 rgb;

@@ -38,13 +38,6 @@ int gsb_tile_bits(uint32_t n) {
 
 namespace {
 
-__global__ void sorted_keys_kernel(const uint32_t* tiles, const uint32_t* list, const float* depths, uint32_t R,
-                                   uint64_t* out) {
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= R) return;
-    out[i] = ((uint64_t)tiles[i] << 32) | (uint64_t)__float_as_uint(depths[list[i]]);
-}
-
 __global__ void fill_background_kernel(float* out, const float* bg, int n) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
@@ -95,8 +88,7 @@ int gsb_rasterizer_forward(gsb_alloc_fn geometry_alloc, void* geometry_user, gsb
     im.carve(iptr, (size_t)width * height, (size_t)tiles);
 
     GSB_CUDA_OK(cudaMemsetAsync(g.ctrl, 0, sizeof(GsbCtrl), s));
-    GSB_CUDA_OK(cudaMemsetAsync(g.lookback, 0, GeomWs::lookback_tiles((size_t)P) * 256 * sizeof(unsigned long long), s));
-    GSB_CUDA_OK(cudaMemsetAsync(im.ranges, 0, (size_t)tiles * sizeof(uint2), s));
+    GSB_CUDA_OK(cudaMemsetAsync(im.tile_max, 0, im.zero_bytes((size_t)tiles), s));   // tile_max, tile_count, look-back words
 
     PreprocessArgs pa;
     pa.P = P; pa.D = D; pa.M = M;
@@ -108,19 +100,18 @@ int gsb_rasterizer_forward(gsb_alloc_fn geometry_alloc, void* geometry_user, gsb
     pa.focal_x = width / (2.0f * tan_fovx);
     pa.grid_x = grid_x; pa.grid_y = grid_y; pa.prefiltered = prefiltered;
     pa.radii = g.radii; pa.radii_user = radii; pa.depths = g.depths; pa.tiles_touched = g.tiles_touched;
-    pa.recs = g.recs; pa.cov3D = g.cov3D; pa.clamped = g.clamped; pa.sort_keys = g.pkeys[0]; pa.sort_vals = g.pvals[0];
+    pa.recs = g.recs; pa.cov3D = g.cov3D; pa.clamped = g.clamped; pa.tile_count = im.tile_count; pa.ctrl = g.ctrl;
     launch_preprocess_fwd(pa, s);
     if (int e = check(s, dbg)) return e;
 
     uint32_t epoch = 0;
     BinningArgs ba;
-    ba.P = P; ba.r_cap = 0xFFFFFFFFu; ba.grid_x = grid_x; ba.grid_y = grid_y; ba.tile_bits = gsb_tile_bits((uint32_t)tiles);
-    ba.radii = g.radii; ba.tiles_touched = g.tiles_touched; ba.recs = g.recs;
-    ba.pkeys[0] = g.pkeys[0]; ba.pkeys[1] = g.pkeys[1]; ba.pvals[0] = g.pvals[0]; ba.pvals[1] = g.pvals[1];
-    ba.offsets = g.offsets; ba.rkeys[0] = ba.rkeys[1] = ba.rvals[0] = ba.rvals[1] = nullptr;
-    ba.ranges = im.ranges; ba.lookback = g.lookback; ba.lookback_tiles = (uint32_t)GeomWs::lookback_tiles((size_t)P);
-    ba.epoch = &epoch; ba.ctrl = g.ctrl; ba.num_rendered_host = nullptr;
-    launch_binning_depth_and_scan(ba, s);
+    ba.P = P; ba.r_cap = 0xFFFFFFFFu; ba.grid_x = grid_x; ba.grid_y = grid_y;
+    ba.radii = g.radii; ba.tiles_touched = g.tiles_touched; ba.depths = g.depths; ba.recs = g.recs;
+    ba.tile_count = im.tile_count; ba.ranges = im.ranges; ba.tile_max = im.tile_max;
+    ba.pairs = nullptr; ba.point_list = nullptr;
+    ba.lookback = im.lookback; ba.epoch = &epoch; ba.ctrl = g.ctrl; ba.num_rendered_host = nullptr;
+    launch_tile_scan(ba, s);                       // ranges of every tile, R
     if (int e = check(s, dbg)) return e;
 
     // The one forced device->host crossing of this API (rasterizer_impl.cu:281): R sizes the
@@ -135,19 +126,17 @@ int gsb_rasterizer_forward(gsb_alloc_fn geometry_alloc, void* geometry_user, gsb
     char* bptr = binning_alloc(BinWs::required((size_t)R), binning_user);
     if (!bptr) { gsb_fail_msg("binning allocator returned NULL"); return GSB_ERR_ALLOC; }
     b.carve(bptr, (size_t)R);
-    int fin = 0;
     if (R > 0) {
-        GSB_CUDA_OK(cudaMemsetAsync(b.lookback, 0, BinWs::lookback_tiles((size_t)R) * 256 * sizeof(unsigned long long), s));
         ba.r_cap = R;
-        ba.rkeys[0] = b.rkeys[0]; ba.rkeys[1] = b.rkeys[1]; ba.rvals[0] = b.rvals[0]; ba.rvals[1] = b.rvals[1];
-        ba.lookback = b.lookback; ba.lookback_tiles = (uint32_t)BinWs::lookback_tiles((size_t)R);
-        fin = launch_binning_emit_and_sort(ba, s);
+        ba.pairs = b.pairs; ba.point_list = b.point_list;
+        launch_emit(ba, s);
+        launch_tile_sort(ba, s);
         if (int e = check(s, dbg)) return e;
     }
 
     RenderFwdArgs ra;
     ra.W = width; ra.H = height; ra.grid_x = grid_x; ra.grid_y = grid_y;
-    ra.ranges = im.ranges; ra.point_list = b.rvals[fin]; ra.recs = g.recs; ra.bg = background;
+    ra.ranges = im.ranges; ra.point_list = b.point_list; ra.recs = g.recs; ra.bg = background;
     ra.out_color = out_color; ra.final_T = im.final_T; ra.n_contrib = im.n_contrib; ra.tile_max = im.tile_max;
     launch_render_fwd(ra, s);
     if (int e = check(s, dbg)) return e;
@@ -172,15 +161,13 @@ int gsb_rasterizer_backward(int P, int D, int M, int R, const float* background,
     GeomWs g; g.carve(geom_buffer, (size_t)P);
     ImageWs im; im.carve(image_buffer, (size_t)width * height, (size_t)tiles);
     BinWs b; b.carve(binning_buffer, (size_t)(R > 0 ? R : 0));
-    const int npass = (gsb_tile_bits((uint32_t)tiles) + 7) / 8;
-    const int fin = (npass > 0 ? npass : 1) & 1;
     if (radii == nullptr) radii = g.radii;
 
     GSB_CUDA_OK(cudaMemsetAsync(g.grads, 0, (size_t)P * sizeof(GradRec), s));
     if (R > 0) {
         RenderBwdArgs rb;
         rb.W = width; rb.H = height; rb.grid_x = grid_x; rb.grid_y = grid_y;
-        rb.ranges = im.ranges; rb.point_list = b.rvals[fin]; rb.recs = g.recs; rb.bg = background;
+        rb.ranges = im.ranges; rb.point_list = b.point_list; rb.recs = g.recs; rb.bg = background;
         rb.final_T = im.final_T; rb.n_contrib = im.n_contrib; rb.tile_max = im.tile_max;
         rb.dL_dpix = dL_dpix; rb.truth = nullptr; rb.rendered = nullptr; rb.grads = g.grads; rb.truth2 = nullptr; rb.grads2 = nullptr; rb.loss_out = nullptr;
         launch_render_bwd(rb, s);
@@ -220,15 +207,12 @@ int gsb_rasterizer_state(int P, int width, int height, int R, char* geom_buffer,
     const int tiles = grid_x * grid_y;
     GeomWs g; g.carve(geom_buffer, (size_t)P);
     ImageWs im; im.carve(image_buffer, (size_t)width * height, (size_t)tiles);
-    const int npass = (gsb_tile_bits((uint32_t)tiles) + 7) / 8;
-    const int fin = (npass > 0 ? npass : 1) & 1;
     memset(out, 0, sizeof(*out));
     out->radii = g.radii; out->depths = g.depths; out->tiles_touched = g.tiles_touched;
     out->recs = reinterpret_cast<const float*>(g.recs); out->cov3D = g.cov3D; out->clamped = g.clamped;
-    out->depth_order = g.pvals[0];
     if (binning_buffer && R > 0) {
         BinWs b; b.carve(binning_buffer, (size_t)R);
-        out->point_list = b.rvals[fin]; out->point_list_tiles = b.rkeys[fin];
+        out->point_list = b.point_list;
     }
     out->ranges = reinterpret_cast<const uint32_t*>(im.ranges); out->n_contrib = im.n_contrib; out->final_T = im.final_T;
     out->tile_max = im.tile_max; out->counters = &g.ctrl->num_rendered;
@@ -236,15 +220,15 @@ int gsb_rasterizer_state(int P, int width, int height, int R, char* geom_buffer,
 }
 
 int gsb_rasterizer_sorted_keys(int P, int width, int height, int R, char* geom_buffer, char* binning_buffer,
-                               uint64_t* dev_keys_out, void* stream) {
+                               char* image_buffer, uint64_t* dev_keys_out, void* stream) {
     if (R <= 0) return GSB_OK;
+    if (!geom_buffer || !binning_buffer || !image_buffer || !dev_keys_out) return gsb_fail_msg("gsb_rasterizer_sorted_keys: invalid argument");
     const int grid_x = (width + GSB_TILE - 1) / GSB_TILE, grid_y = (height + GSB_TILE - 1) / GSB_TILE;
-    const int npass = (gsb_tile_bits((uint32_t)(grid_x * grid_y)) + 7) / 8;
-    const int fin = (npass > 0 ? npass : 1) & 1;
+    const int tiles = grid_x * grid_y;
     GeomWs g; g.carve(geom_buffer, (size_t)P);
     BinWs b; b.carve(binning_buffer, (size_t)R);
-    sorted_keys_kernel<<<gsb_div_up(R, 256), 256, 0, (cudaStream_t)stream>>>(b.rkeys[fin], b.rvals[fin], g.depths, (uint32_t)R,
-                                                                           dev_keys_out);
+    ImageWs im; im.carve(image_buffer, (size_t)width * height, (size_t)tiles);
+    launch_sorted_keys(im.ranges, b.point_list, g.depths, (uint32_t)tiles, dev_keys_out, (cudaStream_t)stream);
     GSB_CUDA_OK(cudaGetLastError());
     return GSB_OK;
 }

@@ -35,7 +35,6 @@ constexpr int WB = 32;   // list entries per warp-private chunk (one per lane)
 
 __global__ void __launch_bounds__(RENDER_THREADS) render_fwd_kernel(const RenderFwdArgs a) {
     __shared__ SplatRec s_rec[RENDER_WARPS][2][WB];
-    __shared__ uint32_t s_max;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int tile = blockIdx.y * a.grid_x + blockIdx.x;
@@ -52,7 +51,6 @@ __global__ void __launch_bounds__(RENDER_THREADS) render_fwd_kernel(const Render
     uint32_t last[2] = {0, 0};
 #pragma unroll
     for (int k = 0; k < 2; k++) done[k] = !(pix_x < a.W && pix_y[k] < a.H);
-    if (tid == 0) s_max = 0;
 
     const uint2 range = a.ranges[tile];
     const int len = (int)(range.y - range.x);
@@ -178,11 +176,10 @@ __global__ void __launch_bounds__(RENDER_THREADS) render_fwd_kernel(const Render
             mx = max(mx, last[k]);
         }
     }
+    // largest n_contrib of the tile: one atomicMax per warp into tile_max (zeroed by tile_sort_kernel / the caller), so
+    // a finished warp retires without waiting at a block barrier for the slowest warp of its tile
     mx = __reduce_max_sync(0xffffffffu, mx);
-    __syncthreads();
-    if (lane == 0 && mx) atomicMax(&s_max, mx);
-    __syncthreads();
-    if (tid == 0) a.tile_max[tile] = s_max;
+    if (lane == 0 && mx) atomicMax(&a.tile_max[tile], mx);
 }
 
 }  // namespace

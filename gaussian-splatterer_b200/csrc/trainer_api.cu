@@ -62,6 +62,10 @@ struct gsb_trainer {
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_fdone[2] = {nullptr, nullptr}, ev_bdone[2] = {nullptr, nullptr};
     // preview arena (Trainer::render at another resolution)
     char* pimg = nullptr; size_t pimg_bytes = 0; float* pcolor = nullptr; size_t pcolor_floats = 0;
+    ImageWs pim; size_t pimg_tiles = 0, pimg_N = 0;
+    bool dirty = false;               // a pass was abandoned half way: tile counters / maxima are re-zeroed before the next one
+    cudaEvent_t ev_x[3] = {nullptr, nullptr, nullptr};   // exchange / apply brackets (stage timing)
+    cudaEvent_t ev_scan = nullptr;    // recorded after the last view pass's tile scan: every R of the iteration is on the host
 
     float* avg_own = nullptr; size_t avg_own_floats = 0;
     float* avg_ext = nullptr;
@@ -78,6 +82,8 @@ struct gsb_trainer {
     gsb_allreduce_fn allreduce = nullptr; void* allreduce_user = nullptr;
     gsb_comm* comm = nullptr;         // gsb_trainer_set_comm: native NCCL exchange, takes precedence over the hook
     bool loss_on = false; double* d_loss = nullptr;
+    // lazy read-back of the loss scalar: two pinned slots, iteration k lands in slot k & 1
+    double* h_loss = nullptr; cudaEvent_t ev_loss[2] = {nullptr, nullptr}; bool loss_pending = false; unsigned loss_iter = 0;
     gsb_trainer_stats stats;
 
     // live stage timing (gsb_trainer_set_stage_timing): one event per stage boundary and view pass
@@ -117,7 +123,7 @@ int ensure_geom(gsb_trainer* t, size_t P) {
         activate(t, k);
         if (t->geom) GSB_CUDA_OK(cudaFree(t->geom));
         GSB_CUDA_OK(cudaMalloc(&t->geom, bytes));
-        GSB_CUDA_OK(cudaMemsetAsync(t->geom, 0, bytes, t->stream));   // look-back words and grad scratch start at zero
+        GSB_CUDA_OK(cudaMemsetAsync(t->geom, 0, bytes, t->stream));   // grad scratch starts at zero
         t->g.carve(t->geom, cap);
         if (t->grads2) GSB_CUDA_OK(cudaFree(t->grads2));
         GSB_CUDA_OK(cudaMalloc(&t->grads2, cap * sizeof(GradRec2)));
@@ -158,7 +164,7 @@ int ensure_avg(gsb_trainer* t) {
 
 // Look-back status words carry a 30-bit epoch tag (binning.cu lb_pack) so the status arrays never need clearing
 // between launches.  Before the tag would wrap, every stream is drained, all look-back arrays are cleared and the
-// counter restarts (one view pass consumes at most 9 epochs, a densify 1).
+// counter restarts (one view pass consumes 1 epoch, a densify 1).
 constexpr uint32_t GSB_EPOCH_LIMIT = 0x3FFFFFFFu - 64u;
 
 int epoch_guard(gsb_trainer* t) {
@@ -169,27 +175,45 @@ int epoch_guard(gsb_trainer* t) {
     save_slot(t);
     for (int k = 0; k < 2; k++) {
         const gsb_trainer::ViewSlot& v = t->slot[k];
-        if (v.geom) GSB_CUDA_OK(cudaMemset(v.g.lookback, 0, GeomWs::lookback_tiles(t->geom_P) * 256 * sizeof(unsigned long long)));
-        if (v.bin) GSB_CUDA_OK(cudaMemset(v.b.lookback, 0, BinWs::lookback_tiles(t->r_cap) * 256 * sizeof(unsigned long long)));
+        if (v.img) GSB_CUDA_OK(cudaMemset(v.im.lookback, 0, ImageWs::lookback_words((size_t)t->tiles) * sizeof(unsigned long long)));
     }
+    if (t->pimg) GSB_CUDA_OK(cudaMemset(t->pim.lookback, 0, ImageWs::lookback_words(t->pimg_tiles) * sizeof(unsigned long long)));
     if (t->dens_lb) GSB_CUDA_OK(cudaMemset(t->dens_lb, 0, ((t->dens_P + 1023) / 1024 + 1) * 4 * sizeof(unsigned long long)));
     t->epoch = 0;
     t->stats.epoch_wraps++;
     return GSB_OK;
 }
 
+// tile_sort_kernel leaves the per-tile counters and maxima of a workspace at zero for the next pass.  A pass that was
+// abandoned half way (an error return) breaks that invariant: drain and re-zero everything before the next one.
+int clean_if_dirty(gsb_trainer* t) {
+    if (!t->dirty) return GSB_OK;
+    GSB_CUDA_OK(cudaStreamSynchronize(t->stream));
+    if (t->sF) GSB_CUDA_OK(cudaStreamSynchronize(t->sF));
+    if (t->sB) GSB_CUDA_OK(cudaStreamSynchronize(t->sB));
+    cudaGetLastError();
+    save_slot(t);
+    for (int k = 0; k < 2; k++)
+        if (t->slot[k].img) GSB_CUDA_OK(cudaMemset(t->slot[k].im.tile_max, 0, t->slot[k].im.zero_bytes((size_t)t->tiles)));
+    if (t->pimg) GSB_CUDA_OK(cudaMemset(t->pim.tile_max, 0, t->pim.zero_bytes(t->pimg_tiles)));
+    t->dirty = false;
+    return GSB_OK;
+}
+
 // Stage boundaries of one view pass (gsb_trainer_profile_pass reports the time between them).
-enum { ST_CLEAR = 0, ST_PREPROCESS, ST_DEPTH_SORT, ST_SCAN, ST_EMIT, ST_TILE_SORT, ST_RANGES, ST_RENDER_FWD,
-       ST_RENDER_BWD, ST_PREPROCESS_BWD, ST_COUNT };
+enum { ST_CLEAR = 0, ST_PREPROCESS, ST_TILE_SCAN, ST_EMIT, ST_TILE_SORT, ST_RENDER_FWD, ST_RENDER_BWD, ST_PREPROCESS_BWD,
+       ST_COUNT };
+static_assert(ST_COUNT == GSB_NUM_STAGES, "stage list of include/gsb.h");
 
 inline void mark(cudaEvent_t* ev, int k, cudaStream_t s) {
     if (ev) cudaEventRecord(ev[k], s);
 }
 
-// forward half of one view pass; returns 100 + index of the buffer holding the sorted list
+// forward half of one view pass: preprocess (+ per-tile counts), tile scan, emit, per-tile sort, render forward
 int forward_pass(gsb_trainer* t, const float* view, const float* projview, const float* campos, float tanx, float tany,
                  float scale_modifier, const float* bg, int W, int H, ImageWs& im, float* out_color, uint32_t* h_R,
-                 cudaEvent_t* ev = nullptr) {
+                 cudaEvent_t* ev = nullptr, cudaEvent_t scan_done = nullptr) {
+    GSB_NVTX("gsb forward chain");
     cudaStream_t s = t->exec_f ? t->exec_f : t->stream;
     const int grid_x = (W + GSB_TILE - 1) / GSB_TILE, grid_y = (H + GSB_TILE - 1) / GSB_TILE;
     const int tiles = grid_x * grid_y;
@@ -197,7 +221,6 @@ int forward_pass(gsb_trainer* t, const float* view, const float* projview, const
     if (int e = epoch_guard(t)) return e;
     mark(ev, ST_CLEAR, s);
     GSB_CUDA_OK(cudaMemsetAsync(t->g.ctrl, 0, sizeof(GsbCtrl), s));
-    GSB_CUDA_OK(cudaMemsetAsync(im.ranges, 0, (size_t)tiles * sizeof(uint2), s));
 
     mark(ev, ST_PREPROCESS, s);
     PreprocessArgs pa;
@@ -211,44 +234,38 @@ int forward_pass(gsb_trainer* t, const float* view, const float* projview, const
     pa.grid_x = grid_x; pa.grid_y = grid_y; pa.prefiltered = 0;
     pa.radii = t->g.radii; pa.radii_user = nullptr; pa.depths = t->g.depths; pa.tiles_touched = t->g.tiles_touched;
     pa.recs = t->g.recs; pa.cov3D = t->g.cov3D; pa.clamped = t->g.clamped;
-    pa.sort_keys = t->g.pkeys[0]; pa.sort_vals = t->g.pvals[0];
-    launch_preprocess_fwd(pa, s);
+    pa.tile_count = im.tile_count; pa.ctrl = t->g.ctrl;
+    { GSB_NVTX("preprocess"); launch_preprocess_fwd(pa, s); }
 
     BinningArgs ba;
-    ba.P = P; ba.r_cap = t->r_cap; ba.grid_x = grid_x; ba.grid_y = grid_y; ba.tile_bits = gsb_tile_bits((uint32_t)tiles);
-    ba.radii = t->g.radii; ba.tiles_touched = t->g.tiles_touched; ba.recs = t->g.recs;
-    ba.pkeys[0] = t->g.pkeys[0]; ba.pkeys[1] = t->g.pkeys[1]; ba.pvals[0] = t->g.pvals[0]; ba.pvals[1] = t->g.pvals[1];
-    ba.offsets = t->g.offsets;
-    ba.rkeys[0] = t->b.rkeys[0]; ba.rkeys[1] = t->b.rkeys[1]; ba.rvals[0] = t->b.rvals[0]; ba.rvals[1] = t->b.rvals[1];
-    ba.ranges = im.ranges; ba.epoch = &t->epoch; ba.ctrl = t->g.ctrl; ba.num_rendered_host = h_R;
-    ba.lookback = t->g.lookback; ba.lookback_tiles = (uint32_t)GeomWs::lookback_tiles(t->geom_P);
-    mark(ev, ST_DEPTH_SORT, s);
-    launch_depth_sort(ba, s);
-    mark(ev, ST_SCAN, s);
-    launch_scan_offsets(ba, s);
-    ba.lookback = t->b.lookback; ba.lookback_tiles = (uint32_t)BinWs::lookback_tiles(t->r_cap);
+    ba.P = P; ba.r_cap = t->r_cap; ba.grid_x = grid_x; ba.grid_y = grid_y;
+    ba.radii = t->g.radii; ba.tiles_touched = t->g.tiles_touched; ba.depths = t->g.depths; ba.recs = t->g.recs;
+    ba.tile_count = im.tile_count; ba.ranges = im.ranges; ba.tile_max = im.tile_max;
+    ba.pairs = t->b.pairs; ba.point_list = t->b.point_list;
+    ba.lookback = im.lookback; ba.epoch = &t->epoch; ba.ctrl = t->g.ctrl; ba.num_rendered_host = h_R;
+    mark(ev, ST_TILE_SCAN, s);
+    { GSB_NVTX("tile scan"); launch_tile_scan(ba, s); }
+    if (scan_done) GSB_CUDA_OK(cudaEventRecord(scan_done, s));   // R of this pass is in pinned host memory once this fires
     mark(ev, ST_EMIT, s);
-    launch_emit(ba, s);
+    { GSB_NVTX("emit"); launch_emit(ba, s); }
     mark(ev, ST_TILE_SORT, s);
-    const int fin = launch_tile_sort(ba, s);
-    mark(ev, ST_RANGES, s);
-    launch_tile_ranges(ba, fin, s);
-    const int npass = gsb_tile_sort_passes(ba.tile_bits);
+    { GSB_NVTX("tile sort"); launch_tile_sort(ba, s); }
 
     mark(ev, ST_RENDER_FWD, s);
     RenderFwdArgs ra;
     ra.W = W; ra.H = H; ra.grid_x = grid_x; ra.grid_y = grid_y;
-    ra.ranges = im.ranges; ra.point_list = t->b.rvals[fin]; ra.recs = t->g.recs; ra.bg = bg;
+    ra.ranges = im.ranges; ra.point_list = t->b.point_list; ra.recs = t->g.recs; ra.bg = bg;
     ra.out_color = out_color; ra.final_T = im.final_T; ra.n_contrib = im.n_contrib; ra.tile_max = im.tile_max;
-    launch_render_fwd(ra, s);
-    t->stats.kernel_launches += 1 + 1 + 4 + 1 + 1 + 1 + npass + 1 + 1;
+    { GSB_NVTX("render forward"); launch_render_fwd(ra, s); }
+    t->stats.kernel_launches += 5;
     GSB_CUDA_OK(cudaGetLastError());
-    return fin + 100;
+    return GSB_OK;
 }
 
 // loss + backward + accumulate.  Unfused: training view pass i of 2n (white passes first, then black,
 // T:311-314).  Fused: camera i of n, both backgrounds in one walk (the forward ran on black).
-int backward_pass(gsb_trainer* t, int i, bool fused, int fin, float* avg, float S, cudaEvent_t* ev = nullptr) {
+int backward_pass(gsb_trainer* t, int i, bool fused, float* avg, float S, cudaEvent_t* ev = nullptr) {
+    GSB_NVTX("gsb backward chain");
     cudaStream_t s = t->exec_b ? t->exec_b : t->stream;
     const int n = (int)t->truthW.size();
     const bool white = fused || i < n;
@@ -259,7 +276,7 @@ int backward_pass(gsb_trainer* t, int i, bool fused, int fin, float* avg, float 
     mark(ev, ST_RENDER_BWD, s);
     RenderBwdArgs rb;
     rb.W = t->W; rb.H = t->H; rb.grid_x = t->grid_x; rb.grid_y = t->grid_y;
-    rb.ranges = t->im.ranges; rb.point_list = t->b.rvals[fin]; rb.recs = t->g.recs; rb.bg = bg;
+    rb.ranges = t->im.ranges; rb.point_list = t->b.point_list; rb.recs = t->g.recs; rb.bg = bg;
     rb.final_T = t->im.final_T; rb.n_contrib = t->im.n_contrib; rb.tile_max = t->im.tile_max;
     rb.dL_dpix = nullptr; rb.truth = truth; rb.rendered = t->rendered; rb.grads = t->g.grads;
     rb.truth2 = fused ? t->truthB[cam] : nullptr; rb.grads2 = fused ? t->grads2 : nullptr;
@@ -285,20 +302,18 @@ int backward_pass(gsb_trainer* t, int i, bool fused, int fin, float* avg, float 
     return GSB_OK;
 }
 
-int view_pass(gsb_trainer* t, int i, bool fused, float* avg, float S, cudaEvent_t* ev = nullptr) {
+int view_pass(gsb_trainer* t, int i, bool fused, float* avg, float S, cudaEvent_t* ev = nullptr, cudaEvent_t scan_done = nullptr) {
     const int n = (int)t->truthW.size();
     const int cam = i % n;
     const gsb_camera* dc = t->d_cams + cam;
     const float* bg = t->d_bg + ((!fused && i < n) ? 0 : 3);
-    const int r = forward_pass(t, dc->view, dc->projview, dc->location, t->cams[cam].tan_fovx, t->cams[cam].tan_fovy, 1.0f, bg,
-                               t->W, t->H, t->im, t->rendered, t->h_R + i, ev);
-    if (r < 100) return r;
+    if (int e = forward_pass(t, dc->view, dc->projview, dc->location, t->cams[cam].tan_fovx, t->cams[cam].tan_fovy, 1.0f, bg,
+                             t->W, t->H, t->im, t->rendered, t->h_R + i, ev, scan_done)) return e;
     if (t->exec_f) {   // pipelined: the backward chain of this pass waits for its forward chain
         GSB_CUDA_OK(cudaEventRecord(t->ev_fdone[t->active], t->exec_f));
         GSB_CUDA_OK(cudaStreamWaitEvent(t->exec_b, t->ev_fdone[t->active], 0));
     }
-    const int e = backward_pass(t, i, fused, r - 100, avg, S, ev);
-    if (e) return e;
+    if (int e = backward_pass(t, i, fused, avg, S, ev)) return e;
     if (t->exec_b) GSB_CUDA_OK(cudaEventRecord(t->ev_bdone[t->active], t->exec_b));
     return GSB_OK;
 }
@@ -327,6 +342,7 @@ int gsb_trainer_create(gsb_trainer** out, int width, int height, void* stream) {
         activate(t, k);
         GSB_CUDA_OK(cudaMalloc(&t->img, ImageWs::required(N, (size_t)t->tiles)));
         t->im.carve(t->img, N, (size_t)t->tiles);
+        GSB_CUDA_OK(cudaMemset(t->im.tile_max, 0, t->im.zero_bytes((size_t)t->tiles)));   // tile_sort_kernel keeps them zero between passes
         GSB_CUDA_OK(cudaMalloc(&t->rendered, 3 * N * sizeof(float)));
         save_slot(t);
     }
@@ -339,12 +355,16 @@ int gsb_trainer_create(gsb_trainer** out, int width, int height, void* stream) {
     GSB_CUDA_OK(cudaStreamCreateWithPriority(&t->sB, cudaStreamNonBlocking, prio_lo));
     GSB_CUDA_OK(cudaEventCreateWithFlags(&t->ev_fork, cudaEventDisableTiming));
     GSB_CUDA_OK(cudaEventCreateWithFlags(&t->ev_join, cudaEventDisableTiming));
+    GSB_CUDA_OK(cudaEventCreateWithFlags(&t->ev_scan, cudaEventDisableTiming));
     for (int k = 0; k < 2; k++) {
         GSB_CUDA_OK(cudaEventCreateWithFlags(&t->ev_fdone[k], cudaEventDisableTiming));
         GSB_CUDA_OK(cudaEventCreateWithFlags(&t->ev_bdone[k], cudaEventDisableTiming));
     }
     GSB_CUDA_OK(cudaMalloc(&t->d_loss, sizeof(double)));
     GSB_CUDA_OK(cudaMemset(t->d_loss, 0, sizeof(double)));
+    GSB_CUDA_OK(cudaHostAlloc(&t->h_loss, 2 * sizeof(double), cudaHostAllocDefault));
+    t->h_loss[0] = t->h_loss[1] = 0.0;
+    for (int k = 0; k < 2; k++) GSB_CUDA_OK(cudaEventCreateWithFlags(&t->ev_loss[k], cudaEventDisableTiming));
     GSB_CUDA_OK(cudaMalloc(&t->totals, 4 * sizeof(uint32_t)));
     GSB_CUDA_OK(cudaMalloc(&t->dens_ticket, sizeof(uint32_t)));
     GSB_CUDA_OK(cudaMalloc(&t->d_pcam, sizeof(gsb_camera)));
@@ -366,12 +386,16 @@ int gsb_trainer_destroy(gsb_trainer* t) {
     }
     if (t->ev_fork) cudaEventDestroy(t->ev_fork);
     if (t->ev_join) cudaEventDestroy(t->ev_join);
+    if (t->ev_scan) cudaEventDestroy(t->ev_scan);
+    for (int k = 0; k < 3; k++) if (t->ev_x[k]) cudaEventDestroy(t->ev_x[k]);
     cudaFree(t->d_cams); cudaFree(t->d_pcam); cudaFree(t->d_bg);
     cudaFree(t->pimg); cudaFree(t->pcolor); cudaFree(t->avg_own); cudaFree(t->d_loss);
     cudaFree(t->flags); cudaFree(t->keep_idx); cudaFree(t->aux_idx); cudaFree(t->totals); cudaFree(t->dens_ticket);
     cudaFree(t->dens_lb); cudaFree(t->d_pairs);
     for (cudaEvent_t e : t->ev_pool) cudaEventDestroy(e);
     if (t->h_R) cudaFreeHost(t->h_R);
+    if (t->h_loss) cudaFreeHost(t->h_loss);
+    for (int k = 0; k < 2; k++) if (t->ev_loss[k]) cudaEventDestroy(t->ev_loss[k]);
     delete t;
     return GSB_OK;
 }
@@ -448,7 +472,21 @@ int gsb_trainer_enable_loss(gsb_trainer* t, int on) {
 
 int gsb_trainer_get_stats(gsb_trainer* t, gsb_trainer_stats* out) {
     if (!t || !out) return gsb_fail_msg("gsb_trainer_get_stats: invalid argument");
+    if (t->loss_pending) {
+        GSB_CUDA_OK(cudaEventSynchronize(t->ev_loss[t->loss_iter & 1]));
+        t->stats.sum_sq_residual = t->h_loss[t->loss_iter & 1];
+        t->loss_pending = false;
+    }
     *out = t->stats;
+    return GSB_OK;
+}
+
+int gsb_trainer_get_loss(gsb_trainer* t, int iterations_back, double* out) {
+    if (!t || !out || iterations_back < 0 || iterations_back > 1) return gsb_fail_msg("gsb_trainer_get_loss: invalid argument");
+    if (!t->loss_on || t->loss_iter < (unsigned)iterations_back + 1u) { gsb_fail_msg("gsb_trainer_get_loss: no such iteration (enable the loss first)"); return GSB_ERR_STATE; }
+    const unsigned slot = (t->loss_iter - (unsigned)iterations_back) & 1u;
+    GSB_CUDA_OK(cudaEventSynchronize(t->ev_loss[slot]));
+    *out = t->h_loss[slot];
     return GSB_OK;
 }
 
@@ -480,9 +518,9 @@ int gsb_trainer_accumulate(gsb_trainer* t) {
     const float S = 2.0f * (float)t->total_cameras;
     t->stats.retries = 0;
 
+    if (int e = clean_if_dirty(t)) return e;
     for (int attempt = 0; attempt < 4; attempt++) {
-        GSB_CUDA_OK(cudaMemsetAsync(avg, 0, grad_floats(t) * sizeof(float), s));
-        if (t->loss_on) GSB_CUDA_OK(cudaMemsetAsync(t->d_loss, 0, sizeof(double), s));
+        GSB_NVTX("gsb accumulate");
         const bool fused = t->fuse_wb;
         const int passes = fused ? n : 2 * n;
         if (t->timing_on) {
@@ -502,13 +540,19 @@ int gsb_trainer_accumulate(gsb_trainer* t) {
             GSB_CUDA_OK(cudaStreamWaitEvent(t->sB, t->ev_fork, 0));
             t->exec_f = t->sF; t->exec_b = t->sB;
         }
+        // zeroing the running means is only needed by the first preprocess backward: on the backward stream it runs
+        // underneath the first forward chain instead of in front of it
+        cudaStream_t sz = pipe ? t->sB : s;
+        GSB_CUDA_OK(cudaMemsetAsync(avg, 0, grad_floats(t) * sizeof(float), sz));
+        if (t->loss_on) GSB_CUDA_OK(cudaMemsetAsync(t->d_loss, 0, sizeof(double), sz));
         int err = GSB_OK;
         for (int i = 0; i < passes && !err; i++) {
             if (pipe) {
                 activate(t, i & 1);
-                if (i >= 2) err = cudaStreamWaitEvent(t->sF, t->ev_bdone[i & 1], 0) == cudaSuccess ? GSB_OK : GSB_ERR_CUDA;
+                if (i >= 2) err = cudaStreamWaitEvent(t->sF, t->ev_bdone[i & 1], 0) == cudaSuccess ? GSB_OK : gsb_fail_msg("cudaStreamWaitEvent failed");
             }
-            if (!err) err = view_pass(t, i, fused, avg, S, t->timing_on ? &t->ev_pool[(size_t)i * (ST_COUNT + 1)] : nullptr);
+            if (!err) err = view_pass(t, i, fused, avg, S, t->timing_on ? &t->ev_pool[(size_t)i * (ST_COUNT + 1)] : nullptr,
+                                      i == passes - 1 ? t->ev_scan : nullptr);
         }
         if (pipe) {
             t->exec_f = t->exec_b = nullptr;
@@ -516,10 +560,14 @@ int gsb_trainer_accumulate(gsb_trainer* t) {
             cudaStreamWaitEvent(s, t->ev_join, 0);
             activate(t, 0);
         }
-        if (err) return err;
+        if (err) { t->dirty = true; return err; }
         GSB_CUDA_OK(cudaGetLastError());
-        // one synchronisation per iteration: learn every view's R, detect arena overflow
-        GSB_CUDA_OK(cudaStreamSynchronize(s));
+        // The host needs every view's R (arena overflow check) before anything may touch the parameters.  It waits for
+        // the LAST TILE SCAN only (the scans of all earlier passes precede it on the forward stream): the last render
+        // forward / backward chain is still queued behind it, so the GPU stays busy while the host checks, returns and
+        // enqueues the all-reduce, apply and the next iteration.  Stage timing needs the whole iteration finished.
+        if (t->timing_on) GSB_CUDA_OK(cudaStreamSynchronize(s));
+        else GSB_CUDA_OK(cudaEventSynchronize(t->ev_scan));
         uint32_t maxR = 0;
         long long total = 0;
         if (fused)
@@ -538,12 +586,18 @@ int gsb_trainer_accumulate(gsb_trainer* t) {
                     }
                 t->stage_passes += passes;
             }
-            if (t->loss_on) GSB_CUDA_OK(cudaMemcpy(&t->stats.sum_sq_residual, t->d_loss, sizeof(double), cudaMemcpyDeviceToHost));
+            if (t->loss_on) {   // read back lazily: gsb_trainer_get_stats waits for this copy, train() does not
+                t->loss_iter++;
+                GSB_CUDA_OK(cudaMemcpyAsync(t->h_loss + (t->loss_iter & 1), t->d_loss, sizeof(double), cudaMemcpyDeviceToHost, s));
+                GSB_CUDA_OK(cudaEventRecord(t->ev_loss[t->loss_iter & 1], s));
+                t->loss_pending = true;
+            }
             return GSB_OK;
         }
         // Some view did not fit: its gradients are incomplete.  Nothing but the running means and the
         // (self-clearing) scratch was written, so grow the arena and redo the iteration.
         t->stats.retries++;
+        GSB_CUDA_OK(cudaStreamSynchronize(s));
         save_slot(t);
         for (int k = 0; k < 2; k++) {
             GSB_CUDA_OK(cudaMemsetAsync(t->slot[k].g.grads, 0, (size_t)t->geom_P * sizeof(GradRec), s));
@@ -565,8 +619,9 @@ int gsb_trainer_profile_pass(gsb_trainer* t, int pass_index, float* stage_ms, un
     }
     cudaEvent_t ev[ST_COUNT + 1];
     for (int k = 0; k <= ST_COUNT; k++) GSB_CUDA_OK(cudaEventCreate(&ev[k]));
+    if (int e = clean_if_dirty(t)) return e;
     const int e = view_pass(t, pass_index, fused, avg_ptr(t), 2.0f * (float)t->total_cameras, ev);
-    if (e) return e;
+    if (e) { t->dirty = true; return e; }
     GSB_CUDA_OK(cudaStreamSynchronize(t->stream));
     for (int k = 0; k < ST_COUNT; k++) GSB_CUDA_OK(cudaEventElapsedTime(&stage_ms[k], ev[k], ev[k + 1]));
     for (int k = 0; k <= ST_COUNT; k++) cudaEventDestroy(ev[k]);
@@ -594,6 +649,8 @@ int gsb_trainer_set_stage_timing(gsb_trainer* t, int on) {
     t->timing_on = on != 0;
     for (int k = 0; k < GSB_NUM_STAGES; k++) t->stage_ms[k] = 0.0;
     t->stage_passes = 0;
+    t->stats.exchange_ms = t->stats.apply_ms = 0.0;
+    t->stats.timed_iterations = 0;
     return GSB_OK;
 }
 
@@ -615,12 +672,15 @@ int gsb_trainer_count_pairs(gsb_trainer* t, int camera_index, unsigned long long
     if (!t->d_pairs) GSB_CUDA_OK(cudaMalloc(&t->d_pairs, 6 * sizeof(unsigned long long)));
     GSB_CUDA_OK(cudaMemsetAsync(t->d_pairs, 0, 6 * sizeof(unsigned long long), s));
     const gsb_camera* dc = t->d_cams + camera_index;
-    const int r = forward_pass(t, dc->view, dc->projview, dc->location, t->cams[camera_index].tan_fovx,
-                               t->cams[camera_index].tan_fovy, 1.0f, t->d_bg + 3, t->W, t->H, t->im, t->rendered, t->h_R);
-    if (r < 100) return r;
+    if (int e = clean_if_dirty(t)) return e;
+    if (int e = forward_pass(t, dc->view, dc->projview, dc->location, t->cams[camera_index].tan_fovx,
+                             t->cams[camera_index].tan_fovy, 1.0f, t->d_bg + 3, t->W, t->H, t->im, t->rendered, t->h_R)) {
+        t->dirty = true;
+        return e;
+    }
     RenderFwdArgs ra;
     ra.W = t->W; ra.H = t->H; ra.grid_x = t->grid_x; ra.grid_y = t->grid_y;
-    ra.ranges = t->im.ranges; ra.point_list = t->b.rvals[r - 100]; ra.recs = t->g.recs; ra.bg = t->d_bg + 3;
+    ra.ranges = t->im.ranges; ra.point_list = t->b.point_list; ra.recs = t->g.recs; ra.bg = t->d_bg + 3;
     ra.out_color = t->rendered; ra.final_T = t->im.final_T; ra.n_contrib = t->im.n_contrib; ra.tile_max = t->im.tile_max;
     launch_count_pairs(ra, t->d_pairs, s);
     GSB_CUDA_OK(cudaMemcpyAsync(out8, t->d_pairs, 6 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
@@ -715,16 +775,33 @@ int gsb_trainer_densify_commit(gsb_trainer* t, float* devLocations, float* devSh
 
 int gsb_trainer_train(gsb_trainer* t, const gsb_project_params* p, int densify, int* new_count) {
     if (!t || !p) return gsb_fail_msg("gsb_trainer_train: invalid argument");
+    GSB_NVTX("gsb train");
     if (int e = gsb_trainer_accumulate(t)) return e;
+    // with stage timing on, the exchange and the update are bracketed too (events on the trainer's stream)
+    const bool timed = t->timing_on;
+    if (timed && !t->ev_x[0])
+        for (int k = 0; k < 3; k++) GSB_CUDA_OK(cudaEventCreate(&t->ev_x[k]));
+    if (timed) GSB_CUDA_OK(cudaEventRecord(t->ev_x[0], t->stream));
     if (t->comm) {
+        GSB_NVTX("all-reduce");
         if (int e = gsb_comm_allreduce_sum(t->comm, avg_ptr(t), grad_floats(t), t->stream)) return e;
     } else if (t->allreduce) {
+        GSB_NVTX("all-reduce hook");
         if (int e = t->allreduce(avg_ptr(t), grad_floats(t), t->stream, t->allreduce_user)) {
             gsb_fail_msg("gsb_trainer_train: all-reduce hook failed");
             return e;
         }
     }
+    if (timed) GSB_CUDA_OK(cudaEventRecord(t->ev_x[1], t->stream));
     if (int e = gsb_trainer_apply(t, p)) return e;
+    if (timed) {
+        GSB_CUDA_OK(cudaEventRecord(t->ev_x[2], t->stream));
+        GSB_CUDA_OK(cudaEventSynchronize(t->ev_x[2]));
+        float a = 0.f, b = 0.f;
+        GSB_CUDA_OK(cudaEventElapsedTime(&a, t->ev_x[0], t->ev_x[1]));
+        GSB_CUDA_OK(cudaEventElapsedTime(&b, t->ev_x[1], t->ev_x[2]));
+        t->stats.exchange_ms += a; t->stats.apply_ms += b; t->stats.timed_iterations++;
+    }
     if (densify) {
         if (!new_count) return gsb_fail_msg("gsb_trainer_train: densify needs new_count");
         return gsb_trainer_densify_plan(t, p, new_count);
@@ -743,6 +820,7 @@ int gsb_trainer_render(gsb_trainer* t, uint32_t* dev_frame_buffer, int width, in
         if (int e = ensure_bin(t, (uint32_t)std::min<size_t>(0x7FFFFFF0u, std::max<size_t>((size_t)1 << 20, (size_t)t->count * 6)))) return e;
     }
     // preview arena: the training image workspace is reused when the size matches (T:159-167)
+    if (int e = clean_if_dirty(t)) return e;
     ImageWs im;
     float* color;
     if (width == t->W && height == t->H) {
@@ -750,16 +828,24 @@ int gsb_trainer_render(gsb_trainer* t, uint32_t* dev_frame_buffer, int width, in
     } else {
         const size_t need = ImageWs::required(N, (size_t)tiles);
         if (need > t->pimg_bytes) {
+            GSB_CUDA_OK(cudaStreamSynchronize(s));
             cudaFree(t->pimg);
             GSB_CUDA_OK(cudaMalloc(&t->pimg, need));
             t->pimg_bytes = need;
+            t->pimg_N = 0;
         }
         if (3 * N > t->pcolor_floats) {
+            GSB_CUDA_OK(cudaStreamSynchronize(s));
             cudaFree(t->pcolor);
             GSB_CUDA_OK(cudaMalloc(&t->pcolor, 3 * N * sizeof(float)));
             t->pcolor_floats = 3 * N;
         }
-        im.carve(t->pimg, N, (size_t)tiles);
+        if (t->pimg_N != N || t->pimg_tiles != (size_t)tiles) {   // new preview size: re-carve, housekeeping arrays start at zero
+            t->pim.carve(t->pimg, N, (size_t)tiles);
+            t->pimg_N = N; t->pimg_tiles = (size_t)tiles;
+            GSB_CUDA_OK(cudaMemsetAsync(t->pim.tile_max, 0, t->pim.zero_bytes((size_t)tiles), s));
+        }
+        im = t->pim;
         color = t->pcolor;
     }
     gsb_camera* dc = t->d_pcam;
@@ -771,9 +857,11 @@ int gsb_trainer_render(gsb_trainer* t, uint32_t* dev_frame_buffer, int width, in
             t->h_R_cap = 2;
         }
         hR = t->h_R;
-        const int r = forward_pass(t, dc->view, dc->projview, dc->location, camera->tan_fovx, camera->tan_fovy, splat_scale,
-                                   t->d_bg + 3, width, height, im, color, hR);
-        if (r < 100) return r;
+        if (int e = forward_pass(t, dc->view, dc->projview, dc->location, camera->tan_fovx, camera->tan_fovy, splat_scale,
+                                 t->d_bg + 3, width, height, im, color, hR)) {
+            t->dirty = true;
+            return e;
+        }
         launch_image_float_to_int(color, dev_frame_buffer, width, height, s);
         t->stats.kernel_launches++;
         GSB_CUDA_OK(cudaStreamSynchronize(s));   // the reference ends render() with a device sync (T:215)

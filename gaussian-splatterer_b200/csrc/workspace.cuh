@@ -27,14 +27,7 @@ struct GeomWs {
     SplatRec* recs;
     float* cov3D;
     uint8_t* clamped;
-    uint32_t* pkeys[2];
-    uint32_t* pvals[2];
-    uint32_t* offsets;
     GradRec* grads;
-    unsigned long long* lookback;
-
-    // scan tiles are 2048 items, sort tiles >= 1024: the sort bounds the tile count
-    static size_t lookback_tiles(size_t P) { return (P + 1023) / 1024 + 1; }
 
     char* carve(char* base, size_t P) {
         Carver c(base);
@@ -45,13 +38,7 @@ struct GeomWs {
         recs = c.take<SplatRec>(P);
         cov3D = c.take<float>(6 * P);
         clamped = c.take<uint8_t>(P);
-        pkeys[0] = c.take<uint32_t>(P);
-        pkeys[1] = c.take<uint32_t>(P);
-        pvals[0] = c.take<uint32_t>(P);
-        pvals[1] = c.take<uint32_t>(P);
-        offsets = c.take<uint32_t>(P);
         grads = c.take<GradRec>(P);
-        lookback = c.take<unsigned long long>(lookback_tiles(P) * 256);
         return c.p;
     }
     static size_t required(size_t P) {
@@ -62,19 +49,13 @@ struct GeomWs {
 
 // Per-duplicate state of one view.
 struct BinWs {
-    uint32_t* rkeys[2];
-    uint32_t* rvals[2];
-    unsigned long long* lookback;
-
-    static size_t lookback_tiles(size_t R) { return (R + 1023) / 1024 + 1; }
+    unsigned long long* pairs;      // [R] depth_bits << 32 | splat, bucketed by tile
+    uint32_t* point_list;           // [R] sorted splat ids
 
     char* carve(char* base, size_t R) {
         Carver c(base);
-        rkeys[0] = c.take<uint32_t>(R);
-        rkeys[1] = c.take<uint32_t>(R);
-        rvals[0] = c.take<uint32_t>(R);
-        rvals[1] = c.take<uint32_t>(R);
-        lookback = c.take<unsigned long long>(lookback_tiles(R) * 256);
+        pairs = c.take<unsigned long long>(R);
+        point_list = c.take<uint32_t>(R);
         return c.p;
     }
     static size_t required(size_t R) {
@@ -89,6 +70,14 @@ struct ImageWs {
     uint32_t* n_contrib;
     uint2* ranges;
     uint32_t* tile_max;
+    uint32_t* tile_count;           // per-tile duplicate count / emit cursor; zero between view passes
+    unsigned long long* lookback;   // chained-scan status words of tile_scan_kernel (2048 tiles per word)
+
+    static size_t lookback_words(size_t tiles) { return (tiles + 2047) / 2048 + 1; }
+    // bytes from `tile_max` to the end of the carved arrays: what must be zero before the first pass
+    size_t zero_bytes(size_t tiles) const {
+        return (size_t)(reinterpret_cast<const char*>(lookback + lookback_words(tiles)) - reinterpret_cast<const char*>(tile_max));
+    }
 
     char* carve(char* base, size_t N, size_t tiles) {
         Carver c(base);
@@ -96,6 +85,8 @@ struct ImageWs {
         n_contrib = c.take<uint32_t>(N);
         ranges = c.take<uint2>(tiles);
         tile_max = c.take<uint32_t>(tiles);
+        tile_count = c.take<uint32_t>(tiles);
+        lookback = c.take<unsigned long long>(lookback_words(tiles));
         return c.p;
     }
     static size_t required(size_t N, size_t tiles) {

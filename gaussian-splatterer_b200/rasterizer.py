@@ -104,9 +104,7 @@ def state(ws, P, width, height, R):
         "rgb": recs[:, 6:9].contiguous(),
         "cov3D": _view(sv.cov3D, (P, 6), torch.float32, dev),
         "clamped": _view(sv.clamped, (P,), torch.uint8, dev),
-        "depth_order": _view(sv.depth_order, (P,), torch.int32, dev),
         "point_list": _view(sv.point_list, (R,), torch.int32, dev),
-        "point_list_tiles": _view(sv.point_list_tiles, (R,), torch.int32, dev),
         "ranges": _view(sv.ranges, (tiles, 2), torch.int32, dev),
         "n_contrib": _view(sv.n_contrib, (height * width,), torch.int32, dev),
         "final_T": _view(sv.final_T, (height * width,), torch.float32, dev),
@@ -115,6 +113,6 @@ def state(ws, P, width, height, R):
     }
     keys = torch.empty(max(R, 1), dtype=torch.int64, device=dev)
     if R > 0:
-        check(lib().gsb_rasterizer_sorted_keys(P, width, height, R, _ptr(ws.geom), _ptr(ws.binning), _ptr(keys), None))
+        check(lib().gsb_rasterizer_sorted_keys(P, width, height, R, _ptr(ws.geom), _ptr(ws.binning), _ptr(ws.image), _ptr(keys), None))
     out["point_list_keys"] = keys[:R]
     return out

@@ -286,17 +286,22 @@ class Trainer:
     def enable_loss(self, on=True):
         check(lib().gsb_trainer_enable_loss(self._h, int(on)))
 
+    def loss(self, iterations_back=0):
+        """Sum of squared residuals of the latest iteration (0) or the one before (1); waits for that value only."""
+        v = C.c_double(0.0)
+        check(lib().gsb_trainer_get_loss(self._h, int(iterations_back), C.byref(v)))
+        return v.value
+
     def stats(self):
         s = TrainerStats()
         check(lib().gsb_trainer_get_stats(self._h, C.byref(s)))
         return {k: getattr(s, k) for k, _ in TrainerStats._fields_}
 
-    STAGES = ("clear", "preprocess", "depth_sort", "scan", "emit", "tile_sort", "ranges", "render_fwd", "render_bwd",
-              "preprocess_bwd")
+    STAGES = ("clear", "preprocess", "tile_scan", "emit", "tile_sort", "render_fwd", "render_bwd", "preprocess_bwd")
 
     def profile_pass(self, pass_index):
         """Per-stage milliseconds (CUDA events) and counters of one training view pass."""
-        ms = (C.c_float * 10)()
+        ms = (C.c_float * 8)()
         cnt = (C.c_uint * 2)()
         check(lib().gsb_trainer_profile_pass(self._h, pass_index, ms, cnt))
         return dict(zip(self.STAGES, [float(x) for x in ms])), {"R": int(cnt[0]), "visible": int(cnt[1])}
@@ -311,7 +316,7 @@ class Trainer:
 
     def stage_times(self):
         """({stage: total ms}, view-pass launches) since set_stage_timing(True)."""
-        ms = (C.c_double * 10)()
+        ms = (C.c_double * 8)()
         n = C.c_longlong(0)
         check(lib().gsb_trainer_get_stage_times(self._h, ms, C.byref(n)))
         return dict(zip(self.STAGES, [float(x) for x in ms])), int(n.value)

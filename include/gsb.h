@@ -85,9 +85,7 @@ typedef struct gsb_state_view {
     const float* recs;                /* [P][12]: x y conic.x conic.y / conic.z opacity r g / b cull-threshold cull-ex cull-ey */
     const float* cov3D;               /* [P][6] */
     const unsigned char* clamped;     /* [P] bit c = channel c clamped */
-    const uint32_t* depth_order;      /* [P] splat ids sorted by depth bits (culled last) */
     const uint32_t* point_list;       /* [R] splat ids sorted by (tile, depth) */
-    const uint32_t* point_list_tiles; /* [R] tile id of each sorted entry */
     const uint32_t* ranges;           /* [tiles][2] */
     const uint32_t* n_contrib;        /* [H*W] */
     const float* final_T;             /* [H*W] */
@@ -99,7 +97,8 @@ int gsb_rasterizer_state(int P, int width, int height, int R, char* geom_buffer,
 /* Materialise the reference's 64-bit sort keys (tile << 32 | depth bits, RI:102-104) of the
  * sorted list into dev_keys_out[R]. */
 int gsb_rasterizer_sorted_keys(int P, int width, int height, int R, char* geom_buffer,
-                               char* binning_buffer, uint64_t* dev_keys_out, void* stream);
+                               char* binning_buffer, char* image_buffer, uint64_t* dev_keys_out,
+                               void* stream);
 
 /* ---- trainer level ---------------------------------------------------------------------- */
 
@@ -203,9 +202,15 @@ typedef struct gsb_trainer_stats {
     long long kernel_launches;     /* kernels launched by this trainer since creation */
     double sum_sq_residual;        /* sum over views of sum(residual^2), if enabled */
     long long epoch_wraps;         /* look-back epoch counter restarts (every ~2^30 look-back launches) */
+    double exchange_ms, apply_ms;  /* with stage timing on: all-reduce and applyGradients, summed over timed_iterations */
+    long long timed_iterations;
 } gsb_trainer_stats;
 int gsb_trainer_get_stats(gsb_trainer* t, gsb_trainer_stats* out);
 int gsb_trainer_enable_loss(gsb_trainer* t, int on);
+/* Sum of squared residuals of the latest iteration (iterations_back = 0) or of the one before it (1).  The scalar is
+ * copied to pinned host memory asynchronously at the end of every iteration; this call waits for that copy only, so
+ * reading iteration k-1 while iteration k runs does not drain the device. */
+int gsb_trainer_get_loss(gsb_trainer* t, int iterations_back, double* out);
 /* White and black pass of a camera (T:311-314) share preprocess, sorts, the forward blend and the
  * alpha / T recomputation of the backward walk (default on; same results up to the summation order
  * of the running means).  0 = one full pass per (camera, background) in the reference's order. */
@@ -213,11 +218,11 @@ int gsb_trainer_set_fuse_backgrounds(gsb_trainer* t, int on);
 
 /* Measurement: run training view pass `pass_index` (0..2n-1, white passes first) once with CUDA
  * events between its stages and return the milliseconds of each, in this order:
- *   0 clear, 1 preprocess, 2 depth sort, 3 offset scan, 4 emit, 5 tile sort, 6 tile ranges,
- *   7 render forward, 8 render backward (+fused loss), 9 preprocess backward (+accumulate).
+ *   0 clear, 1 preprocess (+ per-tile counts), 2 tile scan (ranges, R), 3 emit, 4 per-tile sort,
+ *   5 render forward, 6 render backward (+fused loss), 7 preprocess backward (+accumulate).
  * counters (optional) receives R and the visible-splat count of that pass.  Needs one prior
  * gsb_trainer_accumulate (arenas sized).  The running means are perturbed; call it outside training. */
-#define GSB_NUM_STAGES 10
+#define GSB_NUM_STAGES 8
 int gsb_trainer_profile_pass(gsb_trainer* t, int pass_index, float* stage_ms, unsigned int* counters);
 
 /* View pass i+1's forward chain (preprocess, sorts, forward blend) runs on a second internal stream

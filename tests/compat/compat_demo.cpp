@@ -48,6 +48,7 @@ std::vector<Camera> Camera::getCameras(const Project& project) {
 }
 #endif
 
+static const char* g_stage = "start";   // reported when an exception escapes
 static uint32_t lcg_state = 12345u;
 static float rnd() { lcg_state = lcg_state * 1664525u + 1013904223u; return (float)(lcg_state >> 8) * (1.0f / 16777216.0f); }
 
@@ -145,8 +146,11 @@ static int single_device_demo() {
     project.sphere2.count = 0;
     const std::vector<Camera> cams = Camera::getCameras(project);
 
+    g_stage = "construct";
     Trainer trainer;
+    g_stage = "capture_truths";
     const int rendered = capture_truths(trainer, cams, 2000);
+    g_stage = "train without truths";
 
     // train() with no truths must throw the reference's message: check on a second trainer
     bool threw = false;
@@ -155,13 +159,16 @@ static int single_device_demo() {
         try { empty.train(project, false); } catch (const std::runtime_error&) { threw = true; }
     }
 
+    g_stage = "student";
     set_student(trainer, 3000);
     std::vector<uint32_t> scratch(N);
     uint32_t* devFb;
     cudaMalloc(&devFb, N * sizeof(uint32_t));
     const double err0 = image_error(trainer, cams, scratch, devFb);
     set_rates(project);
+    g_stage = "train x60";
     for (int it = 0; it < 60; it++) trainer.train(project, false);
+    g_stage = "after training";
     const double err1 = image_error(trainer, cams, scratch, devFb);
     const int count0 = trainer.model->count;
     project.paramDensifyVariance = -1.0f;      // every surviving splat splits or clones
@@ -255,7 +262,7 @@ int main(int argc, char** argv) {
     try {
         return devices > 1 ? multi_device_demo(devices) : single_device_demo();
     } catch (const std::exception& e) {
-        fprintf(stderr, "compat_demo: %s\n", e.what());
+        fprintf(stderr, "compat_demo: %s (stage: %s)\n", e.what(), g_stage);
         return 2;
     }
 }

@@ -131,13 +131,18 @@ def test_config_c2_with_periodic_densify_tracks_reference():
             assert worst <= 5e-5, (it, worst)
             counts.append(tr.model.count)
     assert len(counts) == 3                      # iterations 0, 2, 4
-    # and the genuine fused call once more: train(project, true) with everything densifying (no threshold near-ties)
+    # and the genuine fused call once more: train(project, true) = accumulate + apply + densify in one call.  Thresholds
+    # without near-ties: every splat densifies, every densifying splat SPLITS (a clone is displaced along the normalised mean
+    # location gradient, src/Trainer.cu:481-499, which is rounding noise for the many splats whose gradient is ~0), none culled.
     project.paramDensifyVariance = -1.0
+    project.paramSplitSize = 0.0
+    project.paramCullOpacity = -1.0
+    project.paramCullSize = 0.0
     n = tr.model.count
     rt.train(project.params13(), as_shipped=True)
     rt.densify(project.params13())
     tr.train(project, True)
-    assert tr.model.count == rt.count() > n
+    assert tr.model.count == rt.count() == 2 * n
     mine = gsb.ModelSplatsHost.from_device(tr.model)
     assert _match_rows({k: getattr(mine, k) for k in KEYS}, rt.get_model()) <= 5e-5
     rt.close(); tr.close()
@@ -155,7 +160,7 @@ def test_config_c4_running_means_match_reference_replay():
     rt.train(project.params13(), as_shipped=False, apply=False)
     ref = [b.cpu() for b in rt.buffers()]
     for fuse in (True, False):
-        tr = _new_trainer(W, Hh, cloud, cams, tw, tb, square_fov=True)     # Trainer::train's tan_fovx = tan_fovy (T:355-356)
+        tr = _new_trainer(W, Hh, cloud, cams, tw, tb)     # non-square: same aspect-aware tan_fovx as `consts` hands the replay
         tr.set_fuse_backgrounds(fuse)
         avg = tr.grad_tensor()
         tr.accumulate()

@@ -1,0 +1,54 @@
+#!/bin/bash
+# One gpurun call of round 2.  Usage: gpurun --timeout 1800 -- 'bash tools/gpu_round2.sh TAG [sections]'
+# sections (default "test bench ref"): test bench ref ncu refncu full sanitize mgpu
+TAG=${1:-r02}
+shift
+SECTIONS=${*:-test bench ref}
+OUT=gpurun_out
+mkdir -p $OUT
+has() { [[ " $SECTIONS " == *" $1 "* ]]; }
+NGPU=$(nvidia-smi -L | wc -l)
+if has test; then
+  python -m pytest tests -m gpu -x -q > $OUT/${TAG}_pytest.log 2>&1; echo "pytest exit $?" | tee -a $OUT/${TAG}_pytest.log
+  tail -5 $OUT/${TAG}_pytest.log
+fi
+if has bench; then
+  python bench.py --steps 10 --warmup 3 > $OUT/${TAG}_bench_gsb.json 2> $OUT/${TAG}_bench_gsb.err; echo "bench exit $?"
+  head -c 1200 $OUT/${TAG}_bench_gsb.json; echo
+fi
+if has ref; then
+  python bench.py --impl reference --steps 3 --warmup 1 > $OUT/${TAG}_bench_ref.json 2> $OUT/${TAG}_bench_ref.err; echo "ref exit $?"
+  head -c 600 $OUT/${TAG}_bench_ref.json; echo
+fi
+BENCH_SMALL="python bench.py --cameras 2 --steps 2 --warmup 1 --no-cpu-baseline --no-e2e"
+if has ncu; then
+  timeout 600 ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum --clock-control none -c 1500 --csv --log-file $OUT/${TAG}_launches.csv $BENCH_SMALL > $OUT/${TAG}_ncu_launch.log 2>&1; echo "ncu launches exit $?"
+fi
+if has refncu; then
+  # per-kernel table of the REFERENCE build on the same box: one best-case pass over 2+2 cameras x 2 backgrounds at C4
+  timeout 900 ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum --clock-control none -c 3000 --csv --log-file $OUT/${TAG}_ref_launches.csv python bench.py --impl reference --cameras 2 --steps 1 --warmup 1 > $OUT/${TAG}_ncu_ref.log 2>&1; echo "ncu ref exit $?"
+fi
+if has full; then
+  # full capture of the two render kernels in the BENCH configuration (all 64 cameras): roofline.traffic comes from this report
+  CMD="ncu --set full --clock-control none --import-source on -k regex:render_(bwd|fwd)_kernel --launch-skip 40 -c 2 -f -o $OUT/${TAG}_prof_render python bench.py --steps 1 --warmup 1 --no-cpu-baseline --no-e2e"
+  echo "$CMD" > $OUT/${TAG}_prof_render.cmd
+  timeout 900 $CMD > $OUT/${TAG}_ncu_full.log 2>&1; echo "ncu full exit $?"
+fi
+if has sanitize; then
+  timeout 900 compute-sanitizer --tool memcheck --error-exitcode 9 python tools/sanitize_job.py > $OUT/${TAG}_memcheck.log 2>&1; echo "memcheck exit $?"
+  tail -4 $OUT/${TAG}_memcheck.log
+  timeout 1200 compute-sanitizer --tool racecheck --racecheck-report all --error-exitcode 9 python tools/sanitize_job.py > $OUT/${TAG}_racecheck.log 2>&1; echo "racecheck exit $?"
+  tail -4 $OUT/${TAG}_racecheck.log
+  timeout 900 compute-sanitizer --tool synccheck --error-exitcode 9 python tools/sanitize_job.py > $OUT/${TAG}_synccheck.log 2>&1; echo "synccheck exit $?"
+  tail -4 $OUT/${TAG}_synccheck.log
+fi
+if has mgpu; then
+  python -m pytest tests/test_multi_gpu_gpu.py -m gpu -x -q > $OUT/${TAG}_pytest_mgpu.log 2>&1; echo "pytest mgpu exit $?"
+  tail -5 $OUT/${TAG}_pytest_mgpu.log
+  for N in 2 4 8; do
+    if [ $N -le $NGPU ]; then
+      python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 2951$N bench.py --gpus $N --steps 10 --warmup 3 > $OUT/${TAG}_bench_n$N.json 2> $OUT/${TAG}_bench_n$N.err; echo "bench n$N exit $?"
+      head -c 400 $OUT/${TAG}_bench_n$N.json; echo
+    fi
+  done
+fi
