@@ -170,6 +170,7 @@ void launch_render_bwd(const RenderBwdArgs& a, cudaStream_t s);
 // out[6] += { E_eval_f, E_exp_f, E_blend_f, E_eval_b, E_exp_b, E_blend_b }
 void launch_count_pairs(const RenderFwdArgs& a, unsigned long long* out, cudaStream_t s);
 int gsb_measure_fp32_peak_impl(double* out2, cudaStream_t s);
+void launch_bwd_skeleton(const RenderBwdArgs& a, cudaStream_t s);   // A/B lower bound, see measure.cu
 
 // preprocess_bwd.cu
 struct PreprocessBwdArgs {

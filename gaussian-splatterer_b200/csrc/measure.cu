@@ -57,6 +57,102 @@ __global__ void __launch_bounds__(256) count_pairs_kernel(const RenderFwdArgs a,
     }
 }
 
+// ---- A/B skeleton: render backward with lanes = list entries (Mallick et al. 2024) ---------------
+// A LOWER BOUND on the time of a per-splat backward at this workload, measured instead of argued: every warp takes
+// buckets of 32 consecutive list entries of its tile, each lane holds one splat's record and its nine (white, black)
+// sums in registers, and the 256 pixels of the tile stream through the lanes in list order (pixel p is at lane l at
+// step p + l) with the per-pixel running state (T and the two residual-weighted colour prefixes, 3 floats) handed from
+// lane to lane by shfl_up.  Per-pixel constants (two residuals, the two final colour-behind scalars, n_contrib) sit in
+// shared memory.  What a real kernel would need on top is deliberately left out: the forward's per-bucket checkpoints
+// (lane 0 starts every pixel from final_T here), exact equality of the blend decisions, and the fused loss.  Its
+// results are therefore NOT gradients; only its run time is used (gsb_trainer_measure_bwd_skeleton).
+__global__ void __launch_bounds__(128) render_bwd_lanes_are_splats_skeleton(const RenderBwdArgs a) {
+    __shared__ float4 s_pix[256][3];   // {dLw.rgb, SDw}, {dLb.rgb, SDb}, {n_contrib, T_fin, -, -}
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tile = blockIdx.y * a.grid_x + blockIdx.x;
+    const int len = (int)a.tile_max[tile];
+    if (len == 0) return;
+    const uint2 range = a.ranges[tile];
+    const uint32_t* list = a.point_list + range.x;
+    const size_t plane = (size_t)a.W * a.H;
+    for (int p = tid; p < 256; p += 128) {
+        const int x = blockIdx.x * 16 + (p & 15), y = blockIdx.y * 16 + (p >> 4);
+        float4 w = make_float4(0.f, 0.f, 0.f, 0.f), b = w, c = w;
+        if (x < a.W && y < a.H) {
+            const size_t pid = (size_t)y * a.W + x;
+            const float cr = a.rendered[pid], cg = a.rendered[plane + pid], cb = a.rendered[2 * plane + pid];
+            const float Tf = a.final_T[pid];
+            const uint32_t tw = a.truth[pid], tb = a.truth2[pid];
+            w = make_float4((float)(tw & 0xFF) / 255.0f - (cr + Tf), (float)((tw >> 8) & 0xFF) / 255.0f - (cg + Tf),
+                            (float)((tw >> 16) & 0xFF) / 255.0f - (cb + Tf), 0.f);
+            b = make_float4((float)(tb & 0xFF) / 255.0f - cr, (float)((tb >> 8) & 0xFF) / 255.0f - cg,
+                            (float)((tb >> 16) & 0xFF) / 255.0f - cb, 0.f);
+            w.w = w.x * (cr + Tf) + w.y * (cg + Tf) + w.z * (cb + Tf);     // residual . final colour (white)
+            b.w = b.x * cr + b.y * cg + b.z * cb;
+            c = make_float4(__uint_as_float(a.n_contrib[pid]), Tf, 0.f, 0.f);
+        }
+        s_pix[p][0] = w; s_pix[p][1] = b; s_pix[p][2] = c;
+    }
+    __syncthreads();
+    const float ox = (float)(blockIdx.x * 16), oy = (float)(blockIdx.y * 16);
+    const int buckets = (len + 31) / 32;
+    for (int bk = warp; bk < buckets; bk += 4) {
+        const int idx = bk * 32 + lane;
+        const bool valid = idx < len;
+        float4 ra = make_float4(0.f, 0.f, 0.f, 0.f), rb = ra;
+        float2 rc = make_float2(0.f, 0.f);
+        uint32_t splat = 0;
+        if (valid) {
+            splat = list[idx];
+            const SplatRec* g = a.recs + splat;
+            ra = g->a; rb = g->b; rc = make_float2(g->c.x, g->c.y);
+        }
+        float2 sA = make_float2(0.f, 0.f), sB = sA, sC = sA, sD = sA, sE = sA, sF = sA, sr = sA, sg = sA, sb = sA;
+        float T = 1.f, Dw = 0.f, Db = 0.f;
+        bool any = false;
+        for (int step = 0; step < 256 + 31; step++) {
+            // hand-off: the state of pixel p leaves lane l-1 and enters lane l
+            float Tin = __shfl_up_sync(0xffffffffu, T, 1), Dwin = __shfl_up_sync(0xffffffffu, Dw, 1), Dbin = __shfl_up_sync(0xffffffffu, Db, 1);
+            const int p = step - lane;
+            if (lane == 0) { Tin = (p < 256) ? s_pix[p & 255][2].y : 1.f; Dwin = 0.f; Dbin = 0.f; }   // (the forward's checkpoint in a real kernel)
+            T = Tin; Dw = Dwin; Db = Dbin;
+            if (p < 0 || p >= 256 || !valid) continue;
+            const float4 pc = s_pix[p][2];
+            if (idx >= (int)__float_as_uint(pc.x)) continue;
+            const float dx = ra.x - (ox + (float)(p & 15)), dy = ra.y - (oy + (float)(p >> 4));
+            const float power = -0.5f * (ra.z * dx * dx + rb.x * dy * dy) - ra.w * dx * dy;
+            if (power > 0.f || power < rc.y) continue;
+            const float G = expf(power);
+            const float alpha = fminf(0.99f, rb.y * G);
+            if (alpha < 1.0f / 255.0f) continue;
+            any = true;
+            const float4 w = s_pix[p][0], b = s_pix[p][1];
+            const float wgt = alpha * T;
+            const float2 cd = make_float2(rb.z * w.x + rb.w * w.y + rc.x * w.z, rb.z * b.x + rb.w * b.y + rc.x * b.z);
+            Dw = fmaf(wgt, cd.x, Dw); Db = fmaf(wgt, cd.y, Db);
+            const float inv = 1.f / (1.f - alpha);
+            const float2 h = make_float2(G * (T * cd.x - (w.w - Dw) * inv), G * (T * cd.y - (b.w - Db) * inv));
+            T *= (1.f - alpha);
+            sA.x += h.x; sA.y += h.y;
+            sB.x = fmaf(h.x, dx, sB.x); sB.y = fmaf(h.y, dx, sB.y);
+            sC.x = fmaf(h.x, dy, sC.x); sC.y = fmaf(h.y, dy, sC.y);
+            sD.x = fmaf(h.x * dx, dx, sD.x); sD.y = fmaf(h.y * dx, dx, sD.y);
+            sE.x = fmaf(h.x * dx, dy, sE.x); sE.y = fmaf(h.y * dx, dy, sE.y);
+            sF.x = fmaf(h.x * dy, dy, sF.x); sF.y = fmaf(h.y * dy, dy, sF.y);
+            sr.x = fmaf(wgt, w.x, sr.x); sr.y = fmaf(wgt, b.x, sr.y);
+            sg.x = fmaf(wgt, w.y, sg.x); sg.y = fmaf(wgt, b.y, sg.y);
+            sb.x = fmaf(wgt, w.z, sb.x); sb.y = fmaf(wgt, b.z, sb.y);
+        }
+        if (any) {   // one 64-bit RED per pair, issued by the owning lane: no cross-lane reduction at all
+            float* g = reinterpret_cast<float*>(a.grads2 + splat);
+            const float2 v[9] = {sA, sB, sC, sD, sE, sF, sr, sg, sb};
+#pragma unroll
+            for (int q = 0; q < 9; q++)
+                asm volatile("red.global.v2.f32.add [%0], {%1, %2};" ::"l"(g + 2 * q), "f"(v[q].x), "f"(v[q].y) : "memory");
+        }
+    }
+}
+
 // FP32 issue peak, measured: every thread runs 8 independent FFMA chains (scalar) or 8 independent packed FFMA2
 // chains (fma.rn.f32x2: two FMAs per issue slot) long enough for the launch overhead to vanish.  The render kernels'
 // roofline denominator is the scalar figure; the packed one shows what the f32x2 path could add on top.
@@ -131,6 +227,10 @@ int gsb_measure_fp32_peak_impl(double* out2, cudaStream_t s) {
     cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(d_out);
     GSB_CUDA_OK(cudaGetLastError());
     return 0;
+}
+
+void launch_bwd_skeleton(const RenderBwdArgs& a, cudaStream_t s) {
+    render_bwd_lanes_are_splats_skeleton<<<dim3(a.grid_x, a.grid_y), 128, 0, s>>>(a);
 }
 
 void launch_count_pairs(const RenderFwdArgs& a, unsigned long long* out, cudaStream_t s) {

@@ -692,6 +692,50 @@ int gsb_trainer_count_pairs(gsb_trainer* t, int camera_index, unsigned long long
     return GSB_OK;
 }
 
+int gsb_trainer_measure_bwd_skeleton(gsb_trainer* t, int camera_index, int reps, float* out_ms2) {
+    if (!t || !out_ms2 || reps <= 0) return gsb_fail_msg("gsb_trainer_measure_bwd_skeleton: invalid argument");
+    const int n = (int)t->truthW.size();
+    if (n == 0 || camera_index < 0 || camera_index >= n || t->count <= 0 || !t->geom || !t->bin) {
+        gsb_fail_msg("gsb_trainer_measure_bwd_skeleton: run gsb_trainer_accumulate once first");
+        return GSB_ERR_STATE;
+    }
+    cudaStream_t s = t->stream;
+    if (int e = clean_if_dirty(t)) return e;
+    const gsb_camera* dc = t->d_cams + camera_index;
+    if (int e = forward_pass(t, dc->view, dc->projview, dc->location, t->cams[camera_index].tan_fovx,
+                             t->cams[camera_index].tan_fovy, 1.0f, t->d_bg + 3, t->W, t->H, t->im, t->rendered, t->h_R)) {
+        t->dirty = true;
+        return e;
+    }
+    RenderBwdArgs rb;
+    rb.W = t->W; rb.H = t->H; rb.grid_x = t->grid_x; rb.grid_y = t->grid_y;
+    rb.ranges = t->im.ranges; rb.point_list = t->b.point_list; rb.recs = t->g.recs; rb.bg = t->d_bg + 3;
+    rb.final_T = t->im.final_T; rb.n_contrib = t->im.n_contrib; rb.tile_max = t->im.tile_max;
+    rb.dL_dpix = nullptr; rb.truth = t->truthW[camera_index]; rb.rendered = t->rendered; rb.grads = t->g.grads;
+    rb.truth2 = t->truthB[camera_index]; rb.grads2 = t->grads2; rb.loss_out = nullptr;
+    cudaEvent_t e0, e1;
+    GSB_CUDA_OK(cudaEventCreate(&e0));
+    GSB_CUDA_OK(cudaEventCreate(&e1));
+    for (int mode = 0; mode < 2; mode++) {      // 0: the shipped render_bwd_kernel<2>, 1: the lanes = splats skeleton
+        float best = 1e30f;
+        for (int r = 0; r < reps + 1; r++) {
+            GSB_CUDA_OK(cudaEventRecord(e0, s));
+            if (mode == 0) launch_render_bwd(rb, s); else launch_bwd_skeleton(rb, s);
+            GSB_CUDA_OK(cudaEventRecord(e1, s));
+            GSB_CUDA_OK(cudaEventSynchronize(e1));
+            float ms = 0.f;
+            GSB_CUDA_OK(cudaEventElapsedTime(&ms, e0, e1));
+            if (r > 0) best = std::min(best, ms);
+        }
+        out_ms2[mode] = best;
+    }
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    GSB_CUDA_OK(cudaMemsetAsync(t->grads2, 0, (size_t)t->geom_P * sizeof(GradRec2), s));   // the scratch must be clean again
+    GSB_CUDA_OK(cudaStreamSynchronize(s));
+    GSB_CUDA_OK(cudaGetLastError());
+    return GSB_OK;
+}
+
 int gsb_trainer_apply(gsb_trainer* t, const gsb_project_params* p) {
     if (!t || !p) return gsb_fail_msg("gsb_trainer_apply: invalid argument");
     ApplyArgs a;

@@ -246,6 +246,11 @@ int gsb_trainer_count_pairs(gsb_trainer* t, int camera_index, unsigned long long
  * denominator of the render kernels' roofline (MEASURED_PEAKS.json has no FP32 SIMT figure). */
 int gsb_measure_fp32_peak(double* out2, void* stream);
 
+/* Measurement (A/B): time of the shipped fused render backward (out_ms2[0]) and of a skeleton of
+ * the "lanes = list entries" mapping (out_ms2[1], a lower bound: no forward checkpoints, results not gradients) on the
+ * state of local camera `camera_index`, best of `reps`.  Needs one prior gsb_trainer_accumulate. */
+int gsb_trainer_measure_bwd_skeleton(gsb_trainer* t, int camera_index, int reps, float* out_ms2);
+
 /* Testing: preset the look-back epoch counter (30-bit tags in the chained-scan status words) so the wrap
  * path can be exercised without running 2^30 launches. */
 int gsb_trainer_debug_set_epoch(gsb_trainer* t, unsigned int epoch);

@@ -136,7 +136,10 @@ static void set_student(Trainer& trainer, int splats) {
 }
 
 static void set_rates(Project& project) {
-    project.lrLocation = 0.02f; project.lrSh = 0.1f; project.lrScale = 0.002f; project.lrOpacity = 0.05f; project.lrRotation = 0.002f;
+    // the gradients are sums over pixels (src/Trainer.cu:33-44 has no 1/N): rates tuned at 256x256 scale with the pixel count
+    const float k = (256.0f * 256.0f) / ((float)RENDER_RESOLUTION_X * (float)RENDER_RESOLUTION_Y);
+    project.lrLocation = 0.02f * k; project.lrSh = 0.1f * k; project.lrScale = 0.002f * k; project.lrOpacity = 0.05f * k;
+    project.lrRotation = 0.002f * k;
 }
 
 static int single_device_demo() {
