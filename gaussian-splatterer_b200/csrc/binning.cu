@@ -10,9 +10,10 @@
 //   1. preprocess counts, per tile, the splats whose rectangle covers it           (tile_count, one RED per duplicate)
 //   2. tile_scan_kernel: exclusive scan over the tiles -> ranges (= identifyTileRanges' output) and per-tile cursors
 //   3. emit_kernel: every duplicate claims a slot in its tile's range (atomic cursor) and stores depth_bits << 32 | splat
-//   4. tile_sort_kernel: one CTA per tile sorts its own list by that 64-bit key (bitonic network in shared memory;
-//      lists longer than the shared-memory capacity fall back to a hybrid shared/global network) and writes the
-//      splat ids.  The key is unique within a tile, so the unordered claims of step 3 cannot show in the result.
+//   4. tile_sort_kernel: every tile's list is sorted on its own by that 64-bit key -- by one warp in registers (bitonic
+//      network over 32 lanes x up to 32 keys, shuffles between lanes) up to 1024 entries, by the whole CTA in shared /
+//      global memory beyond -- and the splat ids are written out.  The key is unique within a tile, so the unordered
+//      claims of step 3 cannot show in the result.
 // Round-1's decomposed radix sort (4 passes over P + 2 passes over R, fourteen dependent launches, 0.27 ms per view
 // at C4) is replaced by three kernels that move 20 bytes per duplicate.
 
@@ -115,36 +116,101 @@ __global__ void __launch_bounds__(256) tile_scan_kernel(uint32_t* __restrict__ t
 
 // Duplicate emission (duplicateWithKeys, rasterizer_impl.cu:70-111): the rectangle is recomputed from the stored
 // pixel centre and integer radius exactly as the reference does; each duplicate claims the next free slot of its tile.
+// The (splat, tile) pairs of a warp's 32 splats are walked cooperatively (gsb_warp_walk_tiles): all lanes busy, two
+// independent ATOMs in flight per lane and round.
 __global__ void __launch_bounds__(256) emit_kernel(const uint32_t* __restrict__ tiles_touched, const int* __restrict__ radii,
                                                    const float* __restrict__ depths, const SplatRec* __restrict__ recs,
                                                    uint32_t P, int grid_x, int grid_y, uint32_t r_cap,
                                                    uint32_t* __restrict__ cursor, unsigned long long* __restrict__ pairs) {
     const uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
-    if (s >= P) return;
-    if (tiles_touched[s] == 0u) return;
-    const float4 ra = recs[s].a;
-    const float rf = (float)radii[s];
-    const unsigned long long key = ((unsigned long long)__float_as_uint(depths[s]) << 32) | s;
-    const int x0 = (int)__fmul_rn(__fsub_rn(ra.x, rf), 0.0625f), y0 = (int)__fmul_rn(__fsub_rn(ra.y, rf), 0.0625f);
-    const int x1 = (int)__fmul_rn(__fadd_rn(__fadd_rn(__fadd_rn(ra.x, rf), 16.0f), -1.0f), 0.0625f);
-    const int y1 = (int)__fmul_rn(__fadd_rn(__fadd_rn(__fadd_rn(ra.y, rf), 16.0f), -1.0f), 0.0625f);
-    const uint32_t gx = (uint32_t)grid_x, gy = (uint32_t)grid_y;
-    const uint32_t rx0 = min(gx, (uint32_t)max(0, x0)), ry0 = min(gy, (uint32_t)max(0, y0));
-    const uint32_t rx1 = min(gx, (uint32_t)max(0, x1)), ry1 = min(gy, (uint32_t)max(0, y1));
-    for (uint32_t y = ry0; y < ry1; y++)
-        for (uint32_t x = rx0; x < rx1; x++) {
-            const uint32_t pos = atomicAdd(&cursor[y * gx + x], 1u);
-            if (pos < r_cap) pairs[pos] = key;
+    uint32_t cnt = 0, rx0 = 0, ry0 = 0, w = 0, dbits = 0;
+    if (s < P && tiles_touched[s] != 0u) {
+        const float4 ra = recs[s].a;
+        const float rf = (float)radii[s];
+        dbits = __float_as_uint(depths[s]);
+        const int x0 = (int)__fmul_rn(__fsub_rn(ra.x, rf), 0.0625f), y0 = (int)__fmul_rn(__fsub_rn(ra.y, rf), 0.0625f);
+        const int x1 = (int)__fmul_rn(__fadd_rn(__fadd_rn(__fadd_rn(ra.x, rf), 16.0f), -1.0f), 0.0625f);
+        const int y1 = (int)__fmul_rn(__fadd_rn(__fadd_rn(__fadd_rn(ra.y, rf), 16.0f), -1.0f), 0.0625f);
+        const uint32_t gx = (uint32_t)grid_x, gy = (uint32_t)grid_y;
+        rx0 = min(gx, (uint32_t)max(0, x0)); ry0 = min(gy, (uint32_t)max(0, y0));
+        const uint32_t rx1 = min(gx, (uint32_t)max(0, x1)), ry1 = min(gy, (uint32_t)max(0, y1));
+        w = rx1 - rx0;
+        cnt = w * (ry1 - ry0);
+    }
+    if (!__any_sync(0xffffffffu, cnt != 0u)) return;
+    const uint32_t warp_first = s - (threadIdx.x & 31);
+    const uint32_t gxw = (uint32_t)grid_x;
+    gsb_warp_walk_tiles(rx0, ry0, w, cnt, [&](const bool* on, const int* src, const uint32_t* tx, const uint32_t* ty) {
+        uint32_t pos[2] = {0xFFFFFFFFu, 0xFFFFFFFFu};
+        unsigned long long key[2];
+#pragma unroll
+        for (int u = 0; u < 2; u++) {
+            const uint32_t d = __shfl_sync(0xffffffffu, dbits, src[u]);
+            key[u] = ((unsigned long long)d << 32) | (unsigned long long)(warp_first + (uint32_t)src[u]);
+            if (on[u]) pos[u] = atomicAdd(&cursor[ty[u] * gxw + tx[u]], 1u);
         }
+#pragma unroll
+        for (int u = 0; u < 2; u++)
+            if (pos[u] < r_cap) pairs[pos[u]] = key[u];
+    });
 }
 
 // ---- per-tile sort ---------------------------------------------------------------------------------------------
-// Bitonic network in its "always ascending" form: the first sub-stage of merge level k compares element o of a
-// k-block with element k-1-o (mirror), the remaining sub-stages compare i with i + j.  Every comparison puts the
-// smaller key at the lower index, so virtual +inf padding above the list length never moves and a compare-exchange
-// whose upper index is beyond the list is simply skipped.
-constexpr int TS_THREADS = 256;
+// Lists of up to 1024 entries (all but a few tiles at C4) are sorted by ONE WARP entirely in registers: lane l holds
+// elements l*E .. l*E+E-1 of a 32*E-element bitonic network, sub-stages whose partner sits in the same lane are
+// compare-exchanges between registers, the others exchange with lane l ^ (j / E) by shuffle.  No shared memory, no
+// barrier.  The list is loaded striped (coalesced; the network sorts any input order) and padded with ~0.
+// Longer lists are sorted by the whole CTA: a bitonic network in its "always ascending" form in shared memory (the
+// first sub-stage of merge level k compares element o of a k-block with element k-1-o, the remaining sub-stages i with
+// i + j; every comparison puts the smaller key at the lower index, so virtual +inf padding above the list length never
+// moves and a compare-exchange whose upper index is beyond the list is simply skipped), above TS_CAP entries with the
+// wide sub-stages in place in global memory.
+constexpr int TS_THREADS = 256;       // CTA size of the long-list kernel
 constexpr int TS_CAP = 4096;          // keys per shared-memory chunk (32 KB)
+constexpr int TS_WARP_MAX = 1024;     // longest list one warp sorts in registers (32 keys per lane)
+
+template <int E>
+__device__ __forceinline__ void warp_sort_tile(const unsigned long long* __restrict__ keys, int n, uint32_t* __restrict__ out) {
+    const int lane = threadIdx.x & 31;
+    unsigned long long v[E];
+#pragma unroll
+    for (int r = 0; r < E; r++) {
+        const int i = r * 32 + lane;
+        v[r] = (i < n) ? keys[i] : ~0ull;
+    }
+    // element index of register r of lane l: i = l * E + r
+#pragma unroll
+    for (int k = 2; k <= 32 * E; k <<= 1) {
+        // blocks of k elements alternate ascending / descending; the last level (k = 32 E) is ascending everywhere
+        const bool asc_lane = ((lane * E) & k) == 0;
+#pragma unroll
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            if (j >= E) {
+                const int lj = j / E;
+                const bool keep_min = (((lane & lj) == 0) == asc_lane);
+#pragma unroll
+                for (int r = 0; r < E; r++) {
+                    const unsigned long long o = __shfl_xor_sync(0xffffffffu, v[r], lj);
+                    if ((o < v[r]) == keep_min) v[r] = o;     // keep_min: min(v, o); else max(v, o) (keys are distinct or both ~0)
+                }
+            } else {
+#pragma unroll
+                for (int r = 0; r < E; r++) {
+                    if ((r & j) == 0) {
+                        const bool asc = (k >= E) ? asc_lane : ((r & k) == 0);
+                        const unsigned long long a = v[r], b = v[r + j];
+                        if ((b < a) == asc) { v[r] = b; v[r + j] = a; }
+                    }
+                }
+            }
+        }
+    }
+#pragma unroll
+    for (int r = 0; r < E; r++) {
+        const int i = lane * E + r;
+        if (i < n) out[i] = (uint32_t)v[r];
+    }
+}
 
 __device__ __forceinline__ void ce(unsigned long long& a, unsigned long long& b) {
     const unsigned long long lo = min(a, b), hi = max(a, b);
@@ -176,24 +242,9 @@ __device__ __forceinline__ void smem_sort(unsigned long long* s, int m) {
     }
 }
 
-__global__ void __launch_bounds__(TS_THREADS) tile_sort_kernel(const uint2* __restrict__ ranges, unsigned long long* __restrict__ pairs,
-                                                               uint32_t* __restrict__ point_list, uint32_t* __restrict__ tile_count,
-                                                               uint32_t* __restrict__ tile_max) {
-    __shared__ unsigned long long s[TS_CAP];
-    const uint32_t tile = blockIdx.x;
+// whole-CTA sort of one long list (n > TS_WARP_MAX)
+__device__ void cta_sort_tile(unsigned long long* s, unsigned long long* keys, int n, uint32_t* out) {
     const int tid = threadIdx.x;
-    // housekeeping for the kernels around this one: the count / cursor of this tile starts the next view pass at zero,
-    // and the render forward takes the maximum of n_contrib over the tile with atomicMax
-    if (tid == 0) { tile_count[tile] = 0u; tile_max[tile] = 0u; }
-    const uint2 range = ranges[tile];
-    const int n = (int)(range.y - range.x);
-    if (n <= 0) return;
-    unsigned long long* keys = pairs + range.x;
-    uint32_t* out = point_list + range.x;
-    if (n == 1) {
-        if (tid == 0) out[0] = (uint32_t)keys[0];
-        return;
-    }
     int m = 2;
     while (m < n) m <<= 1;
     if (m <= TS_CAP) {
@@ -201,10 +252,11 @@ __global__ void __launch_bounds__(TS_THREADS) tile_sort_kernel(const uint2* __re
         __syncthreads();
         smem_sort(s, m);
         for (int i = tid; i < n; i += TS_THREADS) out[i] = (uint32_t)s[i];
+        __syncthreads();
         return;
     }
-    // Long list: sort TS_CAP-key chunks in shared memory, then merge levels above TS_CAP with their wide sub-stages
-    // (partner at least TS_CAP away) done in place in global memory and the narrow ones per chunk in shared memory.
+    // Sort TS_CAP-key chunks in shared memory, then merge levels above TS_CAP with their wide sub-stages (partner at
+    // least TS_CAP away) done in place in global memory and the narrow ones per chunk in shared memory.
     const int chunks = m / TS_CAP;
     for (int c = 0; c < chunks; c++) {
         const int base = c * TS_CAP;
@@ -249,6 +301,46 @@ __global__ void __launch_bounds__(TS_THREADS) tile_sort_kernel(const uint2* __re
         }
     }
     for (int i = tid; i < n; i += TS_THREADS) out[i] = (uint32_t)keys[i];
+    __syncthreads();
+}
+
+// One 32-thread CTA (one warp) per tile: the list length is uniform over the CTA, so the compiler knows every shuffle
+// of the register network is convergent (inside a per-warp branch of a larger CTA each one is wrapped in
+// WARPSYNC / ENDCOLLECTIVE).  Tiles whose list is too long for one warp are queued for tile_sort_big_kernel.
+__global__ void __launch_bounds__(32) tile_sort_kernel(const uint2* __restrict__ ranges, const unsigned long long* __restrict__ pairs,
+                                                       uint32_t* __restrict__ point_list, uint32_t* __restrict__ tile_count,
+                                                       uint32_t* __restrict__ tile_max, uint32_t* __restrict__ big_list, GsbCtrl* ctrl) {
+    const uint32_t tile = blockIdx.x;
+    // housekeeping for the kernels around this one: the count / cursor of this tile starts the next view pass at zero,
+    // and the render forward takes the maximum of n_contrib over the tile with atomicMax
+    if (threadIdx.x == 0) { tile_count[tile] = 0u; tile_max[tile] = 0u; }
+    const uint2 range = ranges[tile];
+    const int n = (int)(range.y - range.x);
+    if (n <= 0) return;
+    if (n > TS_WARP_MAX) {
+        if (threadIdx.x == 0) big_list[atomicAdd(&ctrl->num_big, 1u)] = tile;
+        return;
+    }
+    const unsigned long long* keys = pairs + range.x;
+    uint32_t* out = point_list + range.x;
+    if (n <= 32) warp_sort_tile<1>(keys, n, out);
+    else if (n <= 64) warp_sort_tile<2>(keys, n, out);
+    else if (n <= 128) warp_sort_tile<4>(keys, n, out);
+    else if (n <= 256) warp_sort_tile<8>(keys, n, out);
+    else if (n <= 512) warp_sort_tile<16>(keys, n, out);
+    else warp_sort_tile<32>(keys, n, out);
+}
+
+// The queued long lists, one per CTA at a time (grid-stride over the queue).
+__global__ void __launch_bounds__(TS_THREADS) tile_sort_big_kernel(const uint2* __restrict__ ranges, unsigned long long* __restrict__ pairs,
+                                                                   uint32_t* __restrict__ point_list, const uint32_t* __restrict__ big_list,
+                                                                   const GsbCtrl* ctrl) {
+    __shared__ unsigned long long s[TS_CAP];
+    const uint32_t count = ctrl->num_big;
+    for (uint32_t q = blockIdx.x; q < count; q += gridDim.x) {
+        const uint2 rg = ranges[big_list[q]];
+        cta_sort_tile(s, pairs + rg.x, (int)(rg.y - rg.x), point_list + rg.x);
+    }
 }
 
 // The reference's 64-bit keys of the sorted list, for the bit-exact parity tests: tile << 32 | depth bits.
@@ -277,7 +369,8 @@ void launch_emit(const BinningArgs& a, cudaStream_t s) {
 
 void launch_tile_sort(const BinningArgs& a, cudaStream_t s) {
     const uint32_t tiles = (uint32_t)(a.grid_x * a.grid_y);
-    tile_sort_kernel<<<tiles, TS_THREADS, 0, s>>>(a.ranges, a.pairs, a.point_list, a.tile_count, a.tile_max);
+    tile_sort_kernel<<<tiles, 32, 0, s>>>(a.ranges, a.pairs, a.point_list, a.tile_count, a.tile_max, a.big_list, a.ctrl);
+    tile_sort_big_kernel<<<min(tiles, 296u), TS_THREADS, 0, s>>>(a.ranges, a.pairs, a.point_list, a.big_list, a.ctrl);
 }
 
 void launch_sorted_keys(const uint2* ranges, const uint32_t* point_list, const float* depths, uint32_t tiles, uint64_t* out,

@@ -34,12 +34,14 @@ struct __align__(16) GradRec2 {
     float2 v[12];   // v[0..5] = H0, Hx, Hy, Hxx, Hxy, Hyy; v[6..8] = dL/dr, dL/dg, dL/db; v[9..11] unused
 };
 
-// Device-resident control block, cleared by one (16-byte) memset per view.
+// Device-resident control block, cleared by one (32-byte) memset per view.
 struct GsbCtrl {
     uint32_t num_rendered;          // R: total duplicates (device copy; host copy is optional)
     uint32_t num_visible;           // splats with radius > 0
     uint32_t overflow;              // 1 if R exceeded the binning capacity
     uint32_t ticket;                // dynamic scan-tile ids of tile_scan_kernel
+    uint32_t num_big;               // tiles queued for tile_sort_big_kernel
+    uint32_t pad[3];
 };
 
 #define GSB_CUDA_OK(expr)                                                              \
@@ -52,6 +54,51 @@ int gsb_fail(cudaError_t e, const char* what, const char* file, int line);
 int gsb_fail_msg(const char* msg);
 
 static inline int gsb_div_up(long long a, long long b) { return (int)((a + b - 1) / b); }
+
+// Warp-cooperative walk over the tile rectangles of the warp's 32 splats (device code, full warp converged).
+// A per-thread loop over its own rectangle runs with ~5 of 32 lanes active (rectangle sizes differ), and every RED /
+// ATOM instruction costs its ~40 LSU cycles whatever the number of active lanes.  Here the (splat, tile) pairs of all
+// lanes are flattened with a warp prefix sum: lane l takes pairs l, l + 32, ... (two per round), finds the owning lane by
+// a 5-step binary search over the prefix (shuffles) and gets the rectangle from that lane.
+//   cnt = tiles of this lane's rectangle (0 if the splat is invisible), rx0 / ry0 / w = its origin and width in tiles.
+//   f(on[2], src_lane[2], tile_x[2], tile_y[2]) is called by ALL lanes once per round with this lane's two pairs
+//   (on[u] false = no pair), so a caller can shuffle from src_lane and issue two atomics back to back (emit_kernel).
+#ifdef __CUDACC__
+template <typename F>
+__device__ __forceinline__ void gsb_warp_walk_tiles(uint32_t rx0, uint32_t ry0, uint32_t w, uint32_t cnt, F&& f) {
+    const int lane = threadIdx.x & 31;
+    uint32_t inc = cnt;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += t;
+    }
+    const uint32_t total = __shfl_sync(0xffffffffu, inc, 31);
+    const uint32_t excl = inc - cnt;
+    for (uint32_t base = 0; base < total; base += 64) {
+        int src[2];
+        uint32_t tx[2], ty[2];
+        bool on[2];
+#pragma unroll
+        for (int u = 0; u < 2; u++) {
+            const uint32_t it = base + 32 * u + lane;
+            int sl = 0;
+#pragma unroll
+            for (int step = 16; step > 0; step >>= 1) {       // largest lane whose exclusive prefix is <= it
+                const int cand = sl + step;
+                const uint32_t e = __shfl_sync(0xffffffffu, excl, cand);
+                if (e <= it) sl = cand;
+            }
+            const uint32_t k = it - __shfl_sync(0xffffffffu, excl, sl);
+            const uint32_t sx = __shfl_sync(0xffffffffu, rx0, sl), sy = __shfl_sync(0xffffffffu, ry0, sl);
+            const uint32_t sw = max(__shfl_sync(0xffffffffu, w, sl), 1u);
+            const uint32_t ky = (uint32_t)__fdividef((float)k + 0.5f, (float)sw);   // k, sw < 2^20: exact floor(k / sw)
+            src[u] = sl; tx[u] = sx + (k - ky * sw); ty[u] = sy + ky; on[u] = it < total;
+        }
+        f(on, src, tx, ty);
+    }
+}
+#endif
 
 // NVTX ranges around the host-side stages: compiled in with `make EXTRA=-DGSB_NVTX`.
 #ifdef GSB_NVTX
@@ -115,6 +162,7 @@ struct BinningArgs {
     uint32_t* tile_count;           // [tiles] per-tile duplicate counts from preprocess; cursors after the scan; zero after the sort
     uint2* ranges;                  // [tiles] written for every tile by the scan
     uint32_t* tile_max;             // [tiles] zeroed by the sort (render forward takes atomicMax into it)
+    uint32_t* big_list;             // [tiles] queue of the tiles whose lists one warp cannot sort in registers
     unsigned long long* pairs;      // [r_cap] depth_bits << 32 | splat, bucketed by tile, sorted in place for long lists
     uint32_t* point_list;           // [r_cap] splat ids sorted by (tile, depth, splat)
     unsigned long long* lookback;   // [scan tiles] chained-scan status words

