@@ -567,6 +567,8 @@ def run_gsb(args):
     if mgpu is not None:
         out["replicas_identical"] = bool(mgpu.get("replicas_identical")) and bool(mgpu.get("rendered_match"))
         out["vs_n1_rel"] = mgpu.get("vs_n1_rel")
+        out["vs_n1_rel_first_iteration"] = mgpu.get("vs_n1_rel_first_iteration")
+        out["n1_rerun_rel"] = mgpu.get("n1_rerun_rel")     # one GPU against itself on the same job: the yardstick for vs_n1_rel
         out["mgpu_check"] = mgpu
     if densify_info is not None:
         out["densify"] = densify_info

@@ -4,9 +4,14 @@ densify block :437-542).  Run under torchrun, one rank per GPU; also called by b
 The job: k = 3 iterations of a camera-sharded trainer with the library's own NCCL exchange (gsb_comm_*), the second one
 densifying (cull + split + clone all occur).  Checked:
   (i)   a 64-bit checksum of count + all five parameter arrays is bit-identical on every rank  -> replicas_identical
-  (ii)  every parameter array is within 1e-5 relative L2 of the N = 1 run of the same job (same canonical densify
-        order)                                                                                 -> vs_n1_rel
-  (iii) R summed over the ranks' view passes equals the N = 1 value                           -> rendered_match
+  (ii)  after the first iteration (sums of per-camera gradients + one linear update) every parameter array is within
+        1e-5 relative L2 of the N = 1 run of the same job                                      -> vs_n1_rel_first_iteration
+  (iii) after all iterations (same canonical densify order, equal counts) the distance to the N = 1 run -> vs_n1_rel,
+        next to the distance between two N = 1 runs of the same job                            -> n1_rerun_rel
+        (clones are displaced along normalize(mean location gradient), src/Trainer.cu:507-515, which turns the
+        summation-order noise of float atomics into O(1e-4..1e-3) relative differences for splats whose gradients
+        nearly cancel -- one GPU against itself shows the same, and that is the yardstick)
+  (iv)  R summed over the ranks' view passes of the first iteration equals the N = 1 value    -> rendered_match
 
     python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29533 \
         tests/mgpu_check.py [--config C3] [--cameras 4]
@@ -106,11 +111,24 @@ def run_check(torch, dist, rank, world, local, config="C4", cameras=8, iteration
     tr = trainer_for(mine, tw, tb, comm)
     pj = copy.deepcopy(project)
     counts = []
-    for it in range(iterations):
-        tr.train(pj, it == densify_at)
-        counts.append(int(tr.model.count))
-    torch.cuda.synchronize()
-    rendered = torch.tensor([tr.stats()["rendered_total"]], dtype=torch.int64, device=dev)
+
+    def run_job(t, p, counts_out):
+        first, rendered_first = None, 0
+        for it in range(iterations):
+            t.train(p, it == densify_at)
+            counts_out.append(int(t.model.count))
+            if it == 0:
+                torch.cuda.synchronize()
+                first = {dk: getattr(t.model, dk).double().clone() for dk in DEVKEYS}
+                rendered_first = int(t.stats()["rendered_total"])
+        torch.cuda.synchronize()
+        return first, rendered_first
+
+    def rel_to(a, b):
+        return float(torch.linalg.norm(a.double() - b.double()) / torch.linalg.norm(b.double()))
+
+    first, r_first = run_job(tr, pj, counts)
+    rendered = torch.tensor([r_first], dtype=torch.int64, device=dev)
     dist.all_reduce(rendered)
     cs = torch.tensor(_checksum(torch, tr.model), dtype=torch.int64, device=dev)
     gathered = [torch.zeros_like(cs) for _ in range(world)]
@@ -123,23 +141,27 @@ def run_check(torch, dist, rank, world, local, config="C4", cameras=8, iteration
     if rank == 0:
         # ---- the same job on ONE GPU --------------------------------------------------------------------------
         one = trainer_for(cams, all_tw, all_tb, None)
-        pj1 = copy.deepcopy(project)
         counts1 = []
-        for it in range(iterations):
-            one.train(pj1, it == densify_at)
-            counts1.append(int(one.model.count))
-        torch.cuda.synchronize()
-        rel = {}
+        first1, r_first1 = run_job(one, copy.deepcopy(project), counts1)
+        again = trainer_for(cams, all_tw, all_tb, None)          # the yardstick: the same N = 1 job once more
+        counts2 = []
+        run_job(again, copy.deepcopy(project), counts2)
+        rel, rerun = {}, {}
+        rel_first = {k: rel_to(first[dk], first1[dk]) for k, dk in zip(KEYS, DEVKEYS)}
         if counts1 == counts:
-            for k, dk in zip(KEYS, DEVKEYS):
-                a, b = getattr(tr.model, dk).double(), getattr(one.model, dk).double()
-                rel[k] = float(torch.linalg.norm(a - b) / torch.linalg.norm(b))
-        res.update({"counts_n1": counts1, "vs_n1_rel": max(rel.values()) if rel else None, "vs_n1_rel_per_array": rel,
-                    "rendered_total": int(rendered.item()), "rendered_total_n1": int(one.stats()["rendered_total"]),
-                    "rendered_match": int(rendered.item()) == int(one.stats()["rendered_total"]),
+            rel = {k: rel_to(getattr(tr.model, dk), getattr(one.model, dk)) for k, dk in zip(KEYS, DEVKEYS)}
+        if counts1 == counts2:
+            rerun = {k: rel_to(getattr(again.model, dk), getattr(one.model, dk)) for k, dk in zip(KEYS, DEVKEYS)}
+        res.update({"counts_n1": counts1, "counts_n1_rerun": counts2,
+                    "vs_n1_rel_first_iteration": max(rel_first.values()),
+                    "vs_n1_rel": max(rel.values()) if rel else None, "vs_n1_rel_per_array": rel,
+                    "n1_rerun_rel": max(rerun.values()) if rerun else None, "n1_rerun_rel_per_array": rerun,
+                    "rendered_first_iteration": int(rendered.item()), "rendered_first_iteration_n1": r_first1,
+                    "rendered_match": int(rendered.item()) == r_first1,
                     "densify_changed_count": counts[densify_at] != P,
                     "thresholds": [float(x) for x in thr.cpu()]})
         one.close()
+        again.close()
     tr.close()
     comm.close()
     return res

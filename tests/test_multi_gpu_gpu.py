@@ -27,7 +27,12 @@ def test_two_ranks_bit_identical_and_equal_to_one_rank(config, cameras):
     res = json.loads(lines[-1][len("MGPU_CHECK "):])
     assert res["replicas_identical"], res
     assert res["counts"] == res["counts_n1"] and res["densify_changed_count"], res
-    assert res["vs_n1_rel"] is not None and res["vs_n1_rel"] <= 1e-5, res
+    res.pop("checksums")
+    assert res["rendered_match"], res
+    assert res["vs_n1_rel_first_iteration"] <= 1e-5, res                 # linear sums + one update: summation order only
+    # after densify + one more iteration the yardstick is one GPU against itself (see mgpu_check.py (iii))
+    assert res["vs_n1_rel"] is not None and res["n1_rerun_rel"] is not None, res
+    assert res["vs_n1_rel"] <= max(1e-5, 5.0 * res["n1_rerun_rel"]), res
     assert res["rendered_match"], res
 
 
