@@ -63,9 +63,13 @@ def parse_args():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-fuse", action="store_true", help="one full pass per (camera, background) like the reference")
     ap.add_argument("--torch-allreduce", action="store_true", help="A/B: torch.distributed.all_reduce through the hook instead of gsb_comm_*")
+    ap.add_argument("--nccl-exchange", action="store_true", help="A/B: ncclAllReduce instead of the library's peer-window kernel (GSB_PEER_EXCHANGE=0)")
     ap.add_argument("--no-mgpu-check", action="store_true", help="skip the N > 1 correctness job (tests/mgpu_check.py)")
     ap.add_argument("--densify-every", type=int, default=0, help="densify every k-th step inside the timed loop (C5 as written)")
-    return ap.parse_args()
+    args = ap.parse_args()
+    if args.nccl_exchange:
+        os.environ["GSB_PEER_EXCHANGE"] = "0"
+    return args
 
 
 # ---------------------------------------------------------------------------------------------
@@ -391,9 +395,10 @@ def run_gsb(args):
     ms_serial = timed_steps(torch, dist, lambda k: tr.train(project, False), args.steps)
     stage_ms, passes = tr.stage_times()
     st_x = tr.stats()
-    iteration_tail = {"exchange_ms": st_x["exchange_ms"] / max(st_x["timed_iterations"], 1),
+    exchange_path = "torch" if (world > 1 and args.torch_allreduce) else tr.exchange_path()
+    iteration_tail = {"exchange_path": exchange_path, "exchange_ms": st_x["exchange_ms"] / max(st_x["timed_iterations"], 1),
                       "apply_ms": st_x["apply_ms"] / max(st_x["timed_iterations"], 1),
-                      "what": "per iteration: all-reduce of the running means (NCCL, on the trainer's stream) and applyGradients; "
+                      "what": "per iteration: all-reduce of the running means (on the trainer's stream) and applyGradients; "
                               "with the first forward chain (nothing to overlap with) they are the serial section of a step"}
     tr.set_stage_timing(False)
 
@@ -534,8 +539,11 @@ def run_gsb(args):
         "config": {"workload": workload_text(args.config, n_total, views_per_step, W, Hh, P),
                    "views_per_step": views_per_step, "cameras_per_rank": n_local,
                    "fused_white_black": fused,
-                   "parallelism": f"cameras partitioned over {world} GPU(s), splats replicated; one NCCL all-reduce of 24 "
-                                  f"floats/splat per iteration issued by libgsb200.so itself (gsb_comm_*)",
+                   "parallelism": f"cameras partitioned over {world} GPU(s), splats replicated; one all-reduce of 24 floats/splat "
+                                  f"per iteration inside libgsb200.so: " + {"peer": "its own two-shot kernel over NVLink peer "
+                                  "windows (gsb_window_allreduce_sum)", "nccl": "ncclAllReduce (gsb_comm_allreduce_sum)",
+                                  "none": "none (one rank)", "torch": "torch.distributed hook"}[exchange_path],
+                   "exchange_path": exchange_path,
                    "l2": "inputs larger than L2: every step streams > 1 GB of truth frames, parameters and per-view state "
                          "through the 126 MB L2; no explicit flush"},
         "gpu_launches": int(launches),
@@ -569,6 +577,7 @@ def run_gsb(args):
         out["vs_n1_rel"] = mgpu.get("vs_n1_rel")
         out["vs_n1_rel_first_iteration"] = mgpu.get("vs_n1_rel_first_iteration")
         out["n1_rerun_rel"] = mgpu.get("n1_rerun_rel")     # one GPU against itself on the same job: the yardstick for vs_n1_rel
+        out["exchange_microbench"] = mgpu.get("exchange_microbench")
         out["mgpu_check"] = mgpu
     if densify_info is not None:
         out["densify"] = densify_info

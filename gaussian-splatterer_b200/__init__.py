@@ -18,7 +18,7 @@ def __getattr__(name):
     if name in ("Rasterizer", "Workspaces", "state"):
         from . import rasterizer
         return getattr(rasterizer, name)
-    if name in ("Trainer", "Comm", "ModelSplatsDevice", "ModelSplatsHost", "camera_struct"):
+    if name in ("Trainer", "Comm", "Window", "ModelSplatsDevice", "ModelSplatsHost", "camera_struct"):
         from . import trainer
         return getattr(trainer, name)
     raise AttributeError(name)

@@ -131,6 +131,20 @@ def lib():
                "broadcast"):
         getattr(L, "gsb_comm_" + _n).restype = i
     L.gsb_trainer_set_comm.restype = i
+    L.gsb_comm_window_create.argtypes = [vp, sz, C.POINTER(vp)]
+    L.gsb_comm_window_create.restype = i
+    L.gsb_comm_window_destroy.argtypes = [vp]
+    L.gsb_comm_window_destroy.restype = i
+    L.gsb_window_data.argtypes = [vp]
+    L.gsb_window_data.restype = vp
+    L.gsb_window_floats.argtypes = [vp]
+    L.gsb_window_floats.restype = sz
+    L.gsb_window_peer_mapped.argtypes = [vp]
+    L.gsb_window_peer_mapped.restype = i
+    L.gsb_window_allreduce_sum.argtypes = [vp, sz, vp]
+    L.gsb_window_allreduce_sum.restype = i
+    L.gsb_trainer_exchange_path.argtypes = [vp]
+    L.gsb_trainer_exchange_path.restype = i
     L.gsb_trainer_measure_bwd_skeleton.argtypes = [vp, i, i, C.POINTER(C.c_float)]
     L.gsb_trainer_measure_bwd_skeleton.restype = i
     L.gsb_measure_fp32_peak.argtypes = [C.POINTER(C.c_double), vp]
@@ -154,7 +168,8 @@ EXPORTED_SYMBOLS = [
     "gsb_trainer_debug_set_epoch", "gsb_measure_fp32_peak", "gsb_trainer_measure_bwd_skeleton",
     "gsb_comm_nccl_version", "gsb_comm_get_unique_id", "gsb_comm_init", "gsb_comm_init_all", "gsb_comm_destroy",
     "gsb_comm_rank", "gsb_comm_world", "gsb_comm_device", "gsb_comm_allreduce_sum", "gsb_comm_broadcast",
-    "gsb_trainer_set_comm",
+    "gsb_trainer_set_comm", "gsb_comm_window_create", "gsb_comm_window_destroy", "gsb_window_data", "gsb_window_floats",
+    "gsb_window_peer_mapped", "gsb_window_allreduce_sum", "gsb_trainer_exchange_path",
     "gsb_image_float_to_int", "gsb_image_int_to_loss",
     "gsb_trainer_create", "gsb_trainer_destroy", "gsb_trainer_bind_model", "gsb_trainer_set_truths",
     "gsb_trainer_set_grad_buffer", "gsb_trainer_grad_floats", "gsb_trainer_grad_buffer",

@@ -80,7 +80,8 @@ struct gsb_trainer {
     uint32_t n_keep = 0, n_split_done = 0, n_clone_done = 0;
 
     gsb_allreduce_fn allreduce = nullptr; void* allreduce_user = nullptr;
-    gsb_comm* comm = nullptr;         // gsb_trainer_set_comm: native NCCL exchange, takes precedence over the hook
+    gsb_comm* comm = nullptr;         // gsb_trainer_set_comm: native exchange, takes precedence over the hook
+    gsb_window* win = nullptr;        // with a communicator the running means live in a peer window (comm.cu)
     bool loss_on = false; double* d_loss = nullptr;
     // lazy read-back of the loss scalar: two pinned slots, iteration k lands in slot k & 1
     double* h_loss = nullptr; cudaEvent_t ev_loss[2] = {nullptr, nullptr}; bool loss_pending = false; unsigned loss_iter = 0;
@@ -153,9 +154,28 @@ int ensure_bin(gsb_trainer* t, uint32_t r_cap) {
     return GSB_OK;
 }
 
+int drop_window(gsb_trainer* t) {
+    if (!t->win) return GSB_OK;
+    const int e = gsb_comm_window_destroy(t->win);      // collective
+    t->win = nullptr; t->avg_own = nullptr; t->avg_own_floats = 0;
+    return e;
+}
+
 int ensure_avg(gsb_trainer* t) {
     const size_t n = grad_floats(t);
-    if (t->avg_ext || n <= t->avg_own_floats) return GSB_OK;
+    if (t->avg_ext) return GSB_OK;
+    if (t->comm && gsb_comm_world(t->comm) > 1) {
+        // Collective: every rank reaches this with the same count (replicas are identical), so all of them keep or
+        // replace their windows in the same iteration.
+        if (t->win && n <= t->avg_own_floats) return GSB_OK;
+        if (t->win) { if (int e = drop_window(t)) return e; }
+        else if (t->avg_own) { GSB_CUDA_OK(cudaFree(t->avg_own)); t->avg_own = nullptr; t->avg_own_floats = 0; }
+        if (int e = gsb_comm_window_create(t->comm, n + n / 2 + 256, &t->win)) return e;
+        t->avg_own = gsb_window_data(t->win);
+        t->avg_own_floats = gsb_window_floats(t->win);
+        return GSB_OK;
+    }
+    if (n <= t->avg_own_floats) return GSB_OK;
     if (t->avg_own) GSB_CUDA_OK(cudaFree(t->avg_own));
     GSB_CUDA_OK(cudaMalloc(&t->avg_own, (n + n / 8 + 256) * sizeof(float)));
     t->avg_own_floats = n + n / 8 + 256;
@@ -389,6 +409,7 @@ int gsb_trainer_destroy(gsb_trainer* t) {
     if (t->ev_scan) cudaEventDestroy(t->ev_scan);
     for (int k = 0; k < 3; k++) if (t->ev_x[k]) cudaEventDestroy(t->ev_x[k]);
     cudaFree(t->d_cams); cudaFree(t->d_pcam); cudaFree(t->d_bg);
+    if (t->win) drop_window(t);        // collective when a communicator is attached: destroy trainers before communicators
     cudaFree(t->pimg); cudaFree(t->pcolor); cudaFree(t->avg_own); cudaFree(t->d_loss);
     cudaFree(t->flags); cudaFree(t->keep_idx); cudaFree(t->aux_idx); cudaFree(t->totals); cudaFree(t->dens_ticket);
     cudaFree(t->dens_lb); cudaFree(t->d_pairs);
@@ -454,8 +475,18 @@ int gsb_trainer_set_allreduce(gsb_trainer* t, gsb_allreduce_fn fn, void* user) {
 
 int gsb_trainer_set_comm(gsb_trainer* t, gsb_comm* comm) {
     if (!t) return gsb_fail_msg("gsb_trainer_set_comm: null trainer");
+    if (comm == t->comm) return GSB_OK;
+    if (t->win) {                      // collective, like the call that created it
+        GSB_CUDA_OK(cudaDeviceSynchronize());
+        if (int e = drop_window(t)) return e;
+    }
     t->comm = comm;
     return GSB_OK;
+}
+
+int gsb_trainer_exchange_path(const gsb_trainer* t) {
+    if (!t || !t->comm || gsb_comm_world(t->comm) <= 1) return 0;
+    return (t->win && !t->avg_ext && gsb_window_peer_mapped(t->win)) ? 2 : 1;
 }
 
 int gsb_trainer_set_fuse_backgrounds(gsb_trainer* t, int on) {
@@ -827,8 +858,10 @@ int gsb_trainer_train(gsb_trainer* t, const gsb_project_params* p, int densify, 
         for (int k = 0; k < 3; k++) GSB_CUDA_OK(cudaEventCreate(&t->ev_x[k]));
     if (timed) GSB_CUDA_OK(cudaEventRecord(t->ev_x[0], t->stream));
     if (t->comm) {
-        GSB_NVTX("all-reduce");
-        if (int e = gsb_comm_allreduce_sum(t->comm, avg_ptr(t), grad_floats(t), t->stream)) return e;
+        GSB_NVTX("exchange");
+        if (t->win && !t->avg_ext) {
+            if (int e = gsb_window_allreduce_sum(t->win, grad_floats(t), t->stream)) return e;    // peer kernel (or NCCL inside)
+        } else if (int e = gsb_comm_allreduce_sum(t->comm, avg_ptr(t), grad_floats(t), t->stream)) return e;
     } else if (t->allreduce) {
         GSB_NVTX("all-reduce hook");
         if (int e = t->allreduce(avg_ptr(t), grad_floats(t), t->stream, t->allreduce_user)) {

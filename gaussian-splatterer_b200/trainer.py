@@ -167,10 +167,53 @@ class Comm:
     def allreduce_sum(self, tensor):
         check(lib().gsb_comm_allreduce_sum(self._h, tensor.data_ptr(), tensor.numel(), None))
 
+    def window(self, floats):
+        """COLLECTIVE: a peer window of `floats` floats (gsb_comm_window_create)."""
+        return Window(self, floats)
+
     def close(self):
         if self._h:
             lib().gsb_comm_destroy(self._h)
             self._h = None
+
+
+class Window:
+    """gsb_window: `floats` floats on this rank that every other rank of the node maps; allreduce_sum() is the library's
+    two-shot kernel over NVLink peer memory (ncclAllReduce inside when the peers could not be mapped)."""
+
+    def __init__(self, comm, floats):
+        h = C.c_void_p()
+        check(lib().gsb_comm_window_create(comm._h, int(floats), C.byref(h)))
+        self._h, self.comm = h, comm
+        self.device = torch.device("cuda", int(lib().gsb_comm_device(comm._h)))
+        self.tensor = _wrap_device_floats(lib().gsb_window_data(h), int(floats), self.device)
+
+    @property
+    def peer_mapped(self):
+        return bool(lib().gsb_window_peer_mapped(self._h))
+
+    def allreduce_sum(self, count=None):
+        n = self.tensor.numel() if count is None else int(count)
+        check(lib().gsb_window_allreduce_sum(self._h, n, C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)))
+
+    def close(self):
+        """COLLECTIVE; before Comm.close()."""
+        if self._h:
+            self.tensor = None
+            check(lib().gsb_comm_window_destroy(self._h))
+            self._h = None
+
+
+class _DeviceFloats:
+    """__cuda_array_interface__ holder so torch can view memory the library owns (no copy, no ownership)."""
+
+    def __init__(self, ptr, n):
+        self.__cuda_array_interface__ = {"shape": (int(n),), "typestr": "<f4", "data": (int(ptr), False), "version": 2}
+
+
+def _wrap_device_floats(ptr, n, device):
+    with torch.cuda.device(device):
+        return torch.as_tensor(_DeviceFloats(ptr, n), device=device)
 
 
 class Trainer:
@@ -192,6 +235,7 @@ class Trainer:
         self._total_cameras = None
         self._allreduce_cb = None
         self._avg = None
+        self._comm = None
         self._render_cams = {}
 
     def close(self):
@@ -200,8 +244,11 @@ class Trainer:
             self._h = None
 
     def __del__(self):
+        # With a communicator the destroy is collective (the running means live in a peer window every rank maps):
+        # never from the garbage collector -- close() explicitly, on every rank, before the Comm.
         try:
-            self.close()
+            if getattr(self, "_comm", None) is None:
+                self.close()
         except Exception:
             pass
 
@@ -216,7 +263,10 @@ class Trainer:
                                                m.devOpacities.data_ptr(), m.devRotations.data_ptr()))
             self._bound = sig
             if self._avg is not None:   # caller-visible gradient buffer must follow the splat count
-                self._alloc_avg()
+                if self._comm is not None:
+                    self._avg = None        # library-owned window: wrapped again on the next grad_tensor()
+                else:
+                    self._alloc_avg()
 
     def set_total_cameras(self, n):
         """Camera count over all ranks (S = 2n in accumulateGradients, src/Trainer.cu:419)."""
@@ -248,6 +298,16 @@ class Trainer:
         """The running-mean buffer [var | loc | sh | scale | opacity | rot] as a torch tensor the
         caller may all-reduce (torch.distributed) between accumulate() and apply()."""
         self._bind()
+        if self._comm is not None:
+            # with a communicator the buffer is the library's peer window (gsb_comm_window_create, allocated collectively
+            # by the first accumulate after the count changed): wrap it, never replace it
+            n = int(lib().gsb_trainer_grad_floats(self._h))
+            ptr = lib().gsb_trainer_grad_buffer(self._h)
+            if not ptr:
+                raise RuntimeError("grad_tensor(): with a communicator the running means exist after the first train()/accumulate()")
+            if self._avg is None or self._avg.data_ptr() != ptr or self._avg.numel() != n:
+                self._avg = _wrap_device_floats(ptr, n, self.device)
+            return self._avg
         if self._avg is None:
             self._alloc_avg()
         return self._avg
@@ -276,8 +336,16 @@ class Trainer:
 
     def set_comm(self, comm):
         """Native exchange: train() all-reduces the running means over `comm` (a Comm) inside libgsb200.so."""
+        if self._avg is not None:
+            torch.cuda.synchronize(self.device)
+            check(lib().gsb_trainer_set_grad_buffer(self._h, None))
+            self._avg = None
         self._comm = comm
         check(lib().gsb_trainer_set_comm(self._h, comm._h if comm is not None else None))
+
+    def exchange_path(self):
+        """"none" (one rank), "nccl" (ncclAllReduce) or "peer" (the library's two-shot kernel over NVLink peer memory)."""
+        return ("none", "nccl", "peer")[int(lib().gsb_trainer_exchange_path(self._h))]
 
     def set_fuse_backgrounds(self, on=True):
         """White + black pass of a camera in one forward / one backward walk (default on)."""

@@ -175,6 +175,27 @@ int gsb_comm_allreduce_sum(gsb_comm* c, float* dev, size_t count, void* stream);
 int gsb_comm_broadcast(gsb_comm* c, void* dev, size_t bytes, int root, void* stream);
 int gsb_trainer_set_comm(gsb_trainer* t, gsb_comm* comm);
 
+/* Peer windows: the exchange as the library's own kernel over NVLink peer memory instead of ncclAllReduce.
+ * gsb_comm_window_create (COLLECTIVE over the communicator) allocates `floats` floats on this rank, ships the
+ * allocation to every other rank (cudaIpc handles between processes, raw pointers + peer access between the devices of
+ * one process) and maps theirs.  gsb_window_allreduce_sum then runs a two-shot kernel on `stream`: rank r reads slice r
+ * of all G windows, adds the G values in rank order and stores the sum into all G windows, between two system-scope
+ * flag barriers; when it returns (in stream order) the local window holds the global sums and may be overwritten.
+ * Each element is summed by one rank and broadcast as bits: replicas are bit-identical by construction.  If any rank
+ * could not map any peer (no P2P / IPC, ranks on different hosts, GSB_PEER_EXCHANGE=0) every rank reports
+ * gsb_window_peer_mapped() == 0 and gsb_window_allreduce_sum forwards to ncclAllReduce on the same buffer.
+ * gsb_comm_window_destroy is COLLECTIVE too and must precede gsb_comm_destroy.  A trainer with a communicator keeps
+ * its running means in such a window (gsb_trainer_exchange_path: 0 none, 1 ncclAllReduce, 2 peer kernel) unless the
+ * caller supplied its own buffer with gsb_trainer_set_grad_buffer. */
+typedef struct gsb_window gsb_window;
+int gsb_comm_window_create(gsb_comm* c, size_t floats, gsb_window** out);
+int gsb_comm_window_destroy(gsb_window* w);
+float* gsb_window_data(gsb_window* w);
+size_t gsb_window_floats(const gsb_window* w);
+int gsb_window_peer_mapped(const gsb_window* w);
+int gsb_window_allreduce_sum(gsb_window* w, size_t count, void* stream);
+int gsb_trainer_exchange_path(const gsb_trainer* t);
+
 /* Trainer::train (T:252-543) split at the point where ranks exchange gradients:
  *   accumulate = zero the means, then forward + loss + backward + accumulate of every local view
  *   apply      = applyGradients (T:428-431)

@@ -17,6 +17,7 @@
 // Prints one JSON line; exit code 0 on success.
 #include <cmath>
 #include <cstdint>
+#include <algorithm>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -201,12 +202,13 @@ struct RunResult {
 };
 
 // k iterations of the same job (6 + 6 cameras, densify on iteration 3 of 5) on `devices` GPUs
+static int g_devices_max = 1;
 static RunResult run_job(int devices) {
     if (devices > 1) setenv("GSB_COMPAT_DEVICES", std::to_string(devices).c_str(), 1);
     else unsetenv("GSB_COMPAT_DEVICES");
     Project project;
-    project.sphere1.count = 6;
-    project.sphere2.count = 6;
+    project.sphere1.count = std::max(6, g_devices_max);      // every rank needs a camera: both runs use the larger set
+    project.sphere2.count = std::max(6, g_devices_max);
     project.sphere2.fovDeg = 30.0f;
     const std::vector<Camera> cams = Camera::getCameras(project);
     Trainer trainer;
@@ -247,6 +249,7 @@ static int multi_device_demo(int devices) {
         printf("{\"skipped\": \"needs %d GPUs, %d visible\"}\n", devices, have);
         return 77;
     }
+    g_devices_max = devices;
     const RunResult one = run_job(1);
     const RunResult many = run_job(devices);
     const double d[5] = {rel_diff(many.loc, one.loc), rel_diff(many.shs, one.shs), rel_diff(many.scales, one.scales),

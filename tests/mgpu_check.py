@@ -50,6 +50,60 @@ def _gap_threshold(values, q):
     return float(0.5 * (v[j] + v[j + 1]))
 
 
+def window_selftest(torch, dist, gsb, comm, dev, rank, world, floats=1000003):
+    """The peer-window all-reduce on its own: random floats per rank, (a) bit-identical result on every rank,
+    (b) equal to the float64 sum of the ranks' inputs rounded once, within the rounding of G-1 float32 additions,
+    (c) a second exchange on the same window (flag sequence numbers) works too."""
+    win = comm.window(floats)
+    out = {"peer_mapped": win.peer_mapped, "floats": floats}
+    worst, same = 0.0, True
+    for rep in range(2):
+        g = torch.Generator(device="cpu").manual_seed(1234 + 97 * rank + rep)
+        x = (torch.rand(floats, generator=g) - 0.5).to(dev)
+        exact = x.double().clone()
+        dist.all_reduce(exact)
+        win.tensor.copy_(x)
+        torch.cuda.synchronize()
+        win.allreduce_sum()
+        torch.cuda.synchronize()
+        y = win.tensor.clone()
+        worst = max(worst, float((y.double() - exact).abs().max()))
+        bits = y.view(torch.int32).to(torch.int64)
+        cs = torch.stack([bits.sum(), (bits * (torch.arange(floats, device=dev) % 8191 + 1)).sum()])
+        gathered = [torch.zeros_like(cs) for _ in range(world)]
+        dist.all_gather(gathered, cs)
+        same = same and all(bool(torch.equal(t, gathered[0])) for t in gathered)
+    out.update({"max_abs_err_vs_f64": worst, "bit_identical": same, "ok": bool(same and worst <= world * 2.0 ** -24 * world)})
+    win.close()
+    return out
+
+
+def exchange_microbench(torch, dist, gsb, comm, dev, world, floats, reps=20):
+    """Back-to-back all-reduces of `floats` floats (rank skew amortised: each exchange re-synchronises the ranks):
+    the library's peer-window kernel against ncclAllReduce on the same communicator.  ms per exchange, max over ranks."""
+    win = comm.window(floats)
+    other = torch.zeros(floats, dtype=torch.float32, device=dev)
+    out = {"floats": int(floats), "mbytes": floats * 4 / 1e6, "reps": reps, "peer_mapped": win.peer_mapped}
+    for name, fn in (("peer_ms", win.allreduce_sum), ("nccl_ms", lambda: comm.allreduce_sum(other))):
+        for _ in range(3):
+            fn()
+        torch.cuda.synchronize()
+        dist.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        t = torch.tensor([e0.elapsed_time(e1) / reps], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        out[name] = float(t.item())
+    out["peer_algbw_gb_s"] = out["mbytes"] / out["peer_ms"]
+    out["nccl_algbw_gb_s"] = out["mbytes"] / out["nccl_ms"]
+    win.close()
+    return out
+
+
 def run_check(torch, dist, rank, world, local, config="C4", cameras=8, iterations=3, densify_at=1):
     import helpers as H
     from gpu_stage_probe import make_truths
@@ -103,6 +157,8 @@ def run_check(torch, dist, rank, world, local, config="C4", cameras=8, iteration
 
     # ---- the N-rank job: camera shards, native NCCL exchange -------------------------------------------------
     comm = gsb.Comm.from_torch_distributed(dist, dev)
+    selftest = window_selftest(torch, dist, gsb, comm, dev, rank, world)
+    micro = exchange_microbench(torch, dist, gsb, comm, dev, world, 24 * P)
     if rank == 0:
         idx = [cams.index(c) for c in mine]
         tw, tb = [all_tw[i] for i in idx], [all_tb[i] for i in idx]
@@ -128,6 +184,7 @@ def run_check(torch, dist, rank, world, local, config="C4", cameras=8, iteration
         return float(torch.linalg.norm(a.double() - b.double()) / torch.linalg.norm(b.double()))
 
     first, r_first = run_job(tr, pj, counts)
+    path = tr.exchange_path()
     rendered = torch.tensor([r_first], dtype=torch.int64, device=dev)
     dist.all_reduce(rendered)
     cs = torch.tensor(_checksum(torch, tr.model), dtype=torch.int64, device=dev)
@@ -137,6 +194,7 @@ def run_check(torch, dist, rank, world, local, config="C4", cameras=8, iteration
 
     res = {"world": world, "config": config, "cameras_total": len(cams), "iterations": iterations,
            "densify_iteration": densify_at, "counts": counts, "replicas_identical": identical,
+           "exchange_path": path, "window_selftest": selftest, "exchange_microbench": micro,
            "checksums": [[int(x) for x in g.cpu().tolist()] for g in gathered]}
     if rank == 0:
         # ---- the same job on ONE GPU --------------------------------------------------------------------------

@@ -52,3 +52,29 @@ if has mgpu; then
     fi
   done
 fi
+if has scale8; then
+  # the 8-GPU evidence of round 2: strong scaling at C4 with the correctness job, C5 with periodic densify, host-link ceiling
+  for N in 4 8; do
+    if [ $N -le $NGPU ]; then
+      python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 2952$N bench.py --gpus $N --steps 10 --warmup 3 > $OUT/${TAG}_bench_n$N.json 2> $OUT/${TAG}_bench_n$N.err; echo "bench n$N exit $?"
+      head -c 300 $OUT/${TAG}_bench_n$N.json; echo
+    fi
+  done
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node $NGPU --master-addr 127.0.0.1 --master-port 29531 bench.py --gpus $NGPU --config C5 --densify-every 2 --steps 6 --warmup 3 --no-mgpu-check > $OUT/${TAG}_bench_c5_n$NGPU.json 2> $OUT/${TAG}_bench_c5_n$NGPU.err; echo "bench c5 exit $?"
+  head -c 300 $OUT/${TAG}_bench_c5_n$NGPU.json; echo
+  timeout 300 python tools/h2d_probe.py --mb 133 --reps 20 > $OUT/${TAG}_h2d_probe.json 2> $OUT/${TAG}_h2d_probe.err; echo "h2d probe exit $?"
+  head -c 600 $OUT/${TAG}_h2d_probe.json; echo
+  (cd tests/compat && timeout 300 ./compat_demo --devices $NGPU > ../../$OUT/${TAG}_compat_devices.json 2> ../../$OUT/${TAG}_compat_devices.err; echo "compat devices exit $?")
+  head -c 400 $OUT/${TAG}_compat_devices.json; echo
+fi
+if has scale8b; then
+  # peer-window exchange at 8 GPUs: full bench line (with the correctness job + exchange microbench), the NCCL A/B, C5 with densify, compat devices
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node $NGPU --master-addr 127.0.0.1 --master-port 29528 bench.py --gpus $NGPU --steps 10 --warmup 3 > $OUT/${TAG}_bench_n$NGPU.json 2> $OUT/${TAG}_bench_n$NGPU.err; echo "bench n$NGPU exit $?"
+  head -c 300 $OUT/${TAG}_bench_n$NGPU.json; echo
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node $NGPU --master-addr 127.0.0.1 --master-port 29529 bench.py --gpus $NGPU --steps 10 --warmup 3 --nccl-exchange --no-mgpu-check --no-cpu-baseline > $OUT/${TAG}_bench_n${NGPU}_nccl.json 2> $OUT/${TAG}_bench_n${NGPU}_nccl.err; echo "bench nccl exit $?"
+  head -c 300 $OUT/${TAG}_bench_n${NGPU}_nccl.json; echo
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node $NGPU --master-addr 127.0.0.1 --master-port 29531 bench.py --gpus $NGPU --config C5 --densify-every 2 --steps 6 --warmup 3 --no-mgpu-check --no-cpu-baseline > $OUT/${TAG}_bench_c5_n$NGPU.json 2> $OUT/${TAG}_bench_c5_n$NGPU.err; echo "bench c5 exit $?"
+  head -c 300 $OUT/${TAG}_bench_c5_n$NGPU.json; echo
+  (cd tests/compat && timeout 300 ./compat_demo --devices $NGPU > ../../$OUT/${TAG}_compat_devices.json 2> ../../$OUT/${TAG}_compat_devices.err; echo "compat devices exit $?")
+  head -c 400 $OUT/${TAG}_compat_devices.json; echo
+fi
