@@ -351,6 +351,8 @@ def run_gsb(args):
 
     # ---- value: inputs resident in HBM ------------------------------------------------------
     tr = new_trainer()
+    if args.densify_every > 0 and comm is None:
+        tr.grad_tensor()     # caller-owned buffer must exist BEFORE the iterations whose means the thresholds are taken from
     for _ in range(args.warmup):
         tr.train(project, False)
     densify_info = None

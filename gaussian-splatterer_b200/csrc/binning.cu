@@ -160,17 +160,15 @@ __global__ void __launch_bounds__(256) emit_kernel(const uint32_t* __restrict__ 
 // elements l*E .. l*E+E-1 of a 32*E-element bitonic network, sub-stages whose partner sits in the same lane are
 // compare-exchanges between registers, the others exchange with lane l ^ (j / E) by shuffle.  No shared memory, no
 // barrier.  The list is loaded striped (coalesced; the network sorts any input order) and padded with ~0.
-// Longer lists are sorted by the whole CTA: a bitonic network in its "always ascending" form in shared memory (the
-// first sub-stage of merge level k compares element o of a k-block with element k-1-o, the remaining sub-stages i with
-// i + j; every comparison puts the smaller key at the lower index, so virtual +inf padding above the list length never
-// moves and a compare-exchange whose upper index is beyond the list is simply skipped), above TS_CAP entries with the
-// wide sub-stages in place in global memory.
-constexpr int TS_THREADS = 256;       // CTA size of the long-list kernel
-constexpr int TS_CAP = 4096;          // keys per shared-memory chunk (32 KB)
-constexpr int TS_WARP_MAX = 1024;     // longest list one warp sorts in registers (32 keys per lane)
+// Longer lists (every tile at C5) are cut into 1024-key chunks, each sorted the same way by its own warp (in place, as
+// keys), and then merged: one CTA per list, log2(chunks) rounds of pairwise merge-path merges between `pairs` and a
+// second buffer, the last round writing the splat ids.
+constexpr int TS_WARP_MAX = 1024;     // longest list (or chunk) one warp sorts in registers (32 keys per lane)
+constexpr int MG_THREADS = 256;       // merge CTA
+constexpr int MG_ITEMS = 8;           // outputs per thread per block of MG_THREADS * MG_ITEMS = 2048 merged keys
 
-template <int E>
-__device__ __forceinline__ void warp_sort_tile(const unsigned long long* __restrict__ keys, int n, uint32_t* __restrict__ out) {
+template <int E, bool IDS>
+__device__ __forceinline__ void warp_sort_tile(const unsigned long long* __restrict__ keys, int n, void* __restrict__ out) {
     const int lane = threadIdx.x & 31;
     unsigned long long v[E];
 #pragma unroll
@@ -205,111 +203,35 @@ __device__ __forceinline__ void warp_sort_tile(const unsigned long long* __restr
             }
         }
     }
+    // (in place is safe: every key of the list is in a register by now)
 #pragma unroll
     for (int r = 0; r < E; r++) {
         const int i = lane * E + r;
-        if (i < n) out[i] = (uint32_t)v[r];
+        if (i < n) {
+            if (IDS) static_cast<uint32_t*>(out)[i] = (uint32_t)v[r];
+            else static_cast<unsigned long long*>(out)[i] = v[r];
+        }
     }
 }
 
-__device__ __forceinline__ void ce(unsigned long long& a, unsigned long long& b) {
-    const unsigned long long lo = min(a, b), hi = max(a, b);
-    a = lo; b = hi;
-}
-
-// sub-stages j = j0, j0/2, ..., 1 of the plain (i, i + j) form on m keys in shared memory (m a power of two)
-__device__ __forceinline__ void smem_plain_stages(unsigned long long* s, int m, int j0) {
-    for (int j = j0; j > 0; j >>= 1) {
-        for (int i = threadIdx.x; i < (m >> 1); i += TS_THREADS) {
-            const int lo = 2 * i - (i & (j - 1));
-            ce(s[lo], s[lo + j]);
-        }
-        __syncthreads();
-    }
-}
-
-// full sort of m keys in shared memory (m a power of two, padded with ~0)
-__device__ __forceinline__ void smem_sort(unsigned long long* s, int m) {
-    for (int k = 2; k <= m; k <<= 1) {
-        const int half = k >> 1;
-        for (int i = threadIdx.x; i < (m >> 1); i += TS_THREADS) {
-            const int b = i / half, o = i - b * half;
-            const int lo = b * k + o;
-            ce(s[lo], s[b * k + k - 1 - o]);
-        }
-        __syncthreads();
-        smem_plain_stages(s, m, half >> 1);
-    }
-}
-
-// whole-CTA sort of one long list (n > TS_WARP_MAX)
-__device__ void cta_sort_tile(unsigned long long* s, unsigned long long* keys, int n, uint32_t* out) {
-    const int tid = threadIdx.x;
-    int m = 2;
-    while (m < n) m <<= 1;
-    if (m <= TS_CAP) {
-        for (int i = tid; i < m; i += TS_THREADS) s[i] = (i < n) ? keys[i] : ~0ull;
-        __syncthreads();
-        smem_sort(s, m);
-        for (int i = tid; i < n; i += TS_THREADS) out[i] = (uint32_t)s[i];
-        __syncthreads();
-        return;
-    }
-    // Sort TS_CAP-key chunks in shared memory, then merge levels above TS_CAP with their wide sub-stages (partner at
-    // least TS_CAP away) done in place in global memory and the narrow ones per chunk in shared memory.
-    const int chunks = m / TS_CAP;
-    for (int c = 0; c < chunks; c++) {
-        const int base = c * TS_CAP;
-        if (base >= n) break;
-        for (int i = tid; i < TS_CAP; i += TS_THREADS) s[i] = (base + i < n) ? keys[base + i] : ~0ull;
-        __syncthreads();
-        smem_sort(s, TS_CAP);
-        for (int i = tid; i < TS_CAP; i += TS_THREADS)
-            if (base + i < n) keys[base + i] = s[i];
-        __syncthreads();
-    }
-    for (int k = 2 * TS_CAP; k <= m; k <<= 1) {
-        const int half = k >> 1;
-        for (int i = tid; i < (m >> 1); i += TS_THREADS) {          // mirror sub-stage
-            const int b = i / half, o = i - b * half;
-            const int lo = b * k + o, hi = b * k + k - 1 - o;
-            if (hi < n) {
-                unsigned long long a = keys[lo], z = keys[hi];
-                if (z < a) { keys[lo] = z; keys[hi] = a; }
-            }
-        }
-        __syncthreads();
-        for (int j = half >> 1; j >= TS_CAP; j >>= 1) {             // wide plain sub-stages
-            for (int i = tid; i < (m >> 1); i += TS_THREADS) {
-                const int lo = 2 * i - (i & (j - 1)), hi = lo + j;
-                if (hi < n) {
-                    unsigned long long a = keys[lo], z = keys[hi];
-                    if (z < a) { keys[lo] = z; keys[hi] = a; }
-                }
-            }
-            __syncthreads();
-        }
-        for (int c = 0; c < chunks; c++) {                          // narrow sub-stages, chunk by chunk
-            const int base = c * TS_CAP;
-            if (base >= n) break;
-            for (int i = tid; i < TS_CAP; i += TS_THREADS) s[i] = (base + i < n) ? keys[base + i] : ~0ull;
-            __syncthreads();
-            smem_plain_stages(s, TS_CAP, TS_CAP >> 1);
-            for (int i = tid; i < TS_CAP; i += TS_THREADS)
-                if (base + i < n) keys[base + i] = s[i];
-            __syncthreads();
-        }
-    }
-    for (int i = tid; i < n; i += TS_THREADS) out[i] = (uint32_t)keys[i];
-    __syncthreads();
+template <bool IDS>
+__device__ __forceinline__ void warp_sort_dispatch(const unsigned long long* keys, int n, void* out) {
+    if (n <= 32) warp_sort_tile<1, IDS>(keys, n, out);
+    else if (n <= 64) warp_sort_tile<2, IDS>(keys, n, out);
+    else if (n <= 128) warp_sort_tile<4, IDS>(keys, n, out);
+    else if (n <= 256) warp_sort_tile<8, IDS>(keys, n, out);
+    else if (n <= 512) warp_sort_tile<16, IDS>(keys, n, out);
+    else warp_sort_tile<32, IDS>(keys, n, out);
 }
 
 // One 32-thread CTA (one warp) per tile: the list length is uniform over the CTA, so the compiler knows every shuffle
 // of the register network is convergent (inside a per-warp branch of a larger CTA each one is wrapped in
-// WARPSYNC / ENDCOLLECTIVE).  Tiles whose list is too long for one warp are queued for tile_sort_big_kernel.
+// WARPSYNC / ENDCOLLECTIVE).  A list too long for one warp is queued: the tile for the merge kernel, its chunks for
+// the chunk-sort kernel.
 __global__ void __launch_bounds__(32) tile_sort_kernel(const uint2* __restrict__ ranges, const unsigned long long* __restrict__ pairs,
                                                        uint32_t* __restrict__ point_list, uint32_t* __restrict__ tile_count,
-                                                       uint32_t* __restrict__ tile_max, uint32_t* __restrict__ big_list, GsbCtrl* ctrl) {
+                                                       uint32_t* __restrict__ tile_max, uint32_t* __restrict__ big_list,
+                                                       uint2* __restrict__ chunk_list, GsbCtrl* ctrl) {
     const uint32_t tile = blockIdx.x;
     // housekeeping for the kernels around this one: the count / cursor of this tile starts the next view pass at zero,
     // and the render forward takes the maximum of n_contrib over the tile with atomicMax
@@ -318,28 +240,86 @@ __global__ void __launch_bounds__(32) tile_sort_kernel(const uint2* __restrict__
     const int n = (int)(range.y - range.x);
     if (n <= 0) return;
     if (n > TS_WARP_MAX) {
-        if (threadIdx.x == 0) big_list[atomicAdd(&ctrl->num_big, 1u)] = tile;
+        const uint32_t chunks = ((uint32_t)n + TS_WARP_MAX - 1) / TS_WARP_MAX;
+        uint32_t base = 0;
+        if (threadIdx.x == 0) {
+            big_list[atomicAdd(&ctrl->num_big, 1u)] = tile;
+            base = atomicAdd(&ctrl->num_chunks, chunks);
+        }
+        base = __shfl_sync(0xffffffffu, base, 0);
+        for (uint32_t c = threadIdx.x; c < chunks; c += 32) chunk_list[base + c] = make_uint2(tile, c);
         return;
     }
-    const unsigned long long* keys = pairs + range.x;
-    uint32_t* out = point_list + range.x;
-    if (n <= 32) warp_sort_tile<1>(keys, n, out);
-    else if (n <= 64) warp_sort_tile<2>(keys, n, out);
-    else if (n <= 128) warp_sort_tile<4>(keys, n, out);
-    else if (n <= 256) warp_sort_tile<8>(keys, n, out);
-    else if (n <= 512) warp_sort_tile<16>(keys, n, out);
-    else warp_sort_tile<32>(keys, n, out);
+    warp_sort_dispatch<true>(pairs + range.x, n, point_list + range.x);
 }
 
-// The queued long lists, one per CTA at a time (grid-stride over the queue).
-__global__ void __launch_bounds__(TS_THREADS) tile_sort_big_kernel(const uint2* __restrict__ ranges, unsigned long long* __restrict__ pairs,
-                                                                   uint32_t* __restrict__ point_list, const uint32_t* __restrict__ big_list,
-                                                                   const GsbCtrl* ctrl) {
-    __shared__ unsigned long long s[TS_CAP];
+// Persistent one-warp CTAs over the chunk queue (uniform control flow again: the queue index comes from blockIdx).
+__global__ void __launch_bounds__(32, 24) chunk_sort_kernel(const uint2* __restrict__ ranges, unsigned long long* __restrict__ pairs,
+                                                        const uint2* __restrict__ chunk_list, const GsbCtrl* ctrl) {
+    const uint32_t count = ctrl->num_chunks;
+    for (uint32_t q = blockIdx.x; q < count; q += gridDim.x) {
+        const uint2 e = chunk_list[q];
+        const uint2 range = ranges[e.x];
+        const uint32_t off = e.y * TS_WARP_MAX;
+        const int m = (int)min((uint32_t)TS_WARP_MAX, range.y - range.x - off);
+        unsigned long long* keys = pairs + range.x + off;
+        warp_sort_dispatch<false>(keys, m, keys);
+    }
+}
+
+// Merge rounds of the queued long lists, one list per CTA at a time.  Round w merges runs [2pw, 2pw + w) and
+// [2pw + w, 2pw + 2w) of `src` into `dst`; every thread finds the merge-path split of its diagonal by binary search
+// (keys are distinct), stages the at most MG_ITEMS keys it can need from each run in shared memory with independent
+// loads, and merges MG_ITEMS outputs from there.  The last round stores the splat ids into the point list.
+__global__ void __launch_bounds__(MG_THREADS) tile_merge_kernel(const uint2* __restrict__ ranges, unsigned long long* __restrict__ pairs,
+                                                               unsigned long long* __restrict__ pairs2, uint32_t* __restrict__ point_list,
+                                                               const uint32_t* __restrict__ big_list, const GsbCtrl* ctrl) {
+    __shared__ unsigned long long s_a[MG_ITEMS][MG_THREADS], s_b[MG_ITEMS][MG_THREADS];
+    const int tid = threadIdx.x;
     const uint32_t count = ctrl->num_big;
     for (uint32_t q = blockIdx.x; q < count; q += gridDim.x) {
         const uint2 rg = ranges[big_list[q]];
-        cta_sort_tile(s, pairs + rg.x, (int)(rg.y - rg.x), point_list + rg.x);
+        const int n = (int)(rg.y - rg.x);
+        const unsigned long long* src = pairs + rg.x;
+        unsigned long long* dst = pairs2 + rg.x;
+        uint32_t* ids = point_list + rg.x;
+        for (int w = TS_WARP_MAX; w < n; w <<= 1) {
+            const bool last = 2 * w >= n;
+            for (int o0 = tid * MG_ITEMS; o0 < n; o0 += MG_THREADS * MG_ITEMS) {
+                const int pbase = (o0 / (2 * w)) * (2 * w);          // 2w is a multiple of MG_ITEMS: no straddling
+                const unsigned long long* A = src + pbase;
+                const int la = min(w, n - pbase), lb = min(w, n - pbase - la);
+                const unsigned long long* B = A + la;
+                const int d = o0 - pbase;
+                int lo = max(0, d - lb), hi = min(d, la);
+                while (lo < hi) {
+                    const int mid = (lo + hi) >> 1;
+                    if (A[mid] < B[d - 1 - mid]) lo = mid + 1; else hi = mid;
+                }
+                int i = lo, j = d - lo;
+                const int cnt = min(MG_ITEMS, la + lb - d);
+#pragma unroll
+                for (int k = 0; k < MG_ITEMS; k++) {
+                    s_a[k][tid] = (i + k < la) ? A[i + k] : ~0ull;
+                    s_b[k][tid] = (j + k < lb) ? B[j + k] : ~0ull;
+                }
+                int ia = 0, ib = 0;
+                unsigned long long a = s_a[0][tid], b = s_b[0][tid];
+#pragma unroll
+                for (int k = 0; k < MG_ITEMS; k++) {
+                    const bool take_a = a < b;
+                    const unsigned long long v = take_a ? a : b;
+                    if (take_a) { ia++; a = ia < MG_ITEMS ? s_a[ia][tid] : ~0ull; }
+                    else { ib++; b = ib < MG_ITEMS ? s_b[ib][tid] : ~0ull; }
+                    if (k < cnt) {
+                        if (last) ids[o0 + k] = (uint32_t)v;
+                        else dst[o0 + k] = v;
+                    }
+                }
+            }
+            __syncthreads();              // the round's stores are visible to the whole CTA; shared staging is per thread
+            const unsigned long long* t = src; src = dst; dst = const_cast<unsigned long long*>(t);
+        }
     }
 }
 
@@ -369,8 +349,10 @@ void launch_emit(const BinningArgs& a, cudaStream_t s) {
 
 void launch_tile_sort(const BinningArgs& a, cudaStream_t s) {
     const uint32_t tiles = (uint32_t)(a.grid_x * a.grid_y);
-    tile_sort_kernel<<<tiles, 32, 0, s>>>(a.ranges, a.pairs, a.point_list, a.tile_count, a.tile_max, a.big_list, a.ctrl);
-    tile_sort_big_kernel<<<min(tiles, 296u), TS_THREADS, 0, s>>>(a.ranges, a.pairs, a.point_list, a.big_list, a.ctrl);
+    tile_sort_kernel<<<tiles, 32, 0, s>>>(a.ranges, a.pairs, a.point_list, a.tile_count, a.tile_max, a.big_list, a.chunk_list, a.ctrl);
+    // the two kernels of the long lists run over device-side queues (empty at C4 but for a few tiles): fixed grids
+    chunk_sort_kernel<<<148 * 16, 32, 0, s>>>(a.ranges, a.pairs, a.chunk_list, a.ctrl);
+    tile_merge_kernel<<<min(tiles, 148u * 4u), MG_THREADS, 0, s>>>(a.ranges, a.pairs, a.pairs2, a.point_list, a.big_list, a.ctrl);
 }
 
 void launch_sorted_keys(const uint2* ranges, const uint32_t* point_list, const float* depths, uint32_t tiles, uint64_t* out,

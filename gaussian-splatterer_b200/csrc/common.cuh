@@ -40,8 +40,9 @@ struct GsbCtrl {
     uint32_t num_visible;           // splats with radius > 0
     uint32_t overflow;              // 1 if R exceeded the binning capacity
     uint32_t ticket;                // dynamic scan-tile ids of tile_scan_kernel
-    uint32_t num_big;               // tiles queued for tile_sort_big_kernel
-    uint32_t pad[3];
+    uint32_t num_big;               // tiles queued for tile_merge_kernel
+    uint32_t num_chunks;            // 1024-key chunks of those tiles queued for chunk_sort_kernel
+    uint32_t pad[2];
 };
 
 #define GSB_CUDA_OK(expr)                                                              \
@@ -163,6 +164,8 @@ struct BinningArgs {
     uint2* ranges;                  // [tiles] written for every tile by the scan
     uint32_t* tile_max;             // [tiles] zeroed by the sort (render forward takes atomicMax into it)
     uint32_t* big_list;             // [tiles] queue of the tiles whose lists one warp cannot sort in registers
+    uint2* chunk_list;              // [R / 512 + 2] (tile, chunk) queue of their 1024-key chunks
+    unsigned long long* pairs2;     // [R] second buffer of the merge rounds
     unsigned long long* pairs;      // [r_cap] depth_bits << 32 | splat, bucketed by tile, sorted in place for long lists
     uint32_t* point_list;           // [r_cap] splat ids sorted by (tile, depth, splat)
     unsigned long long* lookback;   // [scan tiles] chained-scan status words

@@ -109,7 +109,7 @@ int gsb_rasterizer_forward(gsb_alloc_fn geometry_alloc, void* geometry_user, gsb
     ba.P = P; ba.r_cap = 0xFFFFFFFFu; ba.grid_x = grid_x; ba.grid_y = grid_y;
     ba.radii = g.radii; ba.tiles_touched = g.tiles_touched; ba.depths = g.depths; ba.recs = g.recs;
     ba.tile_count = im.tile_count; ba.ranges = im.ranges; ba.tile_max = im.tile_max; ba.big_list = im.big_list;
-    ba.pairs = nullptr; ba.point_list = nullptr;
+    ba.pairs = nullptr; ba.point_list = nullptr; ba.pairs2 = nullptr; ba.chunk_list = nullptr;
     ba.lookback = im.lookback; ba.epoch = &epoch; ba.ctrl = g.ctrl; ba.num_rendered_host = nullptr;
     launch_tile_scan(ba, s);                       // ranges of every tile, R
     if (int e = check(s, dbg)) return e;
@@ -128,7 +128,7 @@ int gsb_rasterizer_forward(gsb_alloc_fn geometry_alloc, void* geometry_user, gsb
     b.carve(bptr, (size_t)R);
     if (R > 0) {
         ba.r_cap = R;
-        ba.pairs = b.pairs; ba.point_list = b.point_list;
+        ba.pairs = b.pairs; ba.point_list = b.point_list; ba.pairs2 = b.pairs2; ba.chunk_list = b.chunk_list;
         launch_emit(ba, s);
         launch_tile_sort(ba, s);
         if (int e = check(s, dbg)) return e;

@@ -58,6 +58,9 @@ struct gsb_trainer {
     int active = 0;
     bool overlap = true;              // gsb_trainer_set_overlap
     cudaStream_t sF = nullptr, sB = nullptr;          // non-blocking: forward chain / backward chain
+    cudaStream_t sF2 = nullptr;                       // forward chains of the odd passes (slot 1): chains of different slots are independent
+    cudaEvent_t ev_scan_prev = nullptr;               // tile scan of the second-to-last pass (it runs on the other forward stream)
+    bool two_fwd_streams = true;
     cudaStream_t exec_f = nullptr, exec_b = nullptr;  // null = everything on `stream`
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_fdone[2] = {nullptr, nullptr}, ev_bdone[2] = {nullptr, nullptr};
     // preview arena (Trainer::render at another resolution)
@@ -191,6 +194,7 @@ int epoch_guard(gsb_trainer* t) {
     if (t->epoch < GSB_EPOCH_LIMIT) return GSB_OK;
     GSB_CUDA_OK(cudaStreamSynchronize(t->stream));
     if (t->sF) GSB_CUDA_OK(cudaStreamSynchronize(t->sF));
+    if (t->sF2) GSB_CUDA_OK(cudaStreamSynchronize(t->sF2));
     if (t->sB) GSB_CUDA_OK(cudaStreamSynchronize(t->sB));
     save_slot(t);
     for (int k = 0; k < 2; k++) {
@@ -210,6 +214,7 @@ int clean_if_dirty(gsb_trainer* t) {
     if (!t->dirty) return GSB_OK;
     GSB_CUDA_OK(cudaStreamSynchronize(t->stream));
     if (t->sF) GSB_CUDA_OK(cudaStreamSynchronize(t->sF));
+    if (t->sF2) GSB_CUDA_OK(cudaStreamSynchronize(t->sF2));
     if (t->sB) GSB_CUDA_OK(cudaStreamSynchronize(t->sB));
     cudaGetLastError();
     save_slot(t);
@@ -261,7 +266,7 @@ int forward_pass(gsb_trainer* t, const float* view, const float* projview, const
     ba.P = P; ba.r_cap = t->r_cap; ba.grid_x = grid_x; ba.grid_y = grid_y;
     ba.radii = t->g.radii; ba.tiles_touched = t->g.tiles_touched; ba.depths = t->g.depths; ba.recs = t->g.recs;
     ba.tile_count = im.tile_count; ba.ranges = im.ranges; ba.tile_max = im.tile_max; ba.big_list = im.big_list;
-    ba.pairs = t->b.pairs; ba.point_list = t->b.point_list;
+    ba.pairs = t->b.pairs; ba.point_list = t->b.point_list; ba.pairs2 = t->b.pairs2; ba.chunk_list = t->b.chunk_list;
     ba.lookback = im.lookback; ba.epoch = &t->epoch; ba.ctrl = t->g.ctrl; ba.num_rendered_host = h_R;
     mark(ev, ST_TILE_SCAN, s);
     { GSB_NVTX("tile scan"); launch_tile_scan(ba, s); }
@@ -277,7 +282,7 @@ int forward_pass(gsb_trainer* t, const float* view, const float* projview, const
     ra.ranges = im.ranges; ra.point_list = t->b.point_list; ra.recs = t->g.recs; ra.bg = bg;
     ra.out_color = out_color; ra.final_T = im.final_T; ra.n_contrib = im.n_contrib; ra.tile_max = im.tile_max;
     { GSB_NVTX("render forward"); launch_render_fwd(ra, s); }
-    t->stats.kernel_launches += 6;
+    t->stats.kernel_launches += 7;
     GSB_CUDA_OK(cudaGetLastError());
     return GSB_OK;
 }
@@ -372,7 +377,10 @@ int gsb_trainer_create(gsb_trainer** out, int width, int height, void* stream) {
     int prio_lo = 0, prio_hi = 0;
     GSB_CUDA_OK(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
     GSB_CUDA_OK(cudaStreamCreateWithPriority(&t->sF, cudaStreamNonBlocking, prio_hi));
+    GSB_CUDA_OK(cudaStreamCreateWithPriority(&t->sF2, cudaStreamNonBlocking, prio_hi));
     GSB_CUDA_OK(cudaStreamCreateWithPriority(&t->sB, cudaStreamNonBlocking, prio_lo));
+    GSB_CUDA_OK(cudaEventCreateWithFlags(&t->ev_scan_prev, cudaEventDisableTiming));
+    if (const char* e = getenv("GSB_FWD_STREAMS")) t->two_fwd_streams = atoi(e) != 1;
     GSB_CUDA_OK(cudaEventCreateWithFlags(&t->ev_fork, cudaEventDisableTiming));
     GSB_CUDA_OK(cudaEventCreateWithFlags(&t->ev_join, cudaEventDisableTiming));
     GSB_CUDA_OK(cudaEventCreateWithFlags(&t->ev_scan, cudaEventDisableTiming));
@@ -396,6 +404,8 @@ int gsb_trainer_destroy(gsb_trainer* t) {
     if (!t) return GSB_OK;
     cudaStreamSynchronize(t->stream);
     if (t->sF) { cudaStreamSynchronize(t->sF); cudaStreamDestroy(t->sF); }
+    if (t->sF2) { cudaStreamSynchronize(t->sF2); cudaStreamDestroy(t->sF2); }
+    if (t->ev_scan_prev) cudaEventDestroy(t->ev_scan_prev);
     if (t->sB) { cudaStreamSynchronize(t->sB); cudaStreamDestroy(t->sB); }
     save_slot(t);
     for (int k = 0; k < 2; k++) {
@@ -568,6 +578,7 @@ int gsb_trainer_accumulate(gsb_trainer* t) {
         if (pipe) {
             GSB_CUDA_OK(cudaEventRecord(t->ev_fork, s));
             GSB_CUDA_OK(cudaStreamWaitEvent(t->sF, t->ev_fork, 0));
+            GSB_CUDA_OK(cudaStreamWaitEvent(t->sF2, t->ev_fork, 0));
             GSB_CUDA_OK(cudaStreamWaitEvent(t->sB, t->ev_fork, 0));
             t->exec_f = t->sF; t->exec_b = t->sB;
         }
@@ -580,10 +591,13 @@ int gsb_trainer_accumulate(gsb_trainer* t) {
         for (int i = 0; i < passes && !err; i++) {
             if (pipe) {
                 activate(t, i & 1);
-                if (i >= 2) err = cudaStreamWaitEvent(t->sF, t->ev_bdone[i & 1], 0) == cudaSuccess ? GSB_OK : gsb_fail_msg("cudaStreamWaitEvent failed");
+                // the two slots' forward chains are independent of each other: on two streams the first two chains of
+                // an iteration (nothing else to overlap with yet) share the machine instead of running back to back
+                t->exec_f = (t->two_fwd_streams && (i & 1)) ? t->sF2 : t->sF;
+                if (i >= 2) err = cudaStreamWaitEvent(t->exec_f, t->ev_bdone[i & 1], 0) == cudaSuccess ? GSB_OK : gsb_fail_msg("cudaStreamWaitEvent failed");
             }
             if (!err) err = view_pass(t, i, fused, avg, S, t->timing_on ? &t->ev_pool[(size_t)i * (ST_COUNT + 1)] : nullptr,
-                                      i == passes - 1 ? t->ev_scan : nullptr);
+                                      i == passes - 1 ? t->ev_scan : (i == passes - 2 ? t->ev_scan_prev : nullptr));
         }
         if (pipe) {
             t->exec_f = t->exec_b = nullptr;
@@ -594,11 +608,14 @@ int gsb_trainer_accumulate(gsb_trainer* t) {
         if (err) { t->dirty = true; return err; }
         GSB_CUDA_OK(cudaGetLastError());
         // The host needs every view's R (arena overflow check) before anything may touch the parameters.  It waits for
-        // the LAST TILE SCAN only (the scans of all earlier passes precede it on the forward stream): the last render
+        // the LAST TILE SCAN of each forward stream only (the scans of all earlier passes precede them): the last render
         // forward / backward chain is still queued behind it, so the GPU stays busy while the host checks, returns and
         // enqueues the all-reduce, apply and the next iteration.  Stage timing needs the whole iteration finished.
         if (t->timing_on) GSB_CUDA_OK(cudaStreamSynchronize(s));
-        else GSB_CUDA_OK(cudaEventSynchronize(t->ev_scan));
+        else {
+            if (pipe && passes >= 2) GSB_CUDA_OK(cudaEventSynchronize(t->ev_scan_prev));
+            GSB_CUDA_OK(cudaEventSynchronize(t->ev_scan));
+        }
         uint32_t maxR = 0;
         long long total = 0;
         if (fused)

@@ -51,11 +51,15 @@ struct GeomWs {
 struct BinWs {
     unsigned long long* pairs;      // [R] depth_bits << 32 | splat, bucketed by tile
     uint32_t* point_list;           // [R] sorted splat ids
+    unsigned long long* pairs2;     // [R] ping-pong partner of `pairs` in the merge rounds of lists longer than 1024
+    uint2* chunk_list;              // [R / 512 + 2] queue of (tile, chunk): sum of ceil(n / 1024) over lists with n > 1024
 
     char* carve(char* base, size_t R) {
         Carver c(base);
         pairs = c.take<unsigned long long>(R);
         point_list = c.take<uint32_t>(R);
+        pairs2 = c.take<unsigned long long>(R);
+        chunk_list = c.take<uint2>(R / 512 + 2);
         return c.p;
     }
     static size_t required(size_t R) {

@@ -37,21 +37,27 @@ RAW_METRICS = [
 
 def launches(path):
     lines = [l for l in open(path) if not l.startswith("==")]
-    agg = collections.OrderedDict()
+    agg = collections.OrderedDict()     # full demangled name -> [launches, time us, dram bytes]
     for row in csv.DictReader(lines):
-        if row.get("Metric Name") != "gpu__time_duration.sum":
+        name, metric = row["Kernel Name"], row.get("Metric Name")
+        if metric not in ("gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum"):
             continue
         v = float(row["Metric Value"].replace(",", ""))
         u = row["Metric Unit"]
-        v = v / 1000 if u == "ns" else (v * 1000 if u == "ms" else v)
-        a = agg.setdefault(row["Kernel Name"][:70], [0, 0.0])
-        a[0] += 1
-        a[1] += v
+        a = agg.setdefault(name, [0, 0.0, 0.0])
+        if metric == "gpu__time_duration.sum":
+            a[0] += 1
+            a[1] += v / 1000 if u == "ns" else (v * 1000 if u in ("ms", "msecond") else v)
+        else:
+            a[2] += v * {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}.get(u, 1)
+    # kernels that share a 70-character prefix (the reference's forward and backward renderCUDA<3>) stay separate:
+    # the label is the prefix plus the parameter count
     tot = sum(a[1] for a in agg.values())
-    print(f"# ncu --metrics gpu__time_duration.sum --clock-control none: {sum(a[0] for a in agg.values())} launches, {tot / 1000:.2f} ms")
-    print("# cold-cache, serialised launches: compare SHARES, not absolutes")
+    print(f"# ncu --metrics gpu__time_duration.sum,dram__bytes_*: {sum(a[0] for a in agg.values())} launches, {tot / 1000:.2f} ms")
+    print("# cold-cache, serialised launches: compare SHARES, not absolutes; dram = read + write bytes per launch (mean)")
     for k, a in sorted(agg.items(), key=lambda x: -x[1][1]):
-        print(f"{k:72s} n={a[0]:4d} total={a[1]:10.1f}us mean={a[1] / a[0]:8.1f}us share={a[1] / tot * 100:5.1f}%")
+        label = f"{k[:64]} [{k.count(',') + 1} args]"
+        print(f"{label:76s} n={a[0]:4d} total={a[1]:10.1f}us mean={a[1] / a[0]:8.1f}us share={a[1] / tot * 100:5.1f}% dram={a[2] / a[0] / 1e6:8.2f}MB")
 
 
 def _ncu(rep, page, extra=()):
