@@ -61,12 +61,14 @@ __device__ __forceinline__ uint32_t lookback_exclusive(unsigned long long* lb, u
 // emit_kernel; the total R goes to ctrl->num_rendered and, optionally, to pinned host memory.  If R exceeds the
 // capacity of the duplicate arrays the ranges are clipped to it, so every later kernel stays in bounds, and
 // ctrl->overflow is raised (the caller grows the arena and repeats the pass).
+constexpr uint32_t SORT_WARP_MAX = 1024;   // longest list (or chunk) one warp sorts in registers (32 keys per lane)
 constexpr int SC_IPT = 8;
 constexpr int SC_TILE = 256 * SC_IPT;
 
 __global__ void __launch_bounds__(256) tile_scan_kernel(uint32_t* __restrict__ tile_count, uint32_t tiles, uint2* __restrict__ ranges,
                                                         unsigned long long* lookback, uint32_t epoch, GsbCtrl* ctrl,
-                                                        uint32_t r_cap, uint32_t* num_rendered_host) {
+                                                        uint32_t r_cap, uint32_t* num_rendered_host,
+                                                        uint32_t* __restrict__ big_list, uint2* __restrict__ chunk_list) {
     __shared__ uint32_t s_warp[8];
     __shared__ uint32_t s_tile, s_excl;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -102,8 +104,17 @@ __global__ void __launch_bounds__(256) tile_scan_kernel(uint32_t* __restrict__ t
     for (int k = 0; k < SC_IPT; k++) {
         const uint32_t i = base + k;
         if (i < tiles) {
-            ranges[i] = v[k] ? make_uint2(min(run, r_cap), min(run + v[k], r_cap)) : make_uint2(0u, 0u);
+            const uint32_t lo = min(run, r_cap), hi = min(run + v[k], r_cap);
+            ranges[i] = v[k] ? make_uint2(lo, hi) : make_uint2(0u, 0u);
             tile_count[i] = run;
+            if (chunk_list && hi - lo > SORT_WARP_MAX) {
+                // a list too long for one warp's registers: queue the tile for the merge kernel and its 1024-key
+                // chunks for the chunk-sort kernel (sum of chunks <= R / 1024 + number of such tiles <= R / 512)
+                const uint32_t chunks = (hi - lo + SORT_WARP_MAX - 1) / SORT_WARP_MAX;
+                big_list[atomicAdd(&ctrl->num_big, 1u)] = i;
+                const uint32_t at = atomicAdd(&ctrl->num_chunks, chunks);
+                for (uint32_t c = 0; c < chunks; c++) chunk_list[at + c] = make_uint2(i, c);
+            }
         }
         run += v[k];
     }
@@ -111,6 +122,21 @@ __global__ void __launch_bounds__(256) tile_scan_kernel(uint32_t* __restrict__ t
         ctrl->num_rendered = run;
         if (run > r_cap) ctrl->overflow = 1u;
         if (num_rendered_host) *num_rendered_host = run;
+    }
+}
+
+// The same queueing as a kernel of its own, for callers whose duplicate arena (and with it the chunk queue) is only
+// allocated once R is known (gsb_rasterizer_forward: the scan runs before the binning allocation).
+__global__ void __launch_bounds__(256) queue_long_lists_kernel(const uint2* __restrict__ ranges, uint32_t tiles, uint32_t* __restrict__ big_list,
+                                                               uint2* __restrict__ chunk_list, GsbCtrl* ctrl) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= tiles) return;
+    const uint2 r = ranges[i];
+    if (r.y - r.x > SORT_WARP_MAX) {
+        const uint32_t chunks = (r.y - r.x + SORT_WARP_MAX - 1) / SORT_WARP_MAX;
+        big_list[atomicAdd(&ctrl->num_big, 1u)] = i;
+        const uint32_t at = atomicAdd(&ctrl->num_chunks, chunks);
+        for (uint32_t c = 0; c < chunks; c++) chunk_list[at + c] = make_uint2(i, c);
     }
 }
 
@@ -163,7 +189,7 @@ __global__ void __launch_bounds__(256) emit_kernel(const uint32_t* __restrict__ 
 // Longer lists (every tile at C5) are cut into 1024-key chunks, each sorted the same way by its own warp (in place, as
 // keys), and then merged: one CTA per list, log2(chunks) rounds of pairwise merge-path merges between `pairs` and a
 // second buffer, the last round writing the splat ids.
-constexpr int TS_WARP_MAX = 1024;     // longest list (or chunk) one warp sorts in registers (32 keys per lane)
+constexpr int TS_WARP_MAX = (int)SORT_WARP_MAX;
 constexpr int MG_THREADS = 256;       // merge CTA
 constexpr int MG_ITEMS = 8;           // outputs per thread per block of MG_THREADS * MG_ITEMS = 2048 merged keys
 
@@ -226,36 +252,22 @@ __device__ __forceinline__ void warp_sort_dispatch(const unsigned long long* key
 
 // One 32-thread CTA (one warp) per tile: the list length is uniform over the CTA, so the compiler knows every shuffle
 // of the register network is convergent (inside a per-warp branch of a larger CTA each one is wrapped in
-// WARPSYNC / ENDCOLLECTIVE).  A list too long for one warp is queued: the tile for the merge kernel, its chunks for
-// the chunk-sort kernel.
-__global__ void __launch_bounds__(32) tile_sort_kernel(const uint2* __restrict__ ranges, const unsigned long long* __restrict__ pairs,
-                                                       uint32_t* __restrict__ point_list, uint32_t* __restrict__ tile_count,
-                                                       uint32_t* __restrict__ tile_max, uint32_t* __restrict__ big_list,
-                                                       uint2* __restrict__ chunk_list, GsbCtrl* ctrl) {
-    const uint32_t tile = blockIdx.x;
-    // housekeeping for the kernels around this one: the count / cursor of this tile starts the next view pass at zero,
-    // and the render forward takes the maximum of n_contrib over the tile with atomicMax
-    if (threadIdx.x == 0) { tile_count[tile] = 0u; tile_max[tile] = 0u; }
-    const uint2 range = ranges[tile];
-    const int n = (int)(range.y - range.x);
-    if (n <= 0) return;
-    if (n > TS_WARP_MAX) {
-        const uint32_t chunks = ((uint32_t)n + TS_WARP_MAX - 1) / TS_WARP_MAX;
-        uint32_t base = 0;
-        if (threadIdx.x == 0) {
-            big_list[atomicAdd(&ctrl->num_big, 1u)] = tile;
-            base = atomicAdd(&ctrl->num_chunks, chunks);
-        }
-        base = __shfl_sync(0xffffffffu, base, 0);
-        for (uint32_t c = threadIdx.x; c < chunks; c += 32) chunk_list[base + c] = make_uint2(tile, c);
-        return;
+// WARPSYNC / ENDCOLLECTIVE).  Lists too long for one warp were queued by the tile scan as 1024-key chunks; after its
+// own tile every CTA takes its share of that queue (grid-stride from blockIdx: uniform control flow again) and sorts
+// the chunks in place, as keys, for the merge kernel.
+__global__ void __launch_bounds__(32, 24) tile_sort_kernel(const uint2* __restrict__ ranges, unsigned long long* __restrict__ pairs,
+                                                           uint32_t* __restrict__ point_list, uint32_t* __restrict__ tile_count,
+                                                           uint32_t* __restrict__ tile_max, uint32_t tiles,
+                                                           const uint2* __restrict__ chunk_list, const GsbCtrl* ctrl) {
+    if (blockIdx.x < tiles) {
+        const uint32_t tile = blockIdx.x;
+        // housekeeping for the kernels around this one: the count / cursor of this tile starts the next view pass at
+        // zero, and the render forward takes the maximum of n_contrib over the tile with atomicMax
+        if (threadIdx.x == 0) { tile_count[tile] = 0u; tile_max[tile] = 0u; }
+        const uint2 range = ranges[tile];
+        const int n = (int)(range.y - range.x);
+        if (n > 0 && n <= TS_WARP_MAX) warp_sort_dispatch<true>(pairs + range.x, n, point_list + range.x);
     }
-    warp_sort_dispatch<true>(pairs + range.x, n, point_list + range.x);
-}
-
-// Persistent one-warp CTAs over the chunk queue (uniform control flow again: the queue index comes from blockIdx).
-__global__ void __launch_bounds__(32, 24) chunk_sort_kernel(const uint2* __restrict__ ranges, unsigned long long* __restrict__ pairs,
-                                                        const uint2* __restrict__ chunk_list, const GsbCtrl* ctrl) {
     const uint32_t count = ctrl->num_chunks;
     for (uint32_t q = blockIdx.x; q < count; q += gridDim.x) {
         const uint2 e = chunk_list[q];
@@ -337,7 +349,12 @@ __global__ void __launch_bounds__(256) sorted_keys_kernel(const uint2* __restric
 void launch_tile_scan(const BinningArgs& a, cudaStream_t s) {
     const uint32_t tiles = (uint32_t)(a.grid_x * a.grid_y);
     tile_scan_kernel<<<gsb_div_up(tiles, SC_TILE), 256, 0, s>>>(a.tile_count, tiles, a.ranges, a.lookback, ++(*a.epoch), a.ctrl, a.r_cap,
-                                                                a.num_rendered_host);
+                                                                a.num_rendered_host, a.big_list, a.chunk_list);
+}
+
+void launch_queue_long_lists(const BinningArgs& a, cudaStream_t s) {
+    const uint32_t tiles = (uint32_t)(a.grid_x * a.grid_y);
+    queue_long_lists_kernel<<<gsb_div_up(tiles, 256), 256, 0, s>>>(a.ranges, tiles, a.big_list, a.chunk_list, a.ctrl);
 }
 
 void launch_emit(const BinningArgs& a, cudaStream_t s) {
@@ -349,9 +366,8 @@ void launch_emit(const BinningArgs& a, cudaStream_t s) {
 
 void launch_tile_sort(const BinningArgs& a, cudaStream_t s) {
     const uint32_t tiles = (uint32_t)(a.grid_x * a.grid_y);
-    tile_sort_kernel<<<tiles, 32, 0, s>>>(a.ranges, a.pairs, a.point_list, a.tile_count, a.tile_max, a.big_list, a.chunk_list, a.ctrl);
-    // the two kernels of the long lists run over device-side queues (empty at C4 but for a few tiles): fixed grids
-    chunk_sort_kernel<<<148 * 16, 32, 0, s>>>(a.ranges, a.pairs, a.chunk_list, a.ctrl);
+    tile_sort_kernel<<<max(tiles, 148u * 24u), 32, 0, s>>>(a.ranges, a.pairs, a.point_list, a.tile_count, a.tile_max, tiles, a.chunk_list, a.ctrl);
+    // the merge kernel runs over the device-side queue of long lists with a grid-stride loop (nearly empty at C4)
     tile_merge_kernel<<<min(tiles, 148u * 4u), MG_THREADS, 0, s>>>(a.ranges, a.pairs, a.pairs2, a.point_list, a.big_list, a.ctrl);
 }
 

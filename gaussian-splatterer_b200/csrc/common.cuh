@@ -176,6 +176,7 @@ struct BinningArgs {
 // The stages, in order (preprocess has filled tile_count).
 void launch_tile_scan(const BinningArgs& a, cudaStream_t s);
 void launch_emit(const BinningArgs& a, cudaStream_t s);
+void launch_queue_long_lists(const BinningArgs& a, cudaStream_t s);   // only when the tile scan ran without a chunk queue
 void launch_tile_sort(const BinningArgs& a, cudaStream_t s);
 void launch_sorted_keys(const uint2* ranges, const uint32_t* point_list, const float* depths, uint32_t tiles, uint64_t* out,
                         cudaStream_t s);

@@ -129,6 +129,7 @@ int gsb_rasterizer_forward(gsb_alloc_fn geometry_alloc, void* geometry_user, gsb
     if (R > 0) {
         ba.r_cap = R;
         ba.pairs = b.pairs; ba.point_list = b.point_list; ba.pairs2 = b.pairs2; ba.chunk_list = b.chunk_list;
+        launch_queue_long_lists(ba, s);      // the scan ran before this arena existed
         launch_emit(ba, s);
         launch_tile_sort(ba, s);
         if (int e = check(s, dbg)) return e;

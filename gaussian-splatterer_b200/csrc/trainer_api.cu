@@ -282,7 +282,7 @@ int forward_pass(gsb_trainer* t, const float* view, const float* projview, const
     ra.ranges = im.ranges; ra.point_list = t->b.point_list; ra.recs = t->g.recs; ra.bg = bg;
     ra.out_color = out_color; ra.final_T = im.final_T; ra.n_contrib = im.n_contrib; ra.tile_max = im.tile_max;
     { GSB_NVTX("render forward"); launch_render_fwd(ra, s); }
-    t->stats.kernel_launches += 7;
+    t->stats.kernel_launches += 6;
     GSB_CUDA_OK(cudaGetLastError());
     return GSB_OK;
 }
