@@ -30,7 +30,7 @@ if has refncu; then
 fi
 if has full; then
   # full capture of the two render kernels in the BENCH configuration (all 64 cameras): roofline.traffic comes from this report
-  CMD="ncu --set full --clock-control none --import-source on -k regex:render_(bwd|fwd)_kernel --launch-skip 40 -c 2 -f -o $OUT/${TAG}_prof_render python bench.py --steps 1 --warmup 1 --no-cpu-baseline --no-e2e"
+  CMD="ncu --set full --clock-control none --import-source on -k regex:render_(bwd|fwd)_kernel --launch-skip 40 -c 8 -f -o $OUT/${TAG}_prof_render python bench.py --steps 1 --warmup 1 --no-cpu-baseline --no-e2e"
   echo "$CMD" > $OUT/${TAG}_prof_render.cmd
   timeout 900 $CMD > $OUT/${TAG}_ncu_full.log 2>&1; echo "ncu full exit $?"
 fi
