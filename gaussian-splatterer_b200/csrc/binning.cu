@@ -193,8 +193,17 @@ constexpr int TS_WARP_MAX = (int)SORT_WARP_MAX;
 constexpr int MG_THREADS = 256;       // merge CTA
 constexpr int MG_ITEMS = 8;           // outputs per thread per block of MG_THREADS * MG_ITEMS = 2048 merged keys
 
-template <int E, bool IDS>
-__device__ __forceinline__ void warp_sort_tile(const unsigned long long* __restrict__ keys, int n, void* __restrict__ out) {
+// The network is written so that its code stays small: the levels that live inside one lane (k <= E) are unrolled (their
+// compare directions depend on the register index), every later level k = 2E .. 32E runs through ONE rolled body -- a
+// runtime loop over the cross-lane distances (shfl_xor takes the lane mask from a register) followed by the unrolled
+// in-lane merge-down, whose direction is the lane's for all of them.  A fully unrolled network is 6.7 k instructions for
+// E = 32 alone and 26.7 k for the six list classes together (427 KB of SASS): with every warp of an SM at a different
+// place in a different class, ncu showed 75 % of the stall samples on "no instruction" (instruction-cache misses) and
+// 0.04 instructions per clock and warp.
+// One copy of each list class in the kernel (__noinline__, the store form is a runtime flag): the tile path and the
+// chunk path share the E = 32 body.
+template <int E>
+__device__ __noinline__ void warp_sort_tile(const unsigned long long* __restrict__ keys, int n, void* __restrict__ out, bool ids) {
     const int lane = threadIdx.x & 31;
     unsigned long long v[E];
 #pragma unroll
@@ -202,29 +211,42 @@ __device__ __forceinline__ void warp_sort_tile(const unsigned long long* __restr
         const int i = r * 32 + lane;
         v[r] = (i < n) ? keys[i] : ~0ull;
     }
-    // element index of register r of lane l: i = l * E + r
+    // element index of register r of lane l: i = l * E + r.  Blocks of k elements alternate ascending / descending; the
+    // last level (k = 32 E) is ascending everywhere.
 #pragma unroll
-    for (int k = 2; k <= 32 * E; k <<= 1) {
-        // blocks of k elements alternate ascending / descending; the last level (k = 32 E) is ascending everywhere
-        const bool asc_lane = ((lane * E) & k) == 0;
+    for (int k = 2; k <= E; k <<= 1) {
+        const bool asc_lane = ((lane * E) & k) == 0;      // only k == E depends on the lane
 #pragma unroll
         for (int j = k >> 1; j > 0; j >>= 1) {
-            if (j >= E) {
-                const int lj = j / E;
-                const bool keep_min = (((lane & lj) == 0) == asc_lane);
 #pragma unroll
-                for (int r = 0; r < E; r++) {
-                    const unsigned long long o = __shfl_xor_sync(0xffffffffu, v[r], lj);
-                    if ((o < v[r]) == keep_min) v[r] = o;     // keep_min: min(v, o); else max(v, o) (keys are distinct or both ~0)
+            for (int r = 0; r < E; r++) {
+                if ((r & j) == 0) {
+                    const bool asc = (k >= E) ? asc_lane : ((r & k) == 0);
+                    const unsigned long long a = v[r], b = v[r + j];
+                    if ((b < a) == asc) { v[r] = b; v[r + j] = a; }
                 }
-            } else {
+            }
+        }
+    }
+#pragma unroll 1
+    for (int k = 2 * E; k <= 32 * E; k <<= 1) {
+        const bool asc_lane = ((lane * E) & k) == 0;
+#pragma unroll 1
+        for (int lj = k / (2 * E); lj > 0; lj >>= 1) {
+            const bool keep_min = (((lane & lj) == 0) == asc_lane);
 #pragma unroll
-                for (int r = 0; r < E; r++) {
-                    if ((r & j) == 0) {
-                        const bool asc = (k >= E) ? asc_lane : ((r & k) == 0);
-                        const unsigned long long a = v[r], b = v[r + j];
-                        if ((b < a) == asc) { v[r] = b; v[r + j] = a; }
-                    }
+            for (int r = 0; r < E; r++) {
+                const unsigned long long o = __shfl_xor_sync(0xffffffffu, v[r], lj);
+                if ((o < v[r]) == keep_min) v[r] = o;     // keep_min: min(v, o); else max(v, o) (keys are distinct or both ~0)
+            }
+        }
+#pragma unroll
+        for (int j = E >> 1; j > 0; j >>= 1) {
+#pragma unroll
+            for (int r = 0; r < E; r++) {
+                if ((r & j) == 0) {
+                    const unsigned long long a = v[r], b = v[r + j];
+                    if ((b < a) == asc_lane) { v[r] = b; v[r + j] = a; }
                 }
             }
         }
@@ -234,20 +256,19 @@ __device__ __forceinline__ void warp_sort_tile(const unsigned long long* __restr
     for (int r = 0; r < E; r++) {
         const int i = lane * E + r;
         if (i < n) {
-            if (IDS) static_cast<uint32_t*>(out)[i] = (uint32_t)v[r];
+            if (ids) static_cast<uint32_t*>(out)[i] = (uint32_t)v[r];
             else static_cast<unsigned long long*>(out)[i] = v[r];
         }
     }
 }
 
-template <bool IDS>
-__device__ __forceinline__ void warp_sort_dispatch(const unsigned long long* keys, int n, void* out) {
-    if (n <= 32) warp_sort_tile<1, IDS>(keys, n, out);
-    else if (n <= 64) warp_sort_tile<2, IDS>(keys, n, out);
-    else if (n <= 128) warp_sort_tile<4, IDS>(keys, n, out);
-    else if (n <= 256) warp_sort_tile<8, IDS>(keys, n, out);
-    else if (n <= 512) warp_sort_tile<16, IDS>(keys, n, out);
-    else warp_sort_tile<32, IDS>(keys, n, out);
+__device__ __forceinline__ void warp_sort_dispatch(const unsigned long long* keys, int n, void* out, bool ids) {
+    if (n <= 32) warp_sort_tile<1>(keys, n, out, ids);
+    else if (n <= 64) warp_sort_tile<2>(keys, n, out, ids);
+    else if (n <= 128) warp_sort_tile<4>(keys, n, out, ids);
+    else if (n <= 256) warp_sort_tile<8>(keys, n, out, ids);
+    else if (n <= 512) warp_sort_tile<16>(keys, n, out, ids);
+    else warp_sort_tile<32>(keys, n, out, ids);
 }
 
 // One 32-thread CTA (one warp) per tile: the list length is uniform over the CTA, so the compiler knows every shuffle
@@ -266,7 +287,7 @@ __global__ void __launch_bounds__(32, 24) tile_sort_kernel(const uint2* __restri
         if (threadIdx.x == 0) { tile_count[tile] = 0u; tile_max[tile] = 0u; }
         const uint2 range = ranges[tile];
         const int n = (int)(range.y - range.x);
-        if (n > 0 && n <= TS_WARP_MAX) warp_sort_dispatch<true>(pairs + range.x, n, point_list + range.x);
+        if (n > 0 && n <= TS_WARP_MAX) warp_sort_dispatch(pairs + range.x, n, point_list + range.x, true);
     }
     const uint32_t count = ctrl->num_chunks;
     for (uint32_t q = blockIdx.x; q < count; q += gridDim.x) {
@@ -275,7 +296,7 @@ __global__ void __launch_bounds__(32, 24) tile_sort_kernel(const uint2* __restri
         const uint32_t off = e.y * TS_WARP_MAX;
         const int m = (int)min((uint32_t)TS_WARP_MAX, range.y - range.x - off);
         unsigned long long* keys = pairs + range.x + off;
-        warp_sort_dispatch<false>(keys, m, keys);
+        warp_sort_tile<32>(keys, m, keys, false);     // (one class only: all chunks but a list's last are full, and code size matters here)
     }
 }
 

@@ -192,6 +192,7 @@ struct RenderFwdArgs {
     float* final_T;                 // [H*W]
     uint32_t* n_contrib;            // [H*W]
     uint32_t* tile_max;             // [tiles] max n_contrib in tile
+    uint32_t* frame;                // preview mode (Trainer::render): RGBA8 [H*W] written instead of everything above
 };
 void launch_render_fwd(const RenderFwdArgs& a, cudaStream_t s);
 

@@ -108,6 +108,23 @@ __device__ F3 sh_to_rgb(int deg, int M, float px, float py, float pz, const floa
     return {fmaxf(res.x, 0.f), fmaxf(res.y, 0.f), fmaxf(res.z, 0.f)};
 }
 
+// The same for the trainer's record shape (M = 4: degree <= 1, twelve floats = three 16-byte words per splat, loaded as
+// such): identical expression tree, operands from registers.
+__device__ __forceinline__ F3 sh_to_rgb_m4(int deg, float px, float py, float pz, const float* cam, const float4 s0, const float4 s1,
+                                           const float4 s2, uint8_t& flags) {
+    float dx = px - cam[0], dy = py - cam[1], dz = pz - cam[2];
+    float len = sqrtf(fma_(dz, dz, fma_(dx, dx, mul_(dy, dy))));
+    float x = dx / len, y = dy / len, z = dz / len;
+    F3 res = kSH_C0 * F3{s0.x, s0.y, s0.z};
+    if (deg > 0) res = res - (kSH_C1 * y) * F3{s0.w, s1.x, s1.y} + (kSH_C1 * z) * F3{s1.z, s1.w, s2.x} - (kSH_C1 * x) * F3{s2.y, s2.z, s2.w};
+    res.x += 0.5f; res.y += 0.5f; res.z += 0.5f;
+    flags = (uint8_t)((res.x < 0.f ? 1 : 0) | (res.y < 0.f ? 2 : 0) | (res.z < 0.f ? 4 : 0));
+    return {fmaxf(res.x, 0.f), fmaxf(res.y, 0.f), fmaxf(res.z, 0.f)};
+}
+
+// VEC: rotations, the 12-float SH record and the covariance are moved as 16- / 8-byte words (the arrays are contiguous
+// per splat and the caller's bases are suitably aligned: checked by the launcher); means and scales (stride 3) stay scalar.
+template <bool VEC>
 __global__ void __launch_bounds__(256) preprocess_fwd_kernel(const PreprocessArgs a) {
     // every lane stays to the end (the tile counts are added warp-cooperatively); lanes beyond P shadow splat P-1 and
     // write nothing
@@ -146,11 +163,19 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(const PreprocessArg
 #pragma unroll
             for (int k = 0; k < 6; k++) cov[k] = a.cov3D_precomp[6 * idx + k];
         } else {
-            cov3d_from_scale_rot(a.scales[3 * idx], a.scales[3 * idx + 1], a.scales[3 * idx + 2], a.scale_modifier,
-                                 a.rotations[4 * idx], a.rotations[4 * idx + 1], a.rotations[4 * idx + 2],
-                                 a.rotations[4 * idx + 3], cov);
+            if constexpr (VEC) {
+                const float4 q = __ldg(reinterpret_cast<const float4*>(a.rotations) + idx);
+                cov3d_from_scale_rot(a.scales[3 * idx], a.scales[3 * idx + 1], a.scales[3 * idx + 2], a.scale_modifier,
+                                     q.x, q.y, q.z, q.w, cov);
+                float2* c2 = reinterpret_cast<float2*>(a.cov3D + 6 * (size_t)idx);
+                c2[0] = make_float2(cov[0], cov[1]); c2[1] = make_float2(cov[2], cov[3]); c2[2] = make_float2(cov[4], cov[5]);
+            } else {
+                cov3d_from_scale_rot(a.scales[3 * idx], a.scales[3 * idx + 1], a.scales[3 * idx + 2], a.scale_modifier,
+                                     a.rotations[4 * idx], a.rotations[4 * idx + 1], a.rotations[4 * idx + 2],
+                                     a.rotations[4 * idx + 3], cov);
 #pragma unroll
-            for (int k = 0; k < 6; k++) a.cov3D[6 * idx + k] = cov[k];
+                for (int k = 0; k < 6; k++) a.cov3D[6 * idx + k] = cov[k];
+            }
         }
 
         // EWA projection (computeCov2D).  t = view * p; x/z and y/z clamped to 1.3 tan(fov/2).
@@ -236,7 +261,12 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(const PreprocessArg
     F3 rgb;
     uint8_t flags = 0;
     if (a.colors_precomp == nullptr) {
-        rgb = sh_to_rgb(a.D, a.M, px, py, pz, a.cam_pos, a.shs + (size_t)idx * a.M * 3, flags);
+        if constexpr (VEC) {
+            const float4* sp = reinterpret_cast<const float4*>(a.shs) + 3 * (size_t)idx;
+            rgb = sh_to_rgb_m4(a.D, px, py, pz, a.cam_pos, __ldg(sp), __ldg(sp + 1), __ldg(sp + 2), flags);
+        } else {
+            rgb = sh_to_rgb(a.D, a.M, px, py, pz, a.cam_pos, a.shs + (size_t)idx * a.M * 3, flags);
+        }
     } else {
         rgb = ld3(a.colors_precomp + 3 * (size_t)idx);
     }
@@ -276,7 +306,11 @@ __global__ void mark_visible_kernel(int P, const float* means3D, const float* V,
 
 void launch_preprocess_fwd(const PreprocessArgs& a, cudaStream_t s) {
     if (a.P <= 0) return;
-    preprocess_fwd_kernel<<<gsb_div_up(a.P, 256), 256, 0, s>>>(a);
+    auto al = [](const void* p, uintptr_t n) { return reinterpret_cast<uintptr_t>(p) % n == 0; };
+    const bool vec = a.cov3D_precomp == nullptr && a.colors_precomp == nullptr && a.M == 4 && a.D <= 1 && al(a.rotations, 16) &&
+                     al(a.shs, 16) && al(a.cov3D, 8);
+    if (vec) preprocess_fwd_kernel<true><<<gsb_div_up(a.P, 256), 256, 0, s>>>(a);
+    else preprocess_fwd_kernel<false><<<gsb_div_up(a.P, 256), 256, 0, s>>>(a);
 }
 
 void launch_mark_visible(int P, const float* means3D, const float* viewmatrix, bool* present, cudaStream_t s) {

@@ -36,7 +36,7 @@ struct ShDirs { V3 d0, dx, dy, dz; };
 // Writes dL/dsh (M x 3) through `emit(coeff, value)` for the colour gradient dRGB and returns what the
 // view-direction term of dL/dmean needs (dir_grad below); everything here is linear in dRGB.
 template <typename Emit>
-__device__ ShDirs sh_backward(int deg, float px, float py, float pz, const float* cam, const float* sh, V3 dRGB, Emit emit) {
+__device__ __forceinline__ ShDirs sh_backward(int deg, float px, float py, float pz, const float* cam, const float* sh, V3 dRGB, Emit emit) {
     const V3 d0 = {px - cam[0], py - cam[1], pz - cam[2]};
     const float len = sqrtf(d0.x * d0.x + d0.y * d0.y + d0.z * d0.z);
     const float x = d0.x / len, y = d0.y / len, z = d0.z / len;
@@ -220,8 +220,14 @@ __global__ void __launch_bounds__(GSB_PB_THREADS, GSB_PB_BLOCKS) preprocess_bwd_
 
     // ---- per-splat geometry of the covariance path (computeCov2DCUDA) ----
     float c3[6];
+    if constexpr (M4) {   // the trainer shape moves covariance, SH record and quaternion as 8- / 16-byte words (launcher checks alignment)
+        const float2* c2 = reinterpret_cast<const float2*>(a.cov3D + 6 * (size_t)idx);
+        const float2 u0 = c2[0], u1 = c2[1], u2 = c2[2];
+        c3[0] = u0.x; c3[1] = u0.y; c3[2] = u1.x; c3[3] = u1.y; c3[4] = u2.x; c3[5] = u2.y;
+    } else {
 #pragma unroll
-    for (int k = 0; k < 6; k++) c3[k] = a.cov3D[6 * idx + k];
+        for (int k = 0; k < 6; k++) c3[k] = a.cov3D[6 * idx + k];
+    }
     float tx = v0 * mx + v4 * my + v8 * mz + __ldg(V + 12);
     float ty = v1 * mx + v5 * my + v9 * mz + __ldg(V + 13);
     const float tz = v2 * mx + v6 * my + v10 * mz + __ldg(V + 14);
@@ -317,7 +323,14 @@ __global__ void __launch_bounds__(GSB_PB_THREADS, GSB_PB_BLOCKS) preprocess_bwd_
                 out[3 * c] = v.x; out[3 * c + 1] = v.y; out[3 * c + 2] = v.z;
             });
         } else if (M4) {
-            dirs = sh_backward(1, mx, my, mz, a.cam_pos, sh, dsum, [&](int c, V3 v) {
+            float shl[12];
+            {
+                const float4* sp = reinterpret_cast<const float4*>(sh);
+                const float4 s0 = __ldg(sp), s1 = __ldg(sp + 1), s2 = __ldg(sp + 2);
+                shl[0] = s0.x; shl[1] = s0.y; shl[2] = s0.z; shl[3] = s0.w; shl[4] = s1.x; shl[5] = s1.y; shl[6] = s1.z; shl[7] = s1.w;
+                shl[8] = s2.x; shl[9] = s2.y; shl[10] = s2.z; shl[11] = s2.w;
+            }
+            dirs = sh_backward(1, mx, my, mz, a.cam_pos, shl, dsum, [&](int c, V3 v) {
                 o_sh[3 * c] += v.x / S; o_sh[3 * c + 1] += v.y / S; o_sh[3 * c + 2] += v.z / S;
             });
             float4* p = reinterpret_cast<float4*>(avg_sh + 12 * (size_t)idx);
@@ -361,7 +374,13 @@ __global__ void __launch_bounds__(GSB_PB_THREADS, GSB_PB_BLOCKS) preprocess_bwd_
 
     // ---- cov3D -> scale, rotation ----
     if (!a.cov3D_is_precomp) {
-        const float r = a.rotations[4 * idx], x = a.rotations[4 * idx + 1], y = a.rotations[4 * idx + 2], z = a.rotations[4 * idx + 3];
+        float r, x, y, z;
+        if constexpr (M4) {
+            const float4 q = __ldg(reinterpret_cast<const float4*>(a.rotations) + idx);
+            r = q.x; x = q.y; y = q.z; z = q.w;
+        } else {
+            r = a.rotations[4 * idx]; x = a.rotations[4 * idx + 1]; y = a.rotations[4 * idx + 2]; z = a.rotations[4 * idx + 3];
+        }
         const float s[3] = {a.scale_modifier * a.scales[3 * idx], a.scale_modifier * a.scales[3 * idx + 1],
                             a.scale_modifier * a.scales[3 * idx + 2]};
         // Rg[c][r]: columns of the reference's R literal
@@ -416,7 +435,9 @@ void launch_preprocess_bwd(const PreprocessBwdArgs& a, cudaStream_t s) {
     const bool trainer = a.avg != nullptr;
     // the fast shape needs 16-byte aligned 12-float SH records in the running-mean buffer
     const bool m4 = trainer && a.M == 4 && a.D == 1 && !a.colors_precomp &&
-                    (reinterpret_cast<uintptr_t>(a.avg) % 16 == 0);
+                    (reinterpret_cast<uintptr_t>(a.avg) % 16 == 0) && (reinterpret_cast<uintptr_t>(a.shs) % 16 == 0) &&
+                    (reinterpret_cast<uintptr_t>(a.rotations) % 16 == 0) && (reinterpret_cast<uintptr_t>(a.cov3D) % 8 == 0) &&
+                    !a.cov3D_is_precomp;
     if (trainer && a.grads2 != nullptr) {
         if (m4) preprocess_bwd_kernel<2, true><<<grid, GSB_PB_THREADS, 0, s>>>(a);
         else preprocess_bwd_kernel<2, false><<<grid, GSB_PB_THREADS, 0, s>>>(a);

@@ -139,6 +139,7 @@ int gsb_rasterizer_forward(gsb_alloc_fn geometry_alloc, void* geometry_user, gsb
     ra.W = width; ra.H = height; ra.grid_x = grid_x; ra.grid_y = grid_y;
     ra.ranges = im.ranges; ra.point_list = b.point_list; ra.recs = g.recs; ra.bg = background;
     ra.out_color = out_color; ra.final_T = im.final_T; ra.n_contrib = im.n_contrib; ra.tile_max = im.tile_max;
+    ra.frame = nullptr;
     launch_render_fwd(ra, s);
     if (int e = check(s, dbg)) return e;
     if (num_rendered) *num_rendered = (int)R;

@@ -33,6 +33,9 @@ constexpr int WB = 32;   // list entries per warp-private chunk (one per lane)
 #define GSB_FWD_CONV 1
 #endif
 
+// PREVIEW: Trainer::render's shape -- the pixel goes out as RGBA8 (imageFloatToInt, src/Trainer.cu:21-31, applied to the
+// same float colour) and nothing a backward pass would need (final_T, n_contrib, the float planes, tile_max) is written.
+template <bool PREVIEW>
 __global__ void __launch_bounds__(RENDER_THREADS) render_fwd_kernel(const RenderFwdArgs a) {
     __shared__ SplatRec s_rec[RENDER_WARPS][2][WB];
 
@@ -168,6 +171,14 @@ __global__ void __launch_bounds__(RENDER_THREADS) render_fwd_kernel(const Render
     for (int k = 0; k < 2; k++) {
         if (pix_x < a.W && pix_y[k] < a.H) {
             const size_t pid = (size_t)pix_y[k] * a.W + pix_x;
+            if constexpr (PREVIEW) {
+                // int(c * 256) clamped to [0, 255], alpha = 0xFF
+                const int r = min(255, max(0, (int)(__fmaf_rn(bg0, T[k], Cr[k]) * 256.0f)));
+                const int g = min(255, max(0, (int)(__fmaf_rn(bg1, T[k], Cg[k]) * 256.0f)));
+                const int b = min(255, max(0, (int)(__fmaf_rn(bg2, T[k], Cb[k]) * 256.0f)));
+                a.frame[pid] = (uint32_t)r | ((uint32_t)g << 8) | ((uint32_t)b << 16) | 0xFF000000u;
+                continue;
+            }
             a.final_T[pid] = T[k];
             a.n_contrib[pid] = last[k];
             a.out_color[pid] = __fmaf_rn(bg0, T[k], Cr[k]);
@@ -178,6 +189,7 @@ __global__ void __launch_bounds__(RENDER_THREADS) render_fwd_kernel(const Render
     }
     // largest n_contrib of the tile: one atomicMax per warp into tile_max (zeroed by tile_sort_kernel / the caller), so
     // a finished warp retires without waiting at a block barrier for the slowest warp of its tile
+    if constexpr (PREVIEW) return;
     mx = __reduce_max_sync(0xffffffffu, mx);
     if (lane == 0 && mx) atomicMax(&a.tile_max[tile], mx);
 }
@@ -185,5 +197,6 @@ __global__ void __launch_bounds__(RENDER_THREADS) render_fwd_kernel(const Render
 }  // namespace
 
 void launch_render_fwd(const RenderFwdArgs& a, cudaStream_t s) {
-    render_fwd_kernel<<<dim3(a.grid_x, a.grid_y), RENDER_THREADS, 0, s>>>(a);
+    if (a.frame != nullptr) render_fwd_kernel<true><<<dim3(a.grid_x, a.grid_y), RENDER_THREADS, 0, s>>>(a);
+    else render_fwd_kernel<false><<<dim3(a.grid_x, a.grid_y), RENDER_THREADS, 0, s>>>(a);
 }

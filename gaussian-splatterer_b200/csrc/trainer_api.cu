@@ -237,7 +237,7 @@ inline void mark(cudaEvent_t* ev, int k, cudaStream_t s) {
 // forward half of one view pass: preprocess (+ per-tile counts), tile scan, emit, per-tile sort, render forward
 int forward_pass(gsb_trainer* t, const float* view, const float* projview, const float* campos, float tanx, float tany,
                  float scale_modifier, const float* bg, int W, int H, ImageWs& im, float* out_color, uint32_t* h_R,
-                 cudaEvent_t* ev = nullptr, cudaEvent_t scan_done = nullptr) {
+                 cudaEvent_t* ev = nullptr, cudaEvent_t scan_done = nullptr, uint32_t* frame = nullptr) {
     GSB_NVTX("gsb forward chain");
     cudaStream_t s = t->exec_f ? t->exec_f : t->stream;
     const int grid_x = (W + GSB_TILE - 1) / GSB_TILE, grid_y = (H + GSB_TILE - 1) / GSB_TILE;
@@ -281,6 +281,7 @@ int forward_pass(gsb_trainer* t, const float* view, const float* projview, const
     ra.W = W; ra.H = H; ra.grid_x = grid_x; ra.grid_y = grid_y;
     ra.ranges = im.ranges; ra.point_list = t->b.point_list; ra.recs = t->g.recs; ra.bg = bg;
     ra.out_color = out_color; ra.final_T = im.final_T; ra.n_contrib = im.n_contrib; ra.tile_max = im.tile_max;
+    ra.frame = frame;                 // Trainer::render: RGBA8 straight from the blend registers (imageFloatToInt fused)
     { GSB_NVTX("render forward"); launch_render_fwd(ra, s); }
     t->stats.kernel_launches += 6;
     GSB_CUDA_OK(cudaGetLastError());
@@ -730,6 +731,7 @@ int gsb_trainer_count_pairs(gsb_trainer* t, int camera_index, unsigned long long
     ra.W = t->W; ra.H = t->H; ra.grid_x = t->grid_x; ra.grid_y = t->grid_y;
     ra.ranges = t->im.ranges; ra.point_list = t->b.point_list; ra.recs = t->g.recs; ra.bg = t->d_bg + 3;
     ra.out_color = t->rendered; ra.final_T = t->im.final_T; ra.n_contrib = t->im.n_contrib; ra.tile_max = t->im.tile_max;
+    ra.frame = nullptr;
     launch_count_pairs(ra, t->d_pairs, s);
     GSB_CUDA_OK(cudaMemcpyAsync(out8, t->d_pairs, 6 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
     uint32_t cnt[2] = {0, 0};
@@ -952,12 +954,10 @@ int gsb_trainer_render(gsb_trainer* t, uint32_t* dev_frame_buffer, int width, in
         }
         hR = t->h_R;
         if (int e = forward_pass(t, dc->view, dc->projview, dc->location, camera->tan_fovx, camera->tan_fovy, splat_scale,
-                                 t->d_bg + 3, width, height, im, color, hR)) {
+                                 t->d_bg + 3, width, height, im, color, hR, nullptr, nullptr, dev_frame_buffer)) {
             t->dirty = true;
             return e;
         }
-        launch_image_float_to_int(color, dev_frame_buffer, width, height, s);
-        t->stats.kernel_launches++;
         GSB_CUDA_OK(cudaStreamSynchronize(s));   // the reference ends render() with a device sync (T:215)
         if (t->count == 0 || hR[0] <= t->r_cap) break;
         if (int e = ensure_bin(t, (uint32_t)std::min<size_t>(0x7FFFFFF0u, (size_t)hR[0] + hR[0] / 4 + 4096))) return e;

@@ -30,9 +30,19 @@ if has refncu; then
 fi
 if has full; then
   # full capture of the two render kernels in the BENCH configuration (all 64 cameras): roofline.traffic comes from this report
-  CMD="ncu --set full --clock-control none --import-source on -k regex:render_(bwd|fwd)_kernel --launch-skip 40 -c 8 -f -o $OUT/${TAG}_prof_render python bench.py --steps 1 --warmup 1 --no-cpu-baseline --no-e2e"
+  # (the first 128 render_fwd launches of the process render the truth frames from the 250 k teacher cloud: skipped)
+  CMD="ncu --set full --clock-control none --import-source on -k regex:render_(bwd|fwd)_kernel --launch-skip 170 -c 6 -f -o $OUT/${TAG}_prof_render python bench.py --steps 1 --warmup 1 --no-cpu-baseline --no-e2e"
   echo "$CMD" > $OUT/${TAG}_prof_render.cmd
   timeout 900 $CMD > $OUT/${TAG}_ncu_full.log 2>&1; echo "ncu full exit $?"
+fi
+if has skeleton; then
+  # A/B of VERDICT r01 item 5: shipped fused render backward vs the lanes = list entries skeleton (lower bound), 6 C4 cameras
+  timeout 600 python tools/gpu_bwd_skeleton.py C4 3 > $OUT/${TAG}_bwd_skeleton.json 2> $OUT/${TAG}_bwd_skeleton.err; echo "skeleton exit $?"
+  head -c 400 $OUT/${TAG}_bwd_skeleton.json; echo
+fi
+if has stream; then
+  # full capture of the streaming kernels (preprocess, binning chain, preprocess backward) at the bench's sizes
+  timeout 900 ncu --set full --clock-control none --import-source on -k regex:'(preprocess_fwd|preprocess_bwd|emit|tile_sort|tile_scan|apply_gradients)' --launch-skip 40 -c 12 -f -o $OUT/${TAG}_prof_stream $BENCH_SMALL > $OUT/${TAG}_ncu_stream.log 2>&1; echo "ncu stream exit $?"
 fi
 if has sanitize; then
   timeout 900 compute-sanitizer --tool memcheck --error-exitcode 9 python tools/sanitize_job.py > $OUT/${TAG}_memcheck.log 2>&1; echo "memcheck exit $?"
