@@ -62,6 +62,25 @@ if has mgpu; then
     fi
   done
 fi
+if has mgputest; then
+  # the world-size-2 parity tests only (torchrun inside pytest) + the C++ compat demo on two devices
+  python -m pytest tests/test_multi_gpu_gpu.py -m gpu -x -q > $OUT/${TAG}_pytest_mgpu.log 2>&1; echo "pytest mgpu exit $?"
+  tail -5 $OUT/${TAG}_pytest_mgpu.log
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29512 bench.py --gpus 2 --steps 10 --warmup 3 > $OUT/${TAG}_bench_n2.json 2> $OUT/${TAG}_bench_n2.err; echo "bench n2 exit $?"
+  head -c 400 $OUT/${TAG}_bench_n2.json; echo
+fi
+if has scale8c; then
+  # 8 GPUs, trimmed to what only this lease can show: the bench line at N = 8 (with the correctness job), C5 as written
+  # (3 M splats, 128 cameras, densify every 2nd step), the host-link ceiling, compat Trainer on 8 devices
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node $NGPU --master-addr 127.0.0.1 --master-port 29528 bench.py --gpus $NGPU --steps 8 --warmup 3 --no-cpu-baseline > $OUT/${TAG}_bench_n$NGPU.json 2> $OUT/${TAG}_bench_n$NGPU.err; echo "bench n$NGPU exit $?"
+  head -c 300 $OUT/${TAG}_bench_n$NGPU.json; echo
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node $NGPU --master-addr 127.0.0.1 --master-port 29531 bench.py --gpus $NGPU --config C5 --densify-every 2 --steps 6 --warmup 3 --no-mgpu-check --no-cpu-baseline > $OUT/${TAG}_bench_c5_n$NGPU.json 2> $OUT/${TAG}_bench_c5_n$NGPU.err; echo "bench c5 exit $?"
+  head -c 300 $OUT/${TAG}_bench_c5_n$NGPU.json; echo
+  timeout 300 python tools/h2d_probe.py --mb 133 --reps 20 > $OUT/${TAG}_h2d_probe.json 2> $OUT/${TAG}_h2d_probe.err; echo "h2d probe exit $?"
+  head -c 600 $OUT/${TAG}_h2d_probe.json; echo
+  (cd tests/compat && timeout 300 ./compat_demo --devices $NGPU > ../../$OUT/${TAG}_compat_devices.json 2> ../../$OUT/${TAG}_compat_devices.err; echo "compat devices exit $?")
+  head -c 400 $OUT/${TAG}_compat_devices.json; echo
+fi
 if has scale8; then
   # the 8-GPU evidence of round 2: strong scaling at C4 with the correctness job, C5 with periodic densify, host-link ceiling
   for N in 4 8; do
