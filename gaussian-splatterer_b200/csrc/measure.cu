@@ -10,6 +10,7 @@
 // One thread per pixel, no staging: this replays the blend decisions with the same pinned arithmetic
 // as render_fwd.cu, so the counts are those of the images actually produced.
 
+#include <cuda.h>
 #include "common.cuh"
 
 namespace {
@@ -153,6 +154,98 @@ __global__ void __launch_bounds__(128) render_bwd_lanes_are_splats_skeleton(cons
     }
 }
 
+// ---- A/B: staging of the render kernels' records, cp.async (LDGSTS) against the TMA row gather ------------------------
+// VERDICT r01 item 8b.  sm_100's cp.async.bulk.tensor.2d...tile::gather4 fetches four rows of a 2-D tensor by index: with
+// the record array described as [P][12 floats] and a box of {12, 1} one instruction brings four 48-byte records into
+// 192 contiguous bytes of shared memory (tools/tma_gather4_probe.cu found the tensor-map shape; the destination must be
+// 128-byte aligned, so every group of four records takes a 256-byte slot).  This kernel does only what the render
+// kernels' staging does -- every warp of a tile walks the tile's whole list in chunks of 32 entries, one chunk ahead,
+// double-buffered -- and consumes a chunk by reading one word of every record, so the time is the staging's:
+//   MODE 0: three 16-byte cp.async per lane and chunk (what ships)
+//   MODE 1: lanes 0-7 issue one gather4 each (the instruction takes its coordinates from uniform registers: the
+//           compiler serialises the eight lanes), completion through an mbarrier per buffer
+//   MODE 2: lane 0 issues the eight gather4 of a chunk
+template <int MODE>
+__global__ void __launch_bounds__(128) staging_ab_kernel(const RenderFwdArgs a, const __grid_constant__ CUtensorMap tmap, float* sink) {
+    __shared__ __align__(128) float4 s_rec[4][2][8][16];        // [warp][buffer][group of four records][256 B slot]
+    __shared__ uint32_t s_id[4][2][32];
+    __shared__ __align__(8) unsigned long long s_bar[4][2];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tile = blockIdx.y * a.grid_x + blockIdx.x;
+    const uint2 range = a.ranges[tile];
+    const int len = (int)(range.y - range.x);
+    const int chunks = (len + 31) / 32;
+    const uint32_t* list = a.point_list + range.x;
+    if (MODE != 0) {
+        if (lane < 2) {
+            const uint32_t b = (uint32_t)__cvta_generic_to_shared(&s_bar[warp][lane]);
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(b) : "memory");
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        __syncwarp();
+    }
+    auto issue = [&](int c) {
+        const int buf = c & 1;
+        const int q = c * 32 + lane;
+        const uint32_t id = q < len ? list[q] : 0u;               // (rows past the end of the list fetch record 0: never consumed)
+        if (MODE == 0) {
+            if (q < len) {
+                const SplatRec* g = a.recs + id;
+                float4* d = &s_rec[warp][buf][lane >> 2][(lane & 3) * 3];
+                const uint32_t da = (uint32_t)__cvta_generic_to_shared(d);
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(da), "l"(&g->a) : "memory");
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(da + 16), "l"(&g->b) : "memory");
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(da + 32), "l"(&g->c) : "memory");
+            }
+            asm volatile("cp.async.commit_group;" ::: "memory");
+        } else {
+            s_id[warp][buf][lane] = id;
+            __syncwarp();
+            const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&s_bar[warp][buf]);
+            if (lane == 0) asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(8 * 192) : "memory");
+            __syncwarp();
+            if (MODE == 1) {
+                if (lane < 8) {
+                    const uint4 r = *reinterpret_cast<const uint4*>(&s_id[warp][buf][4 * lane]);
+                    const uint32_t da = (uint32_t)__cvta_generic_to_shared(&s_rec[warp][buf][lane][0]);
+                    asm volatile("cp.async.bulk.tensor.2d.shared::cta.global.tile::gather4.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4, %5, %6}], [%7];"
+                                 ::"r"(da), "l"(&tmap), "r"(0), "r"(r.x), "r"(r.y), "r"(r.z), "r"(r.w), "r"(bar) : "memory");
+                }
+            } else if (lane == 0) {
+#pragma unroll 1
+                for (int g = 0; g < 8; g++) {
+                    const uint4 r = *reinterpret_cast<const uint4*>(&s_id[warp][buf][4 * g]);
+                    const uint32_t da = (uint32_t)__cvta_generic_to_shared(&s_rec[warp][buf][g][0]);
+                    asm volatile("cp.async.bulk.tensor.2d.shared::cta.global.tile::gather4.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4, %5, %6}], [%7];"
+                                 ::"r"(da), "l"(&tmap), "r"(0), "r"(r.x), "r"(r.y), "r"(r.z), "r"(r.w), "r"(bar) : "memory");
+                }
+            }
+        }
+    };
+    float acc = 0.f;
+    if (chunks > 0) issue(0);
+    for (int c = 0; c < chunks; c++) {
+        const int buf = c & 1;
+        if (MODE == 0) {
+            asm volatile("cp.async.wait_group 0;" ::: "memory");
+        } else {
+            const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&s_bar[warp][buf]);
+            const uint32_t parity = (uint32_t)((c >> 1) & 1);
+            uint32_t done = 0;
+            for (int it = 0; it < (1 << 22) && !done; it++)       // bounded: a copy that never lands must not hang the box
+                asm volatile("{ .reg .pred q; mbarrier.try_wait.parity.shared::cta.b64 q, [%1], %2; selp.u32 %0, 1, 0, q; }"
+                             : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+            if (!done) { if (lane == 0) sink[1] = -1.0f; return; }
+        }
+        __syncwarp();
+        if (c + 1 < chunks) issue(c + 1);
+        if (c * 32 + lane < len) acc += s_rec[warp][buf][lane >> 2][(lane & 3) * 3 + 1].y;   // opacity of this lane's record
+    }
+    if (MODE == 0) asm volatile("cp.async.wait_group 0;" ::: "memory");
+    if (acc == 1.2345e30f) sink[0] = acc;
+}
+
 // FP32 issue peak, measured: every thread runs 8 independent FFMA chains (scalar) or 8 independent packed FFMA2
 // chains (fma.rn.f32x2: two FMAs per issue slot) long enough for the launch overhead to vanish.  The render kernels'
 // roofline denominator is the scalar figure; the packed one shows what the f32x2 path could add on top.
@@ -231,6 +324,15 @@ int gsb_measure_fp32_peak_impl(double* out2, cudaStream_t s) {
 
 void launch_bwd_skeleton(const RenderBwdArgs& a, cudaStream_t s) {
     render_bwd_lanes_are_splats_skeleton<<<dim3(a.grid_x, a.grid_y), 128, 0, s>>>(a);
+}
+
+// opacity check value of mode `mode` is not needed: the three modes are timed only.  Returns the launch error, if any.
+void launch_staging_ab(const RenderFwdArgs& a, const void* tensor_map, int mode, float* sink, cudaStream_t s) {
+    const CUtensorMap tm = *static_cast<const CUtensorMap*>(tensor_map);
+    const dim3 grid(a.grid_x, a.grid_y);
+    if (mode == 0) staging_ab_kernel<0><<<grid, 128, 0, s>>>(a, tm, sink);
+    else if (mode == 1) staging_ab_kernel<1><<<grid, 128, 0, s>>>(a, tm, sink);
+    else staging_ab_kernel<2><<<grid, 128, 0, s>>>(a, tm, sink);
 }
 
 void launch_count_pairs(const RenderFwdArgs& a, unsigned long long* out, cudaStream_t s) {

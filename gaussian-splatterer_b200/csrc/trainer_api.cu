@@ -12,6 +12,7 @@
 //     render-backward prologue and the preprocess-backward epilogue
 //   * densify runs on the GPU (classify + scan + scatter) instead of a D2H / CPU / H2D round trip.
 
+#include <cuda.h>
 #include "workspace.cuh"
 #include "trainer_kernels.cuh"
 #include "../../include/gsb.h"
@@ -782,6 +783,69 @@ int gsb_trainer_measure_bwd_skeleton(gsb_trainer* t, int camera_index, int reps,
     cudaEventDestroy(e0); cudaEventDestroy(e1);
     GSB_CUDA_OK(cudaMemsetAsync(t->grads2, 0, (size_t)t->geom_P * sizeof(GradRec2), s));   // the scratch must be clean again
     GSB_CUDA_OK(cudaStreamSynchronize(s));
+    GSB_CUDA_OK(cudaGetLastError());
+    return GSB_OK;
+}
+
+// A/B of the record staging (csrc/measure.cu staging_ab_kernel): out_ms3 = {cp.async, gather4 by lanes 0-7, gather4 by
+// lane 0}, best of `reps` launches each over the tile lists of training camera `camera_index`; a mode whose copies did not
+// complete reports -1.
+int gsb_trainer_measure_staging(gsb_trainer* t, int camera_index, int reps, float* out_ms3) {
+    if (!t || !out_ms3 || reps <= 0) return gsb_fail_msg("gsb_trainer_measure_staging: invalid argument");
+    const int n = (int)t->truthW.size();
+    if (n == 0 || camera_index < 0 || camera_index >= n || t->count <= 0 || !t->geom || !t->bin) {
+        gsb_fail_msg("gsb_trainer_measure_staging: run gsb_trainer_accumulate once first");
+        return GSB_ERR_STATE;
+    }
+    cudaStream_t s = t->stream;
+    if (int e = clean_if_dirty(t)) return e;
+    const gsb_camera* dc = t->d_cams + camera_index;
+    if (int e = forward_pass(t, dc->view, dc->projview, dc->location, t->cams[camera_index].tan_fovx,
+                             t->cams[camera_index].tan_fovy, 1.0f, t->d_bg + 3, t->W, t->H, t->im, t->rendered, t->h_R)) {
+        t->dirty = true;
+        return e;
+    }
+    typedef CUresult (*EncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                 const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                 CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    GSB_CUDA_OK(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres));
+    if (!fn) return gsb_fail_msg("gsb_trainer_measure_staging: cuTensorMapEncodeTiled unavailable");
+    CUtensorMap tm;
+    const cuuint64_t dims[2] = {12, (cuuint64_t)t->count};
+    const cuuint64_t strides[1] = {sizeof(SplatRec)};
+    const cuuint32_t box[2] = {12, 1}, estr[2] = {1, 1};
+    if (((EncodeFn)fn)(&tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, t->g.recs, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                       CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+        return gsb_fail_msg("gsb_trainer_measure_staging: cuTensorMapEncodeTiled failed");
+    RenderFwdArgs ra;
+    ra.W = t->W; ra.H = t->H; ra.grid_x = t->grid_x; ra.grid_y = t->grid_y;
+    ra.ranges = t->im.ranges; ra.point_list = t->b.point_list; ra.recs = t->g.recs; ra.bg = t->d_bg + 3;
+    ra.out_color = t->rendered; ra.final_T = t->im.final_T; ra.n_contrib = t->im.n_contrib; ra.tile_max = t->im.tile_max;
+    ra.frame = nullptr;
+    float* sink = nullptr;
+    GSB_CUDA_OK(cudaMalloc(&sink, 2 * sizeof(float)));
+    cudaEvent_t e0, e1;
+    GSB_CUDA_OK(cudaEventCreate(&e0));
+    GSB_CUDA_OK(cudaEventCreate(&e1));
+    for (int mode = 0; mode < 3; mode++) {
+        float best = 1e30f;
+        GSB_CUDA_OK(cudaMemsetAsync(sink, 0, 2 * sizeof(float), s));
+        for (int r = 0; r < reps + 1; r++) {
+            GSB_CUDA_OK(cudaEventRecord(e0, s));
+            launch_staging_ab(ra, &tm, mode, sink, s);
+            GSB_CUDA_OK(cudaEventRecord(e1, s));
+            GSB_CUDA_OK(cudaEventSynchronize(e1));
+            float ms = 0.f;
+            GSB_CUDA_OK(cudaEventElapsedTime(&ms, e0, e1));
+            if (r > 0) best = std::min(best, ms);
+        }
+        float flag[2] = {0.f, 0.f};
+        GSB_CUDA_OK(cudaMemcpy(flag, sink, sizeof(flag), cudaMemcpyDeviceToHost));
+        out_ms3[mode] = flag[1] < 0.f ? -1.0f : best;
+    }
+    cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(sink);
     GSB_CUDA_OK(cudaGetLastError());
     return GSB_OK;
 }

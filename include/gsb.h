@@ -271,6 +271,10 @@ int gsb_measure_fp32_peak(double* out2, void* stream);
  * the "lanes = list entries" mapping (out_ms2[1], a lower bound: no forward checkpoints, results not gradients) on the
  * state of local camera `camera_index`, best of `reps`.  Needs one prior gsb_trainer_accumulate. */
 int gsb_trainer_measure_bwd_skeleton(gsb_trainer* t, int camera_index, int reps, float* out_ms2);
+/* Measurement (A/B): staging of the render kernels' 48-byte records over the tile lists of one
+ * training camera, out_ms3 = {16-byte cp.async (what ships), TMA row gather (cp.async.bulk.tensor.2d tile::gather4)
+ * issued by eight lanes, the same issued by one lane}; -1 for a mode whose copies did not complete. */
+int gsb_trainer_measure_staging(gsb_trainer* t, int camera_index, int reps, float* out_ms3);
 
 /* Testing: preset the look-back epoch counter (30-bit tags in the chained-scan status words) so the wrap
  * path can be exercised without running 2^30 launches. */

@@ -40,6 +40,11 @@ if has skeleton; then
   timeout 600 python tools/gpu_bwd_skeleton.py C4 3 > $OUT/${TAG}_bwd_skeleton.json 2> $OUT/${TAG}_bwd_skeleton.err; echo "skeleton exit $?"
   head -c 400 $OUT/${TAG}_bwd_skeleton.json; echo
 fi
+if has staging; then
+  # A/B of VERDICT r01 item 8b: record staging by cp.async against the TMA row gather (tile::gather4)
+  timeout 300 python tools/gpu_staging_ab.py C4 2 > $OUT/${TAG}_staging_ab.json 2> $OUT/${TAG}_staging_ab.err; echo "staging exit $?"
+  head -c 600 $OUT/${TAG}_staging_ab.json; echo; tail -3 $OUT/${TAG}_staging_ab.err
+fi
 if has stream; then
   # full capture of the streaming kernels (preprocess, binning chain, preprocess backward) at the bench's sizes
   timeout 900 ncu --set full --clock-control none --import-source on -k regex:'(preprocess_fwd|preprocess_bwd|emit|tile_sort|tile_scan|apply_gradients)' --launch-skip 40 -c 12 -f -o $OUT/${TAG}_prof_stream $BENCH_SMALL > $OUT/${TAG}_ncu_stream.log 2>&1; echo "ncu stream exit $?"
