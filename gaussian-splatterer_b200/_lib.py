@@ -149,6 +149,8 @@ def lib():
     L.gsb_trainer_measure_bwd_skeleton.restype = i
     L.gsb_trainer_measure_staging.argtypes = [vp, i, i, C.POINTER(C.c_float)]
     L.gsb_trainer_measure_staging.restype = i
+    L.gsb_trainer_reduction_stats.argtypes = [vp, i, C.POINTER(C.c_ulonglong)]
+    L.gsb_trainer_reduction_stats.restype = i
     L.gsb_measure_fp32_peak.argtypes = [C.POINTER(C.c_double), vp]
     L.gsb_measure_fp32_peak.restype = i
     L.gsb_trainer_debug_set_epoch.argtypes = [vp, C.c_uint]
@@ -167,7 +169,7 @@ EXPORTED_SYMBOLS = [
     "gsb_rasterizer_mark_visible", "gsb_rasterizer_state", "gsb_rasterizer_sorted_keys",
     "gsb_trainer_enable_loss", "gsb_trainer_get_loss", "gsb_trainer_set_fuse_backgrounds", "gsb_trainer_profile_pass",
     "gsb_trainer_set_stage_timing", "gsb_trainer_get_stage_times", "gsb_trainer_count_pairs", "gsb_trainer_set_overlap",
-    "gsb_trainer_debug_set_epoch", "gsb_measure_fp32_peak", "gsb_trainer_measure_bwd_skeleton", "gsb_trainer_measure_staging",
+    "gsb_trainer_debug_set_epoch", "gsb_measure_fp32_peak", "gsb_trainer_measure_bwd_skeleton", "gsb_trainer_measure_staging", "gsb_trainer_reduction_stats",
     "gsb_comm_nccl_version", "gsb_comm_get_unique_id", "gsb_comm_init", "gsb_comm_init_all", "gsb_comm_destroy",
     "gsb_comm_rank", "gsb_comm_world", "gsb_comm_device", "gsb_comm_allreduce_sum", "gsb_comm_broadcast",
     "gsb_trainer_set_comm", "gsb_comm_window_create", "gsb_comm_window_destroy", "gsb_window_data", "gsb_window_floats",

@@ -224,6 +224,7 @@ void launch_render_bwd(const RenderBwdArgs& a, cudaStream_t s);
 void launch_count_pairs(const RenderFwdArgs& a, unsigned long long* out, cudaStream_t s);
 int gsb_measure_fp32_peak_impl(double* out2, cudaStream_t s);
 void launch_bwd_skeleton(const RenderBwdArgs& a, cudaStream_t s);   // A/B lower bound, see measure.cu
+void launch_reduction_stats(const RenderBwdArgs& a, unsigned long long* out40, cudaStream_t s);   // measurement, see measure.cu
 void launch_staging_ab(const RenderFwdArgs& a, const void* tensor_map, int mode, float* sink, cudaStream_t s);   // A/B, see measure.cu
 
 // preprocess_bwd.cu

@@ -246,6 +246,75 @@ __global__ void __launch_bounds__(128) staging_ab_kernel(const RenderFwdArgs a, 
     if (acc == 1.2345e30f) sink[0] = acc;
 }
 
+// ---- statistics of the render backward's reductions ---------------------------------------------------------------------
+// For every (8x8 block, list entry) with at least one blended pixel (= one reduction of render_bwd_kernel): how many of
+// the warp's 32 lanes hold a blended pixel (lane = column x row pair (r, r + 4), the backward's mapping), and whether the
+// blended pixels stay inside the top or bottom four rows / the left or right four columns of the block.
+//   out[0..32]  histogram of the number of lanes with a blended pixel (index 0 unused)
+//   out[33]     reductions that go through the shared-memory panel (more than GSB_BWD_DIRECT = 4 lanes)
+//   out[34]     ... of those, blended pixels confined to rows 0-3 or rows 4-7
+//   out[35]     ... of those, confined to columns 0-3 or columns 4-7
+//   out[36]     ... of those, either
+//   out[37]     blended (pixel, entry) pairs
+//   out[38]     (warp, entry) pairs the bounding-box test lets through
+__global__ void __launch_bounds__(128) reduction_stats_kernel(const RenderBwdArgs a, unsigned long long* out) {
+    __shared__ unsigned int s_h[40];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid < 40) s_h[tid] = 0u;
+    __syncthreads();
+    const int tile = blockIdx.y * a.grid_x + blockIdx.x;
+    const int start = (int)a.tile_max[tile];
+    const uint2 range = a.ranges[tile];
+    const int bx0 = blockIdx.x * GSB_TILE + (warp & 1) * 8, by0 = blockIdx.y * GSB_TILE + (warp >> 1) * 8;
+    const int pix_x = bx0 + (lane & 7);
+    const float pxf = (float)pix_x, bcx = (float)bx0 + 3.5f, bcy = (float)by0 + 3.5f;
+    float pyf[2];
+    int nc[2];
+    for (int k = 0; k < 2; k++) {
+        const int py = by0 + (lane >> 3) + 4 * k;
+        pyf[k] = (float)py;
+        nc[k] = (pix_x < a.W && py < a.H) ? (int)a.n_contrib[(size_t)py * a.W + pix_x] : 0;
+    }
+    for (int j = 0; j < start; j++) {
+        const SplatRec& r = a.recs[a.point_list[range.x + j]];
+        const float4 ra = r.a, rb = r.b, rc = r.c;
+        if (!((fabsf(ra.x - bcx) <= rc.z + 3.5f) && (fabsf(ra.y - bcy) <= rc.w + 3.5f))) continue;   // uniform over the warp
+        bool hit[2];
+        for (int k = 0; k < 2; k++) {
+            const float dx = __fsub_rn(ra.x, pxf), dy = __fsub_rn(ra.y, pyf[k]);
+            const float ay = __fmul_rn(dy, __fmul_rn(dy, rb.x));
+            const float power = __fmaf_rn(__fmaf_rn(dx, __fmul_rn(dx, ra.z), ay), -0.5f, -__fmul_rn(dy, __fmul_rn(dx, ra.w)));
+            hit[k] = j < nc[k] && !(power > 0.0f) && !(fminf(0.99f, __fmul_rn(rb.y, expf(power))) < 1.0f / 255.0f);
+        }
+        const unsigned int b0 = __ballot_sync(0xffffffffu, hit[0]), b1 = __ballot_sync(0xffffffffu, hit[1]);
+        if (lane == 0) {
+            atomicAdd(&s_h[38], 1u);
+            const unsigned int any = b0 | b1;
+            if (any) {
+                const int lanes = __popc(any);
+                atomicAdd(&s_h[lanes], 1u);
+                atomicAdd(&s_h[37], (unsigned int)(__popc(b0) + __popc(b1)));
+                if (lanes > 4) {
+                    unsigned int cols = (any | (any >> 8) | (any >> 16) | (any >> 24)) & 0xFFu;
+                    unsigned int rows = 0;
+                    for (int q = 0; q < 4; q++) {
+                        if ((b0 >> (8 * q)) & 0xFFu) rows |= 1u << q;
+                        if ((b1 >> (8 * q)) & 0xFFu) rows |= 1u << (q + 4);
+                    }
+                    const bool tb = (rows & 0xF0u) == 0u || (rows & 0x0Fu) == 0u;
+                    const bool lr = (cols & 0xF0u) == 0u || (cols & 0x0Fu) == 0u;
+                    atomicAdd(&s_h[33], 1u);
+                    if (tb) atomicAdd(&s_h[34], 1u);
+                    if (lr) atomicAdd(&s_h[35], 1u);
+                    if (tb || lr) atomicAdd(&s_h[36], 1u);
+                }
+            }
+        }
+    }
+    __syncthreads();
+    if (tid < 40 && s_h[tid]) atomicAdd(out + tid, (unsigned long long)s_h[tid]);
+}
+
 // FP32 issue peak, measured: every thread runs 8 independent FFMA chains (scalar) or 8 independent packed FFMA2
 // chains (fma.rn.f32x2: two FMAs per issue slot) long enough for the launch overhead to vanish.  The render kernels'
 // roofline denominator is the scalar figure; the packed one shows what the f32x2 path could add on top.
@@ -333,6 +402,10 @@ void launch_staging_ab(const RenderFwdArgs& a, const void* tensor_map, int mode,
     if (mode == 0) staging_ab_kernel<0><<<grid, 128, 0, s>>>(a, tm, sink);
     else if (mode == 1) staging_ab_kernel<1><<<grid, 128, 0, s>>>(a, tm, sink);
     else staging_ab_kernel<2><<<grid, 128, 0, s>>>(a, tm, sink);
+}
+
+void launch_reduction_stats(const RenderBwdArgs& a, unsigned long long* out40, cudaStream_t s) {
+    reduction_stats_kernel<<<dim3(a.grid_x, a.grid_y), 128, 0, s>>>(a, out40);
 }
 
 void launch_count_pairs(const RenderFwdArgs& a, unsigned long long* out, cudaStream_t s) {

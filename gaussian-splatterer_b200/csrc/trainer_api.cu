@@ -850,6 +850,39 @@ int gsb_trainer_measure_staging(gsb_trainer* t, int camera_index, int reps, floa
     return GSB_OK;
 }
 
+// Statistics of the render backward's reductions for training camera `camera_index` (csrc/measure.cu
+// reduction_stats_kernel): out40 as documented there.
+int gsb_trainer_reduction_stats(gsb_trainer* t, int camera_index, unsigned long long* out40) {
+    if (!t || !out40) return gsb_fail_msg("gsb_trainer_reduction_stats: invalid argument");
+    const int n = (int)t->truthW.size();
+    if (n == 0 || camera_index < 0 || camera_index >= n || t->count <= 0 || !t->geom || !t->bin) {
+        gsb_fail_msg("gsb_trainer_reduction_stats: run gsb_trainer_accumulate once first");
+        return GSB_ERR_STATE;
+    }
+    cudaStream_t s = t->stream;
+    if (int e = clean_if_dirty(t)) return e;
+    const gsb_camera* dc = t->d_cams + camera_index;
+    if (int e = forward_pass(t, dc->view, dc->projview, dc->location, t->cams[camera_index].tan_fovx,
+                             t->cams[camera_index].tan_fovy, 1.0f, t->d_bg + 3, t->W, t->H, t->im, t->rendered, t->h_R)) {
+        t->dirty = true;
+        return e;
+    }
+    RenderBwdArgs rb;
+    memset(&rb, 0, sizeof(rb));
+    rb.W = t->W; rb.H = t->H; rb.grid_x = t->grid_x; rb.grid_y = t->grid_y;
+    rb.ranges = t->im.ranges; rb.point_list = t->b.point_list; rb.recs = t->g.recs; rb.bg = t->d_bg + 3;
+    rb.final_T = t->im.final_T; rb.n_contrib = t->im.n_contrib; rb.tile_max = t->im.tile_max;
+    unsigned long long* d = nullptr;
+    GSB_CUDA_OK(cudaMalloc(&d, 40 * sizeof(unsigned long long)));
+    GSB_CUDA_OK(cudaMemsetAsync(d, 0, 40 * sizeof(unsigned long long), s));
+    launch_reduction_stats(rb, d, s);
+    GSB_CUDA_OK(cudaMemcpyAsync(out40, d, 40 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
+    GSB_CUDA_OK(cudaStreamSynchronize(s));
+    cudaFree(d);
+    GSB_CUDA_OK(cudaGetLastError());
+    return GSB_OK;
+}
+
 int gsb_trainer_apply(gsb_trainer* t, const gsb_project_params* p) {
     if (!t || !p) return gsb_fail_msg("gsb_trainer_apply: invalid argument");
     ApplyArgs a;

@@ -275,6 +275,11 @@ int gsb_trainer_measure_bwd_skeleton(gsb_trainer* t, int camera_index, int reps,
  * training camera, out_ms3 = {16-byte cp.async (what ships), TMA row gather (cp.async.bulk.tensor.2d tile::gather4)
  * issued by eight lanes, the same issued by one lane}; -1 for a mode whose copies did not complete. */
 int gsb_trainer_measure_staging(gsb_trainer* t, int camera_index, int reps, float* out_ms3);
+/* Measurement: statistics of the render backward's per-(8x8 block, list entry) reductions of one training camera --
+ * out40[1..32] histogram of the lanes holding a blended pixel, [33] reductions through the shared-memory panel, [34] / [35] /
+ * [36] of those with the blended pixels inside one half of the block's rows / columns / either, [37] blended pairs,
+ * [38] (block, entry) pairs the bounding-box test lets through. */
+int gsb_trainer_reduction_stats(gsb_trainer* t, int camera_index, unsigned long long* out40);
 
 /* Testing: preset the look-back epoch counter (30-bit tags in the chained-scan status words) so the wrap
  * path can be exercised without running 2^30 launches. */

@@ -38,10 +38,22 @@ for i in range(len(cams)):
     pc = tr.count_pairs(i)
     rows.append({"camera": i, "fov": cams[i].fovDegY, "R": pc["R"], "cp_async_ms": round(ms[0], 4),
                  "tma_gather4_8_lanes_ms": round(ms[1], 4), "tma_gather4_1_lane_ms": round(ms[2], 4)})
+hist = [0] * 40
+for i in range(len(cams)):
+    o = (C.c_ulonglong * 40)()
+    gsb._lib.check(gsb.lib().gsb_trainer_reduction_stats(tr._h, i, o))
+    for q in range(40):
+        hist[q] += int(o[q])
+reductions = sum(hist[1:33])
+stats = {"cameras": len(cams), "reductions_per_camera": reductions / len(cams), "lanes_histogram_share": [round(h / max(reductions, 1), 4) for h in hist[1:33]],
+         "direct_share(<=4 lanes)": round(sum(hist[1:5]) / max(reductions, 1), 4), "panel_per_camera": hist[33] / len(cams),
+         "panel_confined_rows_half": round(hist[34] / max(hist[33], 1), 4), "panel_confined_cols_half": round(hist[35] / max(hist[33], 1), 4),
+         "panel_confined_either": round(hist[36] / max(hist[33], 1), 4), "blended_pairs_per_camera": hist[37] / len(cams),
+         "box_survivors_per_camera": hist[38] / len(cams), "mean_lanes_per_reduction": round(sum(q * hist[q] for q in range(1, 33)) / max(reductions, 1), 2)}
 mean = lambda k: round(sum(r[k] for r in rows) / len(rows), 4)
 print(json.dumps({"config": cfg, "cameras": len(cams), "mean_cp_async_ms": mean("cp_async_ms"),
                   "mean_tma_gather4_8_lanes_ms": mean("tma_gather4_8_lanes_ms"), "mean_tma_gather4_1_lane_ms": mean("tma_gather4_1_lane_ms"),
-                  "rows": rows,
+                  "rows": rows, "reduction_stats": stats,
                   "note": "staging only: every warp of a tile walks the tile's whole list in 32-entry chunks, double-buffered, and reads one "
                           "word of each record; best of 5 launches, CUDA events; -1 = the copies of that mode did not complete"}))
 tr.close()
