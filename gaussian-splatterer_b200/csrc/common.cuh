@@ -193,6 +193,7 @@ struct RenderFwdArgs {
     uint32_t* n_contrib;            // [H*W]
     uint32_t* tile_max;             // [tiles] max n_contrib in tile
     uint32_t* frame;                // preview mode (Trainer::render): RGBA8 [H*W] written instead of everything above
+    float expf_k1, expf_k252;       // set by the launcher: two constants of expf2_pinned (render_common.cuh) as kernel parameters
 };
 void launch_render_fwd(const RenderFwdArgs& a, cudaStream_t s);
 
@@ -215,6 +216,7 @@ struct RenderBwdArgs {
     const uint32_t* truth2;
     GradRec2* grads2;
     double* loss_out;               // optional: += sum of squared residuals (fused-loss modes only)
+    float expf_k1, expf_k252;       // set by the launcher (see RenderFwdArgs)
 };
 void launch_render_bwd(const RenderBwdArgs& a, cudaStream_t s);
 

@@ -111,6 +111,9 @@ __global__ void __launch_bounds__(RENDER_THREADS, GSB_BWD_CTAS) render_bwd_kerne
         __syncwarp();
         asm volatile("" : "+r"(col_addr), "+r"(row_addr), "+l"(gbase));
     }
+#if GSB_EXPF_PACKED
+    const ExpfConsts expk = {a.expf_k1, a.expf_k252};
+#endif
     const int tile = blockIdx.y * a.grid_x + blockIdx.x;
     const int start = (int)a.tile_max[tile];       // entries at or beyond this index were blended by no pixel
     if (start == 0 && (MODE == 0 || a.loss_out == nullptr)) return;
@@ -269,10 +272,20 @@ __global__ void __launch_bounds__(RENDER_THREADS, GSB_BWD_CTAS) render_bwd_kerne
                     if (!__any_sync(0xffffffffu, pass[0] || pass[1])) continue;
                     float G[2], alpha[2];
                     bool hit = false;
+#if GSB_EXPF_PACKED
+                    const float2 g2 = expf2_pinned(make_float2(pw[0], pw[1]), expk);
+                    const float2 og2 = mul2(dup2(rb.y), g2);
+                    const float gv[2] = {g2.x, g2.y}, ogv[2] = {og2.x, og2.y};
+#endif
 #pragma unroll
                     for (int k = 0; k < 2; k++) {
+#if GSB_EXPF_PACKED
+                        const float g = gv[k];
+                        const float al = fminf(0.99f, ogv[k]);
+#else
                         const float g = expf(pw[k]);
                         const float al = fminf(0.99f, __fmul_rn(rb.y, g));
+#endif
                         const bool h = pass[k] && !(al < 1.0f / 255.0f);
                         G[k] = h ? g : 0.f;
                         alpha[k] = h ? al : 0.f;
@@ -457,7 +470,9 @@ __global__ void __launch_bounds__(RENDER_THREADS, GSB_BWD_CTAS) render_bwd_kerne
 
 void launch_render_bwd(const RenderBwdArgs& a, cudaStream_t s) {
     const dim3 grid(a.grid_x, a.grid_y);
-    if (a.dL_dpix != nullptr) render_bwd_kernel<0><<<grid, RENDER_THREADS, 0, s>>>(a);
-    else if (a.truth2 == nullptr) render_bwd_kernel<1><<<grid, RENDER_THREADS, 0, s>>>(a);
-    else render_bwd_kernel<2><<<grid, RENDER_THREADS, 0, s>>>(a);
+    RenderBwdArgs b = a;
+    b.expf_k1 = GSB_EXPF_K1; b.expf_k252 = GSB_EXPF_K252;
+    if (b.dL_dpix != nullptr) render_bwd_kernel<0><<<grid, RENDER_THREADS, 0, s>>>(b);
+    else if (b.truth2 == nullptr) render_bwd_kernel<1><<<grid, RENDER_THREADS, 0, s>>>(b);
+    else render_bwd_kernel<2><<<grid, RENDER_THREADS, 0, s>>>(b);
 }

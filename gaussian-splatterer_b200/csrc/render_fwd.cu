@@ -55,6 +55,9 @@ __global__ void __launch_bounds__(RENDER_THREADS) render_fwd_kernel(const Render
 #pragma unroll
     for (int k = 0; k < 2; k++) done[k] = !(pix_x < a.W && pix_y[k] < a.H);
 
+#if GSB_EXPF_PACKED
+    const ExpfConsts expk = {a.expf_k1, a.expf_k252};
+#endif
     const uint2 range = a.ranges[tile];
     const int len = (int)(range.y - range.x);
     const int chunks = (len + WB - 1) / WB;
@@ -117,8 +120,13 @@ __global__ void __launch_bounds__(RENDER_THREADS) render_fwd_kernel(const Render
                 const bool pass0 = !done[0] && !(pw2.x < rc.y) && !(pw2.x > 0.0f);
                 const bool pass1 = !done[1] && !(pw2.y < rc.y) && !(pw2.y > 0.0f);
                 if (!__any_sync(0xffffffffu, pass0 || pass1)) continue;
+#if GSB_EXPF_PACKED
+                const float2 og2 = mul2(dup2(rb.y), expf2_pinned(pw2, expk));          // opacity * expf(power), both pixels
+                const float a0 = fminf(0.99f, og2.x), a1 = fminf(0.99f, og2.y);
+#else
                 const float a0 = fminf(0.99f, __fmul_rn(rb.y, expf(pw2.x)));
                 const float a1 = fminf(0.99f, __fmul_rn(rb.y, expf(pw2.y)));
+#endif
                 const bool hit0 = pass0 && !(a0 < 1.0f / 255.0f), hit1 = pass1 && !(a1 < 1.0f / 255.0f);
                 // (no second vote: a power that passes the stored threshold fails the alpha test in well under 1 % of the cases)
                 const float2 T2 = make_float2(T[0], T[1]);
@@ -197,6 +205,8 @@ __global__ void __launch_bounds__(RENDER_THREADS) render_fwd_kernel(const Render
 }  // namespace
 
 void launch_render_fwd(const RenderFwdArgs& a, cudaStream_t s) {
-    if (a.frame != nullptr) render_fwd_kernel<true><<<dim3(a.grid_x, a.grid_y), RENDER_THREADS, 0, s>>>(a);
-    else render_fwd_kernel<false><<<dim3(a.grid_x, a.grid_y), RENDER_THREADS, 0, s>>>(a);
+    RenderFwdArgs b = a;
+    b.expf_k1 = GSB_EXPF_K1; b.expf_k252 = GSB_EXPF_K252;
+    if (b.frame != nullptr) render_fwd_kernel<true><<<dim3(b.grid_x, b.grid_y), RENDER_THREADS, 0, s>>>(b);
+    else render_fwd_kernel<false><<<dim3(b.grid_x, b.grid_y), RENDER_THREADS, 0, s>>>(b);
 }
