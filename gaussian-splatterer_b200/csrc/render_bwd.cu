@@ -53,6 +53,11 @@ namespace {
 #define GSB_BWD_CTAS 8   // resident CTAs per SM the register budget is cut for (64 registers)
 #endif
 
+#ifndef GSB_BWD_REDUX
+#define GSB_BWD_REDUX 1   // fused mode: eight panel rows read by 8 x 4 lanes, the ninth pair (H0) summed with REDUX in fixed point
+#endif
+constexpr int PANEL8_ROW = 320;  // GSB_BWD_REDUX: bytes per panel row: 32 lanes x 8 B + 64 (consecutive rows land on opposite 64-byte halves of the banks)
+
 constexpr int RED_STRIDE = 36;   // floats per row of the reduction panel: 32 lanes + 4 pad (rows stay 16-byte aligned)
 constexpr int RED_STRIDE2 = 38;  // dual mode: float2 (white, black) per lane: 32 lanes + 4 zero slots (18 chunks of 16 B) + 2 pad; the row
                                  // stride of 304 B = 48 mod 128 keeps the three readers of consecutive rows (48 contiguous bytes per row
@@ -101,6 +106,18 @@ __global__ void __launch_bounds__(RENDER_THREADS, GSB_BWD_CTAS) render_bwd_kerne
     // lane = 3 * row + third (< 27) reads chunks third, third + 3, ..., third + 15 of its row (six 128-bit loads in flight
     // together: one shared-memory round trip; slots 32..35 of a row stay zero); the lanes with third == 0 collect the
     // other two partial pairs with two shuffles and issue the RED for pair `row` of the GradRec2
+#if GSB_BWD_REDUX
+    // fused mode, GSB_BWD_REDUX: the panel holds pairs 1..8 (Hx .. b) as eight rows of 32 (white, black) pairs; lane = 4 * row +
+    // quarter reads chunks quarter, quarter + 4, + 8, + 12 of its row (four 128-bit loads: every quarter-warp covers two rows =
+    // all 32 banks once), two xor-shuffles add the four partial pairs, the lanes with quarter == 0 issue the RED of pair
+    // row + 1; pair 0 (H0) never touches shared memory (see below) and is added by lane 1
+    const int rrow = lane >> 2, third = lane & 3;
+    uint32_t col_addr = (uint32_t)__cvta_generic_to_shared(red) + lane * 8;
+    uint32_t row_addr = (uint32_t)__cvta_generic_to_shared(red) + rrow * PANEL8_ROW + third * 16;
+    float* gbase = third == 0 ? reinterpret_cast<float*>(a.grads2) + (rrow + 1) * 2
+                              : (lane == 1 ? reinterpret_cast<float*>(a.grads2) : nullptr);
+    if (NS == 2) asm volatile("" : "+r"(col_addr), "+r"(row_addr), "+l"(gbase));
+#else
     const int rrow = lane / 3, third = lane - 3 * rrow;
     uint32_t col_addr = (uint32_t)__cvta_generic_to_shared(red) + lane * 8;
     uint32_t row_addr = lane < 27 ? (uint32_t)__cvta_generic_to_shared(red) + rrow * RED_STRIDE2 * 8 + third * 16 : 0u;
@@ -111,6 +128,7 @@ __global__ void __launch_bounds__(RENDER_THREADS, GSB_BWD_CTAS) render_bwd_kerne
         __syncwarp();
         asm volatile("" : "+r"(col_addr), "+r"(row_addr), "+l"(gbase));
     }
+#endif
 #if GSB_EXPF_PACKED
     const ExpfConsts expk = {a.expf_k1, a.expf_k252};
 #endif
@@ -407,6 +425,58 @@ __global__ void __launch_bounds__(RENDER_THREADS, GSB_BWD_CTAS) render_bwd_kerne
                     const float2 dx2 = dup2(dx);
                     const float2 A2 = make_float2(mA[0], mA[1]), B2 = make_float2(mB[0], mB[1]);
                     const float2 ax = mul2(A2, dx2);
+#if GSB_BWD_REDUX
+                    // Eight of the nine pairs go through the panel: 8 x 32 pairs = 128 chunks of 16 B = four 128-bit loads
+                    // for each of 32 reader lanes, no padding, every quarter-warp of a load on all 32 banks once
+                    // (16 + 16 wavefronts against 18 + 24 for nine rows read by 27 lanes).
+                    sts64(col_addr + 0 * PANEL8_ROW, ax);                                        // Hx
+                    sts64(col_addr + 1 * PANEL8_ROW, B2);                                        // Hy
+                    sts64(col_addr + 2 * PANEL8_ROW, mul2(ax, dx2));                             // Hxx
+                    sts64(col_addr + 3 * PANEL8_ROW, mul2(B2, dx2));                             // Hxy
+                    sts64(col_addr + 4 * PANEL8_ROW, make_float2(mC[0], mC[1]));                 // Hyy
+                    sts64(col_addr + 5 * PANEL8_ROW, make_float2(vr[0], vr[1]));
+                    sts64(col_addr + 6 * PANEL8_ROW, make_float2(vg[0], vg[1]));
+                    sts64(col_addr + 7 * PANEL8_ROW, make_float2(vb[0], vb[1]));
+                    __syncwarp();
+                    // The ninth pair, H0 = sum h, is added across the warp by the integer REDUX unit instead (no shared-memory
+                    // wavefront at all): the lanes' values are scaled by a common power of two chosen from the largest
+                    // magnitude in the warp (REDUX.MAX on the float bits) so that each fits 25 bits, rounded to integers,
+                    // summed exactly, and scaled back.  Every addend is represented to 2^-24 of the largest one -- the
+                    // resolution a float sum of these values has anyway.  Non-finite or huge values (exponent >= 127) take a
+                    // shuffle butterfly instead.
+                    float2 h0;
+                    {
+                        const uint32_t mb = __float_as_uint(fmaxf(fabsf(A2.x), fabsf(A2.y)));
+                        const uint32_t wm = __reduce_max_sync(0xffffffffu, mb);
+                        if (wm < 0x7F000000u) {
+                            const int E = max((int)(wm >> 23), 25);                       // biased exponent of the largest magnitude
+                            const float scale = __int_as_float((278 - E) << 23);          // 2^(24 - (E - 127)): |x| * scale < 2^25
+                            const float inv = __int_as_float((E - 24) << 23);             // 1 / scale
+                            const int qw = __float2int_rn(A2.x * scale), qb = __float2int_rn(A2.y * scale);
+                            const int sw = __reduce_add_sync(0xffffffffu, qw), sb = __reduce_add_sync(0xffffffffu, qb);
+                            h0 = make_float2((float)sw * inv, (float)sb * inv);
+                        } else {
+                            h0 = A2;
+#pragma unroll
+                            for (int o = 16; o > 0; o >>= 1) {
+                                h0.x += __shfl_xor_sync(0xffffffffu, h0.x, o);
+                                h0.y += __shfl_xor_sync(0xffffffffu, h0.y, o);
+                            }
+                        }
+                    }
+                    {
+                        float2 p[4];
+#pragma unroll
+                        for (int c = 0; c < 4; c++) {
+                            const float4 t = lds128(row_addr + c * 64);
+                            p[c] = add2(make_float2(t.x, t.y), make_float2(t.z, t.w));
+                        }
+                        float2 part = add2(add2(p[0], p[1]), add2(p[2], p[3]));
+                        part = add2(part, make_float2(__shfl_xor_sync(0xffffffffu, part.x, 1), __shfl_xor_sync(0xffffffffu, part.y, 1)));
+                        part = add2(part, make_float2(__shfl_xor_sync(0xffffffffu, part.x, 2), __shfl_xor_sync(0xffffffffu, part.y, 2)));
+                        if (gbase != nullptr) red_add2(gbase + (size_t)splat * (sizeof(GradRec2) / 4), lane == 1 ? h0 : part);
+                    }
+#else
                     sts64(col_addr + 0 * RED_STRIDE2 * 8, A2);                                   // H0
                     sts64(col_addr + 1 * RED_STRIDE2 * 8, ax);                                   // Hx
                     sts64(col_addr + 2 * RED_STRIDE2 * 8, B2);                                   // Hy
@@ -432,6 +502,7 @@ __global__ void __launch_bounds__(RENDER_THREADS, GSB_BWD_CTAS) render_bwd_kerne
                         const float2 d2 = make_float2(__shfl_down_sync(0xffffffffu, part.x, 2), __shfl_down_sync(0xffffffffu, part.y, 2));
                         if (gbase != nullptr) red_add2(gbase + (size_t)splat * (sizeof(GradRec2) / 4), add2(part, add2(d1, d2)));
                     }
+#endif
                 } else {
                     // one set: [9][RED_STRIDE] floats (conflict-free: bank = 4*row + lane), lane r adds up row r
                     // with eight 128-bit loads and issues the one RED for GradRec float r
