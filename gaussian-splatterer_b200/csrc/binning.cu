@@ -68,11 +68,14 @@ constexpr int SC_TILE = 256 * SC_IPT;
 __global__ void __launch_bounds__(256) tile_scan_kernel(uint32_t* __restrict__ tile_count, uint32_t tiles, uint2* __restrict__ ranges,
                                                         unsigned long long* lookback, uint32_t epoch, GsbCtrl* ctrl,
                                                         uint32_t r_cap, uint32_t* num_rendered_host,
-                                                        uint32_t* __restrict__ big_list, uint2* __restrict__ chunk_list) {
+                                                        uint32_t* __restrict__ big_list, uint2* __restrict__ chunk_list,
+                                                        uint32_t* __restrict__ tile_order) {
     __shared__ uint32_t s_warp[8];
     __shared__ uint32_t s_tile, s_excl;
+    __shared__ uint32_t s_bn[GSB_LPT_BUCKETS], s_bbase[GSB_LPT_BUCKETS];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     if (tid == 0) s_tile = atomicAdd(&ctrl->ticket, 1u);
+    if (tid < GSB_LPT_BUCKETS) s_bn[tid] = 0u;
     __syncthreads();
     const uint32_t tile = s_tile;
     if (tile * SC_TILE >= tiles) return;
@@ -97,8 +100,26 @@ __global__ void __launch_bounds__(256) tile_scan_kernel(uint32_t* __restrict__ t
         if (w < warp) wp += s_warp[w];
         total += s_warp[w];
     }
+    // heavy-first tile order (common.cuh gsb_lpt_tile): rank inside the CTA by shared-memory atomics, one global atomic per
+    // (CTA, class) for the base
+    uint32_t lrank[SC_IPT];
+    if (tile_order) {
+#pragma unroll
+        for (int k = 0; k < SC_IPT; k++)
+            if (base + k < tiles) lrank[k] = atomicAdd(&s_bn[gsb_lpt_bucket(v[k])], 1u);
+    }
     if (tid == 0) s_excl = lookback_exclusive(lookback, tile, epoch, total);
     __syncthreads();
+    if (tile_order && tid < GSB_LPT_BUCKETS && s_bn[tid]) s_bbase[tid] = atomicAdd(&ctrl->bucket_n[tid], s_bn[tid]);
+    __syncthreads();
+    if (tile_order) {
+#pragma unroll
+        for (int k = 0; k < SC_IPT; k++)
+            if (base + k < tiles) {
+                const int b = gsb_lpt_bucket(v[k]);
+                tile_order[(size_t)b * tiles + s_bbase[b] + lrank[k]] = base + k;
+            }
+    }
     uint32_t run = s_excl + wp + inc - sum;
 #pragma unroll
     for (int k = 0; k < SC_IPT; k++) {
@@ -279,9 +300,10 @@ __device__ __forceinline__ void warp_sort_dispatch(const unsigned long long* key
 __global__ void __launch_bounds__(32, 24) tile_sort_kernel(const uint2* __restrict__ ranges, unsigned long long* __restrict__ pairs,
                                                            uint32_t* __restrict__ point_list, uint32_t* __restrict__ tile_count,
                                                            uint32_t* __restrict__ tile_max, uint32_t tiles,
-                                                           const uint2* __restrict__ chunk_list, const GsbCtrl* ctrl) {
+                                                           const uint2* __restrict__ chunk_list, const GsbCtrl* ctrl,
+                                                           const uint32_t* __restrict__ tile_order) {
     if (blockIdx.x < tiles) {
-        const uint32_t tile = blockIdx.x;
+        const uint32_t tile = gsb_lpt_tile(ctrl, tile_order, tiles, blockIdx.x);     // longest lists first
         // housekeeping for the kernels around this one: the count / cursor of this tile starts the next view pass at
         // zero, and the render forward takes the maximum of n_contrib over the tile with atomicMax
         if (threadIdx.x == 0) { tile_count[tile] = 0u; tile_max[tile] = 0u; }
@@ -370,7 +392,7 @@ __global__ void __launch_bounds__(256) sorted_keys_kernel(const uint2* __restric
 void launch_tile_scan(const BinningArgs& a, cudaStream_t s) {
     const uint32_t tiles = (uint32_t)(a.grid_x * a.grid_y);
     tile_scan_kernel<<<gsb_div_up(tiles, SC_TILE), 256, 0, s>>>(a.tile_count, tiles, a.ranges, a.lookback, ++(*a.epoch), a.ctrl, a.r_cap,
-                                                                a.num_rendered_host, a.big_list, a.chunk_list);
+                                                                a.num_rendered_host, a.big_list, a.chunk_list, a.tile_order);
 }
 
 void launch_queue_long_lists(const BinningArgs& a, cudaStream_t s) {
@@ -387,7 +409,7 @@ void launch_emit(const BinningArgs& a, cudaStream_t s) {
 
 void launch_tile_sort(const BinningArgs& a, cudaStream_t s) {
     const uint32_t tiles = (uint32_t)(a.grid_x * a.grid_y);
-    tile_sort_kernel<<<max(tiles, 148u * 24u), 32, 0, s>>>(a.ranges, a.pairs, a.point_list, a.tile_count, a.tile_max, tiles, a.chunk_list, a.ctrl);
+    tile_sort_kernel<<<max(tiles, 148u * 24u), 32, 0, s>>>(a.ranges, a.pairs, a.point_list, a.tile_count, a.tile_max, tiles, a.chunk_list, a.ctrl, a.tile_order);
     // the merge kernel runs over the device-side queue of long lists with a grid-stride loop (nearly empty at C4)
     tile_merge_kernel<<<min(tiles, 148u * 4u), MG_THREADS, 0, s>>>(a.ranges, a.pairs, a.pairs2, a.point_list, a.big_list, a.ctrl);
 }

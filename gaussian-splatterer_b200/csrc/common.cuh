@@ -43,7 +43,9 @@ struct GsbCtrl {
     uint32_t num_big;               // tiles queued for tile_merge_kernel
     uint32_t num_chunks;            // 1024-key chunks of those tiles queued for chunk_sort_kernel
     uint32_t pad[2];
+    uint32_t bucket_n[16];          // tiles per list-length class (gsb_lpt_bucket): the heavy-first tile order of the tile grids
 };
+constexpr int GSB_LPT_BUCKETS = 16;
 
 #define GSB_CUDA_OK(expr)                                                              \
     do {                                                                               \
@@ -98,6 +100,29 @@ __device__ __forceinline__ void gsb_warp_walk_tiles(uint32_t rx0, uint32_t ry0, 
         }
         f(on, src, tx, ty);
     }
+}
+#endif
+
+// Heavy-first order of the tile grids.  The render kernels and the tile sort run one CTA per tile and a tile's list is walked
+// serially, so a long list that starts late IS the tail of the kernel (ncu: SMs active 90 % of the forward's duration in
+// raster order).  The tile scan therefore files every tile under a list-length class (two per octave from 32 entries up)
+// and CTA number t takes the t-th tile counting from the heaviest class down -- longest-processing-time-first, to the
+// resolution of the classes.  Every tile appears exactly once (empty ones in class 0).
+#ifdef __CUDACC__
+__device__ __forceinline__ int gsb_lpt_bucket(uint32_t n) {
+    if (n < 32u) return 0;
+    const int e = 31 - __clz((int)n);                       // >= 5
+    return min(GSB_LPT_BUCKETS - 1, 2 * (e - 5) + (int)((n >> (e - 1)) & 1u) + 1);
+}
+__device__ __forceinline__ uint32_t gsb_lpt_tile(const GsbCtrl* ctrl, const uint32_t* order, uint32_t tiles, uint32_t t) {
+    if (order == nullptr) return t;
+#pragma unroll 1
+    for (int b = GSB_LPT_BUCKETS - 1; b > 0; b--) {
+        const uint32_t n = ctrl->bucket_n[b];
+        if (t < n) return order[(size_t)b * tiles + t];
+        t -= n;
+    }
+    return order[t];
 }
 #endif
 
@@ -164,6 +189,7 @@ struct BinningArgs {
     uint2* ranges;                  // [tiles] written for every tile by the scan
     uint32_t* tile_max;             // [tiles] zeroed by the sort (render forward takes atomicMax into it)
     uint32_t* big_list;             // [tiles] queue of the tiles whose lists one warp cannot sort in registers
+    uint32_t* tile_order;           // [16][tiles] tiles by list-length class, written by the scan (heavy-first order of the tile grids)
     uint2* chunk_list;              // [R / 512 + 2] (tile, chunk) queue of their 1024-key chunks
     unsigned long long* pairs2;     // [R] second buffer of the merge rounds
     unsigned long long* pairs;      // [r_cap] depth_bits << 32 | splat, bucketed by tile, sorted in place for long lists
@@ -193,6 +219,8 @@ struct RenderFwdArgs {
     uint32_t* n_contrib;            // [H*W]
     uint32_t* tile_max;             // [tiles] max n_contrib in tile
     uint32_t* frame;                // preview mode (Trainer::render): RGBA8 [H*W] written instead of everything above
+    const uint32_t* tile_order;     // [16][tiles] + ctrl: CTA -> tile, longest lists first (null: raster order)
+    const GsbCtrl* ctrl;
     float expf_k1, expf_k252;       // set by the launcher: two constants of expf2_pinned (render_common.cuh) as kernel parameters
 };
 void launch_render_fwd(const RenderFwdArgs& a, cudaStream_t s);
@@ -216,6 +244,8 @@ struct RenderBwdArgs {
     const uint32_t* truth2;
     GradRec2* grads2;
     double* loss_out;               // optional: += sum of squared residuals (fused-loss modes only)
+    const uint32_t* tile_order;     // [16][tiles] + ctrl: CTA -> tile, longest lists first (null: raster order)
+    const GsbCtrl* ctrl;
     float expf_k1, expf_k252;       // set by the launcher (see RenderFwdArgs)
 };
 void launch_render_bwd(const RenderBwdArgs& a, cudaStream_t s);

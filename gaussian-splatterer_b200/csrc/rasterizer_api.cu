@@ -109,6 +109,7 @@ int gsb_rasterizer_forward(gsb_alloc_fn geometry_alloc, void* geometry_user, gsb
     ba.P = P; ba.r_cap = 0xFFFFFFFFu; ba.grid_x = grid_x; ba.grid_y = grid_y;
     ba.radii = g.radii; ba.tiles_touched = g.tiles_touched; ba.depths = g.depths; ba.recs = g.recs;
     ba.tile_count = im.tile_count; ba.ranges = im.ranges; ba.tile_max = im.tile_max; ba.big_list = im.big_list;
+    ba.tile_order = im.tile_order;
     ba.pairs = nullptr; ba.point_list = nullptr; ba.pairs2 = nullptr; ba.chunk_list = nullptr;
     ba.lookback = im.lookback; ba.epoch = &epoch; ba.ctrl = g.ctrl; ba.num_rendered_host = nullptr;
     launch_tile_scan(ba, s);                       // ranges of every tile, R
@@ -139,7 +140,7 @@ int gsb_rasterizer_forward(gsb_alloc_fn geometry_alloc, void* geometry_user, gsb
     ra.W = width; ra.H = height; ra.grid_x = grid_x; ra.grid_y = grid_y;
     ra.ranges = im.ranges; ra.point_list = b.point_list; ra.recs = g.recs; ra.bg = background;
     ra.out_color = out_color; ra.final_T = im.final_T; ra.n_contrib = im.n_contrib; ra.tile_max = im.tile_max;
-    ra.frame = nullptr;
+    ra.frame = nullptr; ra.tile_order = im.tile_order; ra.ctrl = g.ctrl;
     launch_render_fwd(ra, s);
     if (int e = check(s, dbg)) return e;
     if (num_rendered) *num_rendered = (int)R;
@@ -172,6 +173,7 @@ int gsb_rasterizer_backward(int P, int D, int M, int R, const float* background,
         rb.ranges = im.ranges; rb.point_list = b.point_list; rb.recs = g.recs; rb.bg = background;
         rb.final_T = im.final_T; rb.n_contrib = im.n_contrib; rb.tile_max = im.tile_max;
         rb.dL_dpix = dL_dpix; rb.truth = nullptr; rb.rendered = nullptr; rb.grads = g.grads; rb.truth2 = nullptr; rb.grads2 = nullptr; rb.loss_out = nullptr;
+        rb.tile_order = im.tile_order; rb.ctrl = g.ctrl;
         launch_render_bwd(rb, s);
         if (int e = check(s, dbg)) return e;
     }

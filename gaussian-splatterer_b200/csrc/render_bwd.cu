@@ -132,13 +132,15 @@ __global__ void __launch_bounds__(RENDER_THREADS, GSB_BWD_CTAS) render_bwd_kerne
 #if GSB_EXPF_PACKED
     const ExpfConsts expk = {a.expf_k1, a.expf_k252};
 #endif
-    const int tile = blockIdx.y * a.grid_x + blockIdx.x;
+    // CTA -> tile, longest lists first (common.cuh gsb_lpt_tile)
+    const int tile = (int)gsb_lpt_tile(a.ctrl, a.tile_order, (uint32_t)(a.grid_x * a.grid_y), blockIdx.y * a.grid_x + blockIdx.x);
+    const int tile_y = tile / a.grid_x, tile_x = tile - tile_y * a.grid_x;
     const int start = (int)a.tile_max[tile];       // entries at or beyond this index were blended by no pixel
     if (start == 0 && (MODE == 0 || a.loss_out == nullptr)) return;
     const uint2 range = a.ranges[tile];
     const uint32_t* list = a.point_list + range.x;
 
-    const int bx0 = blockIdx.x * GSB_TILE + (warp & 1) * 8, by0 = blockIdx.y * GSB_TILE + (warp >> 1) * 8;
+    const int bx0 = tile_x * GSB_TILE + (warp & 1) * 8, by0 = tile_y * GSB_TILE + (warp >> 1) * 8;
     const int pix_x = bx0 + (lane & 7);
     const float pxf = (float)pix_x;
     const float bcx = (float)bx0 + 3.5f, bcy = (float)by0 + 3.5f;

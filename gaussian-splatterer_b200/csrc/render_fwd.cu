@@ -40,9 +40,11 @@ __global__ void __launch_bounds__(RENDER_THREADS) render_fwd_kernel(const Render
     __shared__ SplatRec s_rec[RENDER_WARPS][2][WB];
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int tile = blockIdx.y * a.grid_x + blockIdx.x;
+    // CTA -> tile, longest lists first (common.cuh gsb_lpt_tile)
+    const int tile = (int)gsb_lpt_tile(a.ctrl, a.tile_order, (uint32_t)(a.grid_x * a.grid_y), blockIdx.y * a.grid_x + blockIdx.x);
+    const int tile_y = tile / a.grid_x, tile_x = tile - tile_y * a.grid_x;
     // warp sub-block origin and this lane's two pixels
-    const int bx0 = blockIdx.x * GSB_TILE + (warp & 1) * 8, by0 = blockIdx.y * GSB_TILE + (warp >> 1) * 8;
+    const int bx0 = tile_x * GSB_TILE + (warp & 1) * 8, by0 = tile_y * GSB_TILE + (warp >> 1) * 8;
     const int pix_x = bx0 + (lane & 7);
     const int pix_y[2] = {by0 + (lane >> 3), by0 + (lane >> 3) + 4};
     const float pxf = (float)pix_x;

@@ -267,6 +267,7 @@ int forward_pass(gsb_trainer* t, const float* view, const float* projview, const
     ba.P = P; ba.r_cap = t->r_cap; ba.grid_x = grid_x; ba.grid_y = grid_y;
     ba.radii = t->g.radii; ba.tiles_touched = t->g.tiles_touched; ba.depths = t->g.depths; ba.recs = t->g.recs;
     ba.tile_count = im.tile_count; ba.ranges = im.ranges; ba.tile_max = im.tile_max; ba.big_list = im.big_list;
+    ba.tile_order = im.tile_order;
     ba.pairs = t->b.pairs; ba.point_list = t->b.point_list; ba.pairs2 = t->b.pairs2; ba.chunk_list = t->b.chunk_list;
     ba.lookback = im.lookback; ba.epoch = &t->epoch; ba.ctrl = t->g.ctrl; ba.num_rendered_host = h_R;
     mark(ev, ST_TILE_SCAN, s);
@@ -283,6 +284,7 @@ int forward_pass(gsb_trainer* t, const float* view, const float* projview, const
     ra.ranges = im.ranges; ra.point_list = t->b.point_list; ra.recs = t->g.recs; ra.bg = bg;
     ra.out_color = out_color; ra.final_T = im.final_T; ra.n_contrib = im.n_contrib; ra.tile_max = im.tile_max;
     ra.frame = frame;                 // Trainer::render: RGBA8 straight from the blend registers (imageFloatToInt fused)
+    ra.tile_order = im.tile_order; ra.ctrl = t->g.ctrl;
     { GSB_NVTX("render forward"); launch_render_fwd(ra, s); }
     t->stats.kernel_launches += 6;
     GSB_CUDA_OK(cudaGetLastError());
@@ -308,6 +310,7 @@ int backward_pass(gsb_trainer* t, int i, bool fused, float* avg, float S, cudaEv
     rb.dL_dpix = nullptr; rb.truth = truth; rb.rendered = t->rendered; rb.grads = t->g.grads;
     rb.truth2 = fused ? t->truthB[cam] : nullptr; rb.grads2 = fused ? t->grads2 : nullptr;
     rb.loss_out = t->loss_on ? t->d_loss : nullptr;
+    rb.tile_order = t->im.tile_order; rb.ctrl = t->g.ctrl;
     launch_render_bwd(rb, s);
 
     mark(ev, ST_PREPROCESS_BWD, s);
@@ -732,7 +735,7 @@ int gsb_trainer_count_pairs(gsb_trainer* t, int camera_index, unsigned long long
     ra.W = t->W; ra.H = t->H; ra.grid_x = t->grid_x; ra.grid_y = t->grid_y;
     ra.ranges = t->im.ranges; ra.point_list = t->b.point_list; ra.recs = t->g.recs; ra.bg = t->d_bg + 3;
     ra.out_color = t->rendered; ra.final_T = t->im.final_T; ra.n_contrib = t->im.n_contrib; ra.tile_max = t->im.tile_max;
-    ra.frame = nullptr;
+    ra.frame = nullptr; ra.tile_order = nullptr; ra.ctrl = nullptr;
     launch_count_pairs(ra, t->d_pairs, s);
     GSB_CUDA_OK(cudaMemcpyAsync(out8, t->d_pairs, 6 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
     uint32_t cnt[2] = {0, 0};
@@ -764,6 +767,7 @@ int gsb_trainer_measure_bwd_skeleton(gsb_trainer* t, int camera_index, int reps,
     rb.final_T = t->im.final_T; rb.n_contrib = t->im.n_contrib; rb.tile_max = t->im.tile_max;
     rb.dL_dpix = nullptr; rb.truth = t->truthW[camera_index]; rb.rendered = t->rendered; rb.grads = t->g.grads;
     rb.truth2 = t->truthB[camera_index]; rb.grads2 = t->grads2; rb.loss_out = nullptr;
+    rb.tile_order = t->im.tile_order; rb.ctrl = t->g.ctrl;
     cudaEvent_t e0, e1;
     GSB_CUDA_OK(cudaEventCreate(&e0));
     GSB_CUDA_OK(cudaEventCreate(&e1));
@@ -823,7 +827,7 @@ int gsb_trainer_measure_staging(gsb_trainer* t, int camera_index, int reps, floa
     ra.W = t->W; ra.H = t->H; ra.grid_x = t->grid_x; ra.grid_y = t->grid_y;
     ra.ranges = t->im.ranges; ra.point_list = t->b.point_list; ra.recs = t->g.recs; ra.bg = t->d_bg + 3;
     ra.out_color = t->rendered; ra.final_T = t->im.final_T; ra.n_contrib = t->im.n_contrib; ra.tile_max = t->im.tile_max;
-    ra.frame = nullptr;
+    ra.frame = nullptr; ra.tile_order = nullptr; ra.ctrl = nullptr;
     float* sink = nullptr;
     GSB_CUDA_OK(cudaMalloc(&sink, 2 * sizeof(float)));
     cudaEvent_t e0, e1;

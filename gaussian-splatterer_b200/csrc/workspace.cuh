@@ -76,6 +76,7 @@ struct ImageWs {
     uint32_t* tile_max;
     uint32_t* tile_count;           // per-tile duplicate count / emit cursor; zero between view passes
     uint32_t* big_list;             // queue of long-list tiles (tile_sort_kernel -> tile_sort_big_kernel)
+    uint32_t* tile_order;           // [16][tiles] tiles by list-length class (heavy-first order, written by the tile scan)
     unsigned long long* lookback;   // chained-scan status words of tile_scan_kernel (2048 tiles per word)
 
     static size_t lookback_words(size_t tiles) { return (tiles + 2047) / 2048 + 1; }
@@ -93,6 +94,7 @@ struct ImageWs {
         tile_count = c.take<uint32_t>(tiles);
         big_list = c.take<uint32_t>(tiles);
         lookback = c.take<unsigned long long>(lookback_words(tiles));
+        tile_order = c.take<uint32_t>((size_t)GSB_LPT_BUCKETS * tiles);
         return c.p;
     }
     static size_t required(size_t N, size_t tiles) {
