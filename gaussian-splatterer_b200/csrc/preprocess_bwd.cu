@@ -13,6 +13,7 @@
 // the matching mean gradient term.
 
 #include "common.cuh"
+#include <cmath>
 
 namespace {
 
@@ -123,7 +124,10 @@ __device__ __forceinline__ void pb_red4(float* p, float x, float y, float z, flo
 #define GSB_PB_THREADS 128   // 95 registers: five 128-thread blocks per SM against two of 256
 #define GSB_PB_BLOCKS 1
 #endif
-template <int NS, bool M4>
+// POW2S: the sample count S is a power of two (2 x cameras is, for every preset of the reference): x / S (what
+// accumulateGradients computes, src/Trainer.cu:54-75) is then bit for bit x * (1 / S), and the 27 IEEE divisions of the
+// accumulate epilogue become multiplications.
+template <int NS, bool M4, bool POW2S = false>
 __global__ void __launch_bounds__(GSB_PB_THREADS, GSB_PB_BLOCKS) preprocess_bwd_kernel(const PreprocessBwdArgs a) {
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= a.P || !(a.radii[idx] > 0)) return;
@@ -304,6 +308,7 @@ __global__ void __launch_bounds__(GSB_PB_THREADS, GSB_PB_BLOCKS) preprocess_bwd_
 
     const float S = a.samples;
     const float invS = 1.0f / S;
+    auto divS = [&](float x) -> float { return POW2S ? x * invS : x / S; };
 
     // ---- SH backward ----
     if (!a.colors_precomp) {
@@ -331,7 +336,7 @@ __global__ void __launch_bounds__(GSB_PB_THREADS, GSB_PB_BLOCKS) preprocess_bwd_
                 shl[8] = s2.x; shl[9] = s2.y; shl[10] = s2.z; shl[11] = s2.w;
             }
             dirs = sh_backward(1, mx, my, mz, a.cam_pos, shl, dsum, [&](int c, V3 v) {
-                o_sh[3 * c] += v.x / S; o_sh[3 * c + 1] += v.y / S; o_sh[3 * c + 2] += v.z / S;
+                o_sh[3 * c] += divS(v.x); o_sh[3 * c + 1] += divS(v.y); o_sh[3 * c + 2] += divS(v.z);
             });
             float4* p = reinterpret_cast<float4*>(avg_sh + 12 * (size_t)idx);
 #pragma unroll
@@ -342,7 +347,7 @@ __global__ void __launch_bounds__(GSB_PB_THREADS, GSB_PB_BLOCKS) preprocess_bwd_
         } else {
             float* out = avg_sh + (size_t)idx * M * 3;
             dirs = sh_backward(a.D, mx, my, mz, a.cam_pos, sh, dsum, [&](int c, V3 v) {
-                out[3 * c] += v.x / S; out[3 * c + 1] += v.y / S; out[3 * c + 2] += v.z / S;
+                out[3 * c] += divS(v.x); out[3 * c + 1] += divS(v.y); out[3 * c + 2] += divS(v.z);
             });
         }
 #pragma unroll
@@ -358,8 +363,8 @@ __global__ void __launch_bounds__(GSB_PB_THREADS, GSB_PB_BLOCKS) preprocess_bwd_
         V3 gs_ = {0.f, 0.f, 0.f};
 #pragma unroll
         for (int s = 0; s < NS; s++) {
-            var += sqrtf(gmean[s].x * gmean[s].x + gmean[s].y * gmean[s].y + gmean[s].z * gmean[s].z) / S;
-            gs_.x += gmean[s].x / S; gs_.y += gmean[s].y / S; gs_.z += gmean[s].z / S;
+            var += divS(sqrtf(gmean[s].x * gmean[s].x + gmean[s].y * gmean[s].y + gmean[s].z * gmean[s].z));
+            gs_.x += divS(gmean[s].x); gs_.y += divS(gmean[s].y); gs_.z += divS(gmean[s].z);
         }
         if (RED) {
             pb_red(a.avg + idx, var);
@@ -416,13 +421,13 @@ __global__ void __launch_bounds__(GSB_PB_THREADS, GSB_PB_BLOCKS) preprocess_bwd_
             for (int c = 0; c < 4; c++) a.dL_drot[4 * idx + c] = gq[c];
         } else if (RED) {
 #pragma unroll
-            for (int c = 0; c < 3; c++) pb_red(avg_scale + 3 * idx + c, gs[c] / S);
-            pb_red4(avg_rot + 4 * idx, gq[0] / S, gq[1] / S, gq[2] / S, gq[3] / S);
+            for (int c = 0; c < 3; c++) pb_red(avg_scale + 3 * idx + c, divS(gs[c]));
+            pb_red4(avg_rot + 4 * idx, divS(gq[0]), divS(gq[1]), divS(gq[2]), divS(gq[3]));
         } else {
 #pragma unroll
-            for (int c = 0; c < 3; c++) avg_scale[3 * idx + c] = o_scale[c] + gs[c] / S;
+            for (int c = 0; c < 3; c++) avg_scale[3 * idx + c] = o_scale[c] + divS(gs[c]);
 #pragma unroll
-            for (int c = 0; c < 4; c++) avg_rot[4 * idx + c] = o_rot[c] + gq[c] / S;
+            for (int c = 0; c < 4; c++) avg_rot[4 * idx + c] = o_rot[c] + divS(gq[c]);
         }
     }
 }
@@ -438,9 +443,14 @@ void launch_preprocess_bwd(const PreprocessBwdArgs& a, cudaStream_t s) {
                     (reinterpret_cast<uintptr_t>(a.avg) % 16 == 0) && (reinterpret_cast<uintptr_t>(a.shs) % 16 == 0) &&
                     (reinterpret_cast<uintptr_t>(a.rotations) % 16 == 0) && (reinterpret_cast<uintptr_t>(a.cov3D) % 8 == 0) &&
                     !a.cov3D_is_precomp;
+    int ex = 0;
+    const bool pow2 = trainer && a.samples > 0.f && frexpf(a.samples, &ex) == 0.5f;   // S = 2^(ex - 1)
     if (trainer && a.grads2 != nullptr) {
-        if (m4) preprocess_bwd_kernel<2, true><<<grid, GSB_PB_THREADS, 0, s>>>(a);
+        if (m4 && pow2) preprocess_bwd_kernel<2, true, true><<<grid, GSB_PB_THREADS, 0, s>>>(a);
+        else if (m4) preprocess_bwd_kernel<2, true><<<grid, GSB_PB_THREADS, 0, s>>>(a);
         else preprocess_bwd_kernel<2, false><<<grid, GSB_PB_THREADS, 0, s>>>(a);
+    } else if (m4 && pow2) {
+        preprocess_bwd_kernel<1, true, true><<<grid, GSB_PB_THREADS, 0, s>>>(a);
     } else if (m4) {
         preprocess_bwd_kernel<1, true><<<grid, GSB_PB_THREADS, 0, s>>>(a);
     } else {
