@@ -58,7 +58,10 @@ __global__ void __launch_bounds__(RENDER_THREADS) render_fwd_kernel(const Render
     for (int k = 0; k < 2; k++) done[k] = !(pix_x < a.W && pix_y[k] < a.H);
 
 #if GSB_EXPF_PACKED
-    const ExpfConsts expk = {a.expf_k1, a.expf_k252};
+    // (folded with a value the compiler cannot see through -- W is never negative -- so that it keeps both in registers
+    // instead of re-loading the parameters in front of every survivor's first FMA)
+    const int opaque0 = a.W >> 31;
+    const ExpfConsts expk = {__int_as_float(__float_as_int(a.expf_k1) ^ opaque0), __int_as_float(__float_as_int(a.expf_k252) ^ opaque0)};
 #endif
     const uint2 range = a.ranges[tile];
     const int len = (int)(range.y - range.x);
