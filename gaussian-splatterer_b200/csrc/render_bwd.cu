@@ -50,7 +50,8 @@ namespace {
 #define GSB_BWD_CONV 1   // fused mode: straight-line evaluation of both pixels of a lane
 #endif
 #ifndef GSB_BWD_CTAS
-#define GSB_BWD_CTAS 8   // resident CTAs per SM the register budget is cut for (64 registers)
+#define GSB_BWD_CTAS 7   // resident CTAs per SM the register budget is cut for: with the eight-row panel + REDUX seven (73 registers) beat
+                         // eight (64) by 1.5 %, six and nine lose; the nine-row panel preferred eight (profiles/r02_ab_bwd_variants.txt)
 #endif
 
 #ifndef GSB_BWD_REDUX
