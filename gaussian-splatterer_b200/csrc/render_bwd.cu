@@ -50,8 +50,8 @@ namespace {
 #define GSB_BWD_CONV 1   // fused mode: straight-line evaluation of both pixels of a lane
 #endif
 #ifndef GSB_BWD_CTAS
-#define GSB_BWD_CTAS 7   // resident CTAs per SM the register budget is cut for: with the eight-row panel + REDUX seven (73 registers) beat
-                         // eight (64) by 1.5 %, six and nine lose; the nine-row panel preferred eight (profiles/r02_ab_bwd_variants.txt)
+#define GSB_BWD_CTAS 7   // minimum resident CTAs per SM handed to the register allocator: at 7 the fused kernel takes 64 registers (62 at
+                         // 8) -- eight CTAs still fit -- and runs 1.5 % faster; 6 and 9 lose (profiles/r02_ab_bwd_variants.txt)
 #endif
 
 #ifndef GSB_BWD_REDUX
