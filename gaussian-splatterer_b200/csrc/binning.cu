@@ -211,6 +211,9 @@ __global__ void __launch_bounds__(256) emit_kernel(const uint32_t* __restrict__ 
 // keys), and then merged: one CTA per list, log2(chunks) rounds of pairwise merge-path merges between `pairs` and a
 // second buffer, the last round writing the splat ids.
 constexpr int TS_WARP_MAX = (int)SORT_WARP_MAX;
+#ifndef GSB_TS_CTAS
+#define GSB_TS_CTAS 20   // one-warp CTAs per SM the tile sort is cut for: 95 registers and no spill at 20 (0.0575 ms) against 80 + spills at 24 (0.0615), 32: 0.066
+#endif
 constexpr int MG_THREADS = 256;       // merge CTA
 constexpr int MG_ITEMS = 8;           // outputs per thread per block of MG_THREADS * MG_ITEMS = 2048 merged keys
 
@@ -297,7 +300,7 @@ __device__ __forceinline__ void warp_sort_dispatch(const unsigned long long* key
 // WARPSYNC / ENDCOLLECTIVE).  Lists too long for one warp were queued by the tile scan as 1024-key chunks; after its
 // own tile every CTA takes its share of that queue (grid-stride from blockIdx: uniform control flow again) and sorts
 // the chunks in place, as keys, for the merge kernel.
-__global__ void __launch_bounds__(32, 24) tile_sort_kernel(const uint2* __restrict__ ranges, unsigned long long* __restrict__ pairs,
+__global__ void __launch_bounds__(32, GSB_TS_CTAS) tile_sort_kernel(const uint2* __restrict__ ranges, unsigned long long* __restrict__ pairs,
                                                            uint32_t* __restrict__ point_list, uint32_t* __restrict__ tile_count,
                                                            uint32_t* __restrict__ tile_max, uint32_t tiles,
                                                            const uint2* __restrict__ chunk_list, const GsbCtrl* ctrl,
@@ -409,7 +412,7 @@ void launch_emit(const BinningArgs& a, cudaStream_t s) {
 
 void launch_tile_sort(const BinningArgs& a, cudaStream_t s) {
     const uint32_t tiles = (uint32_t)(a.grid_x * a.grid_y);
-    tile_sort_kernel<<<max(tiles, 148u * 24u), 32, 0, s>>>(a.ranges, a.pairs, a.point_list, a.tile_count, a.tile_max, tiles, a.chunk_list, a.ctrl, a.tile_order);
+    tile_sort_kernel<<<max(tiles, 148u * (uint32_t)GSB_TS_CTAS), 32, 0, s>>>(a.ranges, a.pairs, a.point_list, a.tile_count, a.tile_max, tiles, a.chunk_list, a.ctrl, a.tile_order);
     // the merge kernel runs over the device-side queue of long lists with a grid-stride loop (nearly empty at C4)
     tile_merge_kernel<<<min(tiles, 148u * 4u), MG_THREADS, 0, s>>>(a.ranges, a.pairs, a.pairs2, a.point_list, a.big_list, a.ctrl);
 }

@@ -124,8 +124,11 @@ __device__ __forceinline__ F3 sh_to_rgb_m4(int deg, float px, float py, float pz
 
 // VEC: rotations, the 12-float SH record and the covariance are moved as 16- / 8-byte words (the arrays are contiguous
 // per splat and the caller's bases are suitably aligned: checked by the launcher); means and scales (stride 3) stay scalar.
+#ifndef GSB_PP_THREADS
+#define GSB_PP_THREADS 256   // threads per block (A/B knob)
+#endif
 template <bool VEC>
-__global__ void __launch_bounds__(256) preprocess_fwd_kernel(const PreprocessArgs a) {
+__global__ void __launch_bounds__(GSB_PP_THREADS) preprocess_fwd_kernel(const PreprocessArgs a) {
     // every lane stays to the end (the tile counts are added warp-cooperatively); lanes beyond P shadow splat P-1 and
     // write nothing
     const int gid = blockIdx.x * blockDim.x + threadIdx.x;
@@ -309,8 +312,8 @@ void launch_preprocess_fwd(const PreprocessArgs& a, cudaStream_t s) {
     auto al = [](const void* p, uintptr_t n) { return reinterpret_cast<uintptr_t>(p) % n == 0; };
     const bool vec = a.cov3D_precomp == nullptr && a.colors_precomp == nullptr && a.M == 4 && a.D <= 1 && al(a.rotations, 16) &&
                      al(a.shs, 16) && al(a.cov3D, 8);
-    if (vec) preprocess_fwd_kernel<true><<<gsb_div_up(a.P, 256), 256, 0, s>>>(a);
-    else preprocess_fwd_kernel<false><<<gsb_div_up(a.P, 256), 256, 0, s>>>(a);
+    if (vec) preprocess_fwd_kernel<true><<<gsb_div_up(a.P, GSB_PP_THREADS), GSB_PP_THREADS, 0, s>>>(a);
+    else preprocess_fwd_kernel<false><<<gsb_div_up(a.P, GSB_PP_THREADS), GSB_PP_THREADS, 0, s>>>(a);
 }
 
 void launch_mark_visible(int P, const float* means3D, const float* viewmatrix, bool* present, cudaStream_t s) {

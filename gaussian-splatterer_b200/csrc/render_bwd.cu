@@ -51,7 +51,7 @@ namespace {
 #endif
 #ifndef GSB_BWD_CTAS
 #define GSB_BWD_CTAS 7   // minimum resident CTAs per SM handed to the register allocator: at 7 the fused kernel takes 64 registers (62 at
-                         // 8) -- eight CTAs still fit -- and runs 1.5 % faster; 6 and 9 lose (profiles/r02_ab_bwd_variants.txt)
+                         // 8) -- eight CTAs still fit -- and runs 1.5 % faster; 6 and 9 lose (profiles/r02_ab_variants.txt)
 #endif
 
 #ifndef GSB_BWD_REDUX

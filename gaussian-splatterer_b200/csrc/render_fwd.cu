@@ -29,6 +29,10 @@ constexpr int WB = 32;   // list entries per warp-private chunk (one per lane)
 // 1: both pixels of a lane are evaluated in one straight-line pass with packed FP32 pairs (FFMA2 / FMUL2 / FADD2, IEEE
 // round-to-nearest like the scalar intrinsics, so every bit of T / colour / n_contrib is unchanged); a pixel that does
 // not blend the entry runs with alpha = 0, which leaves T (T * 1) and the colour (C + T * 0) bit for bit unchanged.
+#ifndef GSB_FWD_CTAS
+#define GSB_FWD_CTAS 8    // minimum resident CTAs per SM handed to the register allocator: 55 registers, nine CTAs resident -- 0.292 ms against
+                          // 0.294 (no bound: 45 registers, ten CTAs), 0.299 (12), 0.301 (9), 0.309 (10: 44 registers); same-box A/B
+#endif
 #ifndef GSB_FWD_CONV
 #define GSB_FWD_CONV 1
 #endif
@@ -36,7 +40,7 @@ constexpr int WB = 32;   // list entries per warp-private chunk (one per lane)
 // PREVIEW: Trainer::render's shape -- the pixel goes out as RGBA8 (imageFloatToInt, src/Trainer.cu:21-31, applied to the
 // same float colour) and nothing a backward pass would need (final_T, n_contrib, the float planes, tile_max) is written.
 template <bool PREVIEW>
-__global__ void __launch_bounds__(RENDER_THREADS) render_fwd_kernel(const RenderFwdArgs a) {
+__global__ void __launch_bounds__(RENDER_THREADS, GSB_FWD_CTAS) render_fwd_kernel(const RenderFwdArgs a) {
     __shared__ SplatRec s_rec[RENDER_WARPS][2][WB];
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;

@@ -1,7 +1,13 @@
+#!/bin/bash
+# Same-box A/B of library variants (developer tool): AB_VARIANTS="base x y base" bash tools/ab_variants.sh
+# Each name but "base" is gaussian-splatterer_b200/libgsb200_<name>.so (built out of tree with make EXTRA=-D...; the .so files
+# travel with gpurun); one short bench.py run per variant, one line per variant:
+#   name  views/s  render_bwd  render_fwd  preprocess  emit  tile_sort  preprocess_bwd (ms per launch, stage events)
 for v in ${AB_VARIANTS:-base}; do
   L=gaussian-splatterer_b200/libgsb200_$v.so; [ $v = base ] && L=gaussian-splatterer_b200/libgsb200.so
   GSB_LIB=$PWD/$L python bench.py --steps 5 --warmup 3 --no-cpu-baseline --no-e2e > gpurun_out/ab_$v.json 2> gpurun_out/ab_$v.err
   python -c "
-import json,sys
-d=json.load(open('gpurun_out/ab_$v.json')); print('$v', round(d['value'],1), d['stages']['render_bwd']['ms_per_launch'], d['stages']['render_fwd']['ms_per_launch'])"
+import json
+d=json.load(open('gpurun_out/ab_$v.json')); s=d['stages']
+print('$v', round(d['value'],1), *[s[k]['ms_per_launch'] for k in ('render_bwd','render_fwd','preprocess','emit','tile_sort','preprocess_bwd')])"
 done
