@@ -62,6 +62,7 @@ struct gsb_trainer {
     cudaStream_t sF2 = nullptr;                       // forward chains of the odd passes (slot 1): chains of different slots are independent
     cudaEvent_t ev_scan_prev = nullptr;               // tile scan of the second-to-last pass (it runs on the other forward stream)
     bool two_fwd_streams = true;
+    bool lpt = true;                         // heavy-first tile order (GSB_LPT=0: raster order, developer A/B)
     cudaStream_t exec_f = nullptr, exec_b = nullptr;  // null = everything on `stream`
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_fdone[2] = {nullptr, nullptr}, ev_bdone[2] = {nullptr, nullptr};
     // preview arena (Trainer::render at another resolution)
@@ -267,7 +268,7 @@ int forward_pass(gsb_trainer* t, const float* view, const float* projview, const
     ba.P = P; ba.r_cap = t->r_cap; ba.grid_x = grid_x; ba.grid_y = grid_y;
     ba.radii = t->g.radii; ba.tiles_touched = t->g.tiles_touched; ba.depths = t->g.depths; ba.recs = t->g.recs;
     ba.tile_count = im.tile_count; ba.ranges = im.ranges; ba.tile_max = im.tile_max; ba.big_list = im.big_list;
-    ba.tile_order = im.tile_order;
+    ba.tile_order = t->lpt ? im.tile_order : nullptr;
     ba.pairs = t->b.pairs; ba.point_list = t->b.point_list; ba.pairs2 = t->b.pairs2; ba.chunk_list = t->b.chunk_list;
     ba.lookback = im.lookback; ba.epoch = &t->epoch; ba.ctrl = t->g.ctrl; ba.num_rendered_host = h_R;
     mark(ev, ST_TILE_SCAN, s);
@@ -284,7 +285,7 @@ int forward_pass(gsb_trainer* t, const float* view, const float* projview, const
     ra.ranges = im.ranges; ra.point_list = t->b.point_list; ra.recs = t->g.recs; ra.bg = bg;
     ra.out_color = out_color; ra.final_T = im.final_T; ra.n_contrib = im.n_contrib; ra.tile_max = im.tile_max;
     ra.frame = frame;                 // Trainer::render: RGBA8 straight from the blend registers (imageFloatToInt fused)
-    ra.tile_order = im.tile_order; ra.ctrl = t->g.ctrl;
+    ra.tile_order = ba.tile_order; ra.ctrl = t->g.ctrl;
     { GSB_NVTX("render forward"); launch_render_fwd(ra, s); }
     t->stats.kernel_launches += 6;
     GSB_CUDA_OK(cudaGetLastError());
@@ -310,7 +311,7 @@ int backward_pass(gsb_trainer* t, int i, bool fused, float* avg, float S, cudaEv
     rb.dL_dpix = nullptr; rb.truth = truth; rb.rendered = t->rendered; rb.grads = t->g.grads;
     rb.truth2 = fused ? t->truthB[cam] : nullptr; rb.grads2 = fused ? t->grads2 : nullptr;
     rb.loss_out = t->loss_on ? t->d_loss : nullptr;
-    rb.tile_order = t->im.tile_order; rb.ctrl = t->g.ctrl;
+    rb.tile_order = t->lpt ? t->im.tile_order : nullptr; rb.ctrl = t->g.ctrl;
     launch_render_bwd(rb, s);
 
     mark(ev, ST_PREPROCESS_BWD, s);
@@ -386,6 +387,7 @@ int gsb_trainer_create(gsb_trainer** out, int width, int height, void* stream) {
     GSB_CUDA_OK(cudaStreamCreateWithPriority(&t->sB, cudaStreamNonBlocking, prio_lo));
     GSB_CUDA_OK(cudaEventCreateWithFlags(&t->ev_scan_prev, cudaEventDisableTiming));
     if (const char* e = getenv("GSB_FWD_STREAMS")) t->two_fwd_streams = atoi(e) != 1;
+    if (const char* e = getenv("GSB_LPT")) t->lpt = atoi(e) != 0;
     GSB_CUDA_OK(cudaEventCreateWithFlags(&t->ev_fork, cudaEventDisableTiming));
     GSB_CUDA_OK(cudaEventCreateWithFlags(&t->ev_join, cudaEventDisableTiming));
     GSB_CUDA_OK(cudaEventCreateWithFlags(&t->ev_scan, cudaEventDisableTiming));
