@@ -43,9 +43,12 @@ struct GsbCtrl {
     uint32_t num_big;               // tiles queued for tile_merge_kernel
     uint32_t num_chunks;            // 1024-key chunks of those tiles queued for chunk_sort_kernel
     uint32_t pad[2];
-    uint32_t bucket_n[16];          // tiles per list-length class (gsb_lpt_bucket): the heavy-first tile order of the tile grids
+#ifndef GSB_LPT_FINE
+#define GSB_LPT_FINE 0              // 1: four classes per octave (32 classes) instead of two (16): A/B knob
+#endif
+    uint32_t bucket_n[GSB_LPT_FINE ? 32 : 16];   // tiles per list-length class (gsb_lpt_bucket): the heavy-first tile order of the tile grids
 };
-constexpr int GSB_LPT_BUCKETS = 16;
+constexpr int GSB_LPT_BUCKETS = GSB_LPT_FINE ? 32 : 16;
 
 #define GSB_CUDA_OK(expr)                                                              \
     do {                                                                               \
@@ -112,7 +115,11 @@ __device__ __forceinline__ void gsb_warp_walk_tiles(uint32_t rx0, uint32_t ry0, 
 __device__ __forceinline__ int gsb_lpt_bucket(uint32_t n) {
     if (n < 32u) return 0;
     const int e = 31 - __clz((int)n);                       // >= 5
+#if GSB_LPT_FINE
+    return min(GSB_LPT_BUCKETS - 1, 4 * (e - 5) + (int)((n >> (e - 2)) & 3u) + 1);
+#else
     return min(GSB_LPT_BUCKETS - 1, 2 * (e - 5) + (int)((n >> (e - 1)) & 1u) + 1);
+#endif
 }
 __device__ __forceinline__ uint32_t gsb_lpt_tile(const GsbCtrl* ctrl, const uint32_t* order, uint32_t tiles, uint32_t t) {
     if (order == nullptr) return t;
@@ -189,7 +196,7 @@ struct BinningArgs {
     uint2* ranges;                  // [tiles] written for every tile by the scan
     uint32_t* tile_max;             // [tiles] zeroed by the sort (render forward takes atomicMax into it)
     uint32_t* big_list;             // [tiles] queue of the tiles whose lists one warp cannot sort in registers
-    uint32_t* tile_order;           // [16][tiles] tiles by list-length class, written by the scan (heavy-first order of the tile grids)
+    uint32_t* tile_order;           // [GSB_LPT_BUCKETS][tiles] tiles by list-length class, written by the scan (heavy-first order of the tile grids)
     uint2* chunk_list;              // [R / 512 + 2] (tile, chunk) queue of their 1024-key chunks
     unsigned long long* pairs2;     // [R] second buffer of the merge rounds
     unsigned long long* pairs;      // [r_cap] depth_bits << 32 | splat, bucketed by tile, sorted in place for long lists
@@ -219,7 +226,7 @@ struct RenderFwdArgs {
     uint32_t* n_contrib;            // [H*W]
     uint32_t* tile_max;             // [tiles] max n_contrib in tile
     uint32_t* frame;                // preview mode (Trainer::render): RGBA8 [H*W] written instead of everything above
-    const uint32_t* tile_order;     // [16][tiles] + ctrl: CTA -> tile, longest lists first (null: raster order)
+    const uint32_t* tile_order;     // [GSB_LPT_BUCKETS][tiles] + ctrl: CTA -> tile, longest lists first (null: raster order)
     const GsbCtrl* ctrl;
     float expf_k1, expf_k252;       // set by the launcher: two constants of expf2_pinned (render_common.cuh) as kernel parameters
 };
@@ -244,7 +251,7 @@ struct RenderBwdArgs {
     const uint32_t* truth2;
     GradRec2* grads2;
     double* loss_out;               // optional: += sum of squared residuals (fused-loss modes only)
-    const uint32_t* tile_order;     // [16][tiles] + ctrl: CTA -> tile, longest lists first (null: raster order)
+    const uint32_t* tile_order;     // [GSB_LPT_BUCKETS][tiles] + ctrl: CTA -> tile, longest lists first (null: raster order)
     const GsbCtrl* ctrl;
     float expf_k1, expf_k252;       // set by the launcher (see RenderFwdArgs)
 };

@@ -76,7 +76,7 @@ struct ImageWs {
     uint32_t* tile_max;
     uint32_t* tile_count;           // per-tile duplicate count / emit cursor; zero between view passes
     uint32_t* big_list;             // queue of long-list tiles (tile_sort_kernel -> tile_sort_big_kernel)
-    uint32_t* tile_order;           // [16][tiles] tiles by list-length class (heavy-first order, written by the tile scan)
+    uint32_t* tile_order;           // [GSB_LPT_BUCKETS][tiles] tiles by list-length class (heavy-first order, written by the tile scan)
     unsigned long long* lookback;   // chained-scan status words of tile_scan_kernel (2048 tiles per word)
 
     static size_t lookback_words(size_t tiles) { return (tiles + 2047) / 2048 + 1; }
