@@ -15,7 +15,7 @@ from .camera import Camera, CameraSphere, Project  # noqa: F401
 
 def __getattr__(name):
     # torch-dependent modules load lazily so the CPU-only parts import without CUDA
-    if name in ("Rasterizer", "Workspaces", "state"):
+    if name in ("Rasterizer", "Workspaces", "state", "tile_order"):
         from . import rasterizer
         return getattr(rasterizer, name)
     if name in ("Trainer", "Comm", "Window", "ModelSplatsDevice", "ModelSplatsHost", "camera_struct"):

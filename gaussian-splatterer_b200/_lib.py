@@ -70,6 +70,8 @@ def lib():
     L.gsb_rasterizer_state.restype = i
     L.gsb_rasterizer_sorted_keys.argtypes = [i, i, i, i, vp, vp, vp, vp, vp]
     L.gsb_rasterizer_sorted_keys.restype = i
+    L.gsb_rasterizer_tile_order.argtypes = [i, i, i, vp, vp, vp, vp]
+    L.gsb_rasterizer_tile_order.restype = i
     L.gsb_trainer_create.argtypes = [C.POINTER(vp), i, i, vp]
     L.gsb_trainer_create.restype = i
     L.gsb_trainer_destroy.argtypes = [vp]
@@ -166,7 +168,7 @@ def lib():
 # Every symbol include/gsb.h declares; the CPU test-suite checks the library exports all of them.
 EXPORTED_SYMBOLS = [
     "gsb_last_error", "gsb_version", "gsb_rasterizer_forward", "gsb_rasterizer_backward",
-    "gsb_rasterizer_mark_visible", "gsb_rasterizer_state", "gsb_rasterizer_sorted_keys",
+    "gsb_rasterizer_mark_visible", "gsb_rasterizer_state", "gsb_rasterizer_sorted_keys", "gsb_rasterizer_tile_order",
     "gsb_trainer_enable_loss", "gsb_trainer_get_loss", "gsb_trainer_set_fuse_backgrounds", "gsb_trainer_profile_pass",
     "gsb_trainer_set_stage_timing", "gsb_trainer_get_stage_times", "gsb_trainer_count_pairs", "gsb_trainer_set_overlap",
     "gsb_trainer_debug_set_epoch", "gsb_measure_fp32_peak", "gsb_trainer_measure_bwd_skeleton", "gsb_trainer_measure_staging", "gsb_trainer_reduction_stats",

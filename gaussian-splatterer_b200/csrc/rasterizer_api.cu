@@ -237,6 +237,31 @@ int gsb_rasterizer_sorted_keys(int P, int width, int height, int R, char* geom_b
     return GSB_OK;
 }
 
+// The order in which the tile grids (tile sort, render forward / backward) take their tiles after a forward pass: CTA
+// number t works on tile host_order_out[t] (heaviest list-length class first, common.cuh gsb_lpt_tile).  For tests.
+int gsb_rasterizer_tile_order(int P, int width, int height, char* geom_buffer, char* image_buffer, uint32_t* host_order_out,
+                              void* stream) {
+    if (!geom_buffer || !image_buffer || !host_order_out) return gsb_fail_msg("gsb_rasterizer_tile_order: invalid argument");
+    cudaStream_t s = (cudaStream_t)stream;
+    const int grid_x = (width + GSB_TILE - 1) / GSB_TILE, grid_y = (height + GSB_TILE - 1) / GSB_TILE;
+    const size_t tiles = (size_t)grid_x * grid_y;
+    GeomWs g; g.carve(geom_buffer, (size_t)P);
+    ImageWs im; im.carve(image_buffer, (size_t)width * height, tiles);
+    GsbCtrl ctrl;
+    GSB_CUDA_OK(cudaMemcpyAsync(&ctrl, g.ctrl, sizeof(ctrl), cudaMemcpyDeviceToHost, s));
+    GSB_CUDA_OK(cudaStreamSynchronize(s));
+    size_t at = 0;
+    for (int b = GSB_LPT_BUCKETS - 1; b >= 0; b--) {
+        const size_t n = ctrl.bucket_n[b];
+        if (at + n > tiles) return gsb_fail_msg("gsb_rasterizer_tile_order: class counts exceed the tile count");
+        if (n) GSB_CUDA_OK(cudaMemcpyAsync(host_order_out + at, im.tile_order + (size_t)b * tiles, n * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+        at += n;
+    }
+    GSB_CUDA_OK(cudaStreamSynchronize(s));
+    if (at != tiles) return gsb_fail_msg("gsb_rasterizer_tile_order: class counts do not add up to the tile count");
+    return GSB_OK;
+}
+
 int gsb_measure_fp32_peak(double* out2, void* stream) {
     if (!out2) return gsb_fail_msg("gsb_measure_fp32_peak: null argument");
     return gsb_measure_fp32_peak_impl(out2, (cudaStream_t)stream);

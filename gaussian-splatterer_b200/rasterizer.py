@@ -116,3 +116,12 @@ def state(ws, P, width, height, R):
         check(lib().gsb_rasterizer_sorted_keys(P, width, height, R, _ptr(ws.geom), _ptr(ws.binning), _ptr(ws.image), _ptr(keys), None))
     out["point_list_keys"] = keys[:R]
     return out
+
+
+def tile_order(ws, P, width, height):
+    """CTA number -> tile of the one-CTA-per-tile grids after a forward pass (heaviest list-length class first)."""
+    import numpy as np
+    tiles = ((width + 15) // 16) * ((height + 15) // 16)
+    out = np.zeros(tiles, dtype=np.uint32)
+    check(lib().gsb_rasterizer_tile_order(P, width, height, _ptr(ws.geom), _ptr(ws.image), out.ctypes.data_as(C.c_void_p), None))
+    return out

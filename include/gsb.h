@@ -99,6 +99,10 @@ int gsb_rasterizer_state(int P, int width, int height, int R, char* geom_buffer,
 int gsb_rasterizer_sorted_keys(int P, int width, int height, int R, char* geom_buffer,
                                char* binning_buffer, char* image_buffer, uint64_t* dev_keys_out,
                                void* stream);
+/* Test hook: the order in which the one-CTA-per-tile grids (tile sort, render forward / backward) take their tiles after a
+ * forward pass -- CTA number t works on tile host_order_out[t], longest lists first; a permutation of 0 .. tiles-1. */
+int gsb_rasterizer_tile_order(int P, int width, int height, char* geom_buffer, char* image_buffer,
+                              uint32_t* host_order_out, void* stream);
 
 /* ---- trainer level ---------------------------------------------------------------------- */
 

@@ -57,6 +57,29 @@ def test_forward_matches_reference_golden(name):
 
 
 @pytest.mark.parametrize("name", list(GC.RASTER_CASES))
+def test_tile_order_is_a_heavy_first_permutation(name):
+    """The one-CTA-per-tile grids (tile sort, render forward / backward) take their tiles heaviest list first
+    (csrc/common.cuh gsb_lpt_tile): every tile exactly once, list-length classes (two per octave from 32 entries up) never
+    increasing along the order.  The reference launches its tile grid in raster order (forward.cu:261-280); the order
+    changes no result, which the golden tests above check."""
+    c, cloud, consts, _ = GC.raster_inputs(name)
+    _, _, ws, _, R, st = _run(cloud, consts, c["bg"], c["W"], c["H"])
+    order = gsb.tile_order(ws, cloud["locations"].shape[0], c["W"], c["H"]).astype(np.int64)
+    tiles = ((c["W"] + 15) // 16) * ((c["H"] + 15) // 16)
+    assert order.shape == (tiles,) and np.array_equal(np.sort(order), np.arange(tiles))
+    ranges = st["ranges"].cpu().numpy().astype(np.int64)
+    n = (ranges[:, 1] - ranges[:, 0])[order]
+
+    def cls(v):
+        if v < 32:
+            return 0
+        e = int(v).bit_length() - 1
+        return min(15, 2 * (e - 5) + ((int(v) >> (e - 1)) & 1) + 1)
+    k = np.array([cls(v) for v in n])
+    assert np.all(np.diff(k) <= 0), (k[:20], n[:20])
+
+
+@pytest.mark.parametrize("name", list(GC.RASTER_CASES))
 def test_backward_matches_reference_golden(name):
     g = GC.load("raster_" + name)
     c, cloud, consts, dL = GC.raster_inputs(name)
