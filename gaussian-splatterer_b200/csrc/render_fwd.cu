@@ -29,6 +29,9 @@ constexpr int WB = 32;   // list entries per warp-private chunk (one per lane)
 // 1: both pixels of a lane are evaluated in one straight-line pass with packed FP32 pairs (FFMA2 / FMUL2 / FADD2, IEEE
 // round-to-nearest like the scalar intrinsics, so every bit of T / colour / n_contrib is unchanged); a pixel that does
 // not blend the entry runs with alpha = 0, which leaves T (T * 1) and the colour (C + T * 0) bit for bit unchanged.
+#ifndef GSB_FWD_CA
+#define GSB_FWD_CA 0      // 1: record staging through L1 (see cp_async16): the stage alone gains 0.7 %, the pipelined step nothing
+#endif
 #ifndef GSB_FWD_CTAS
 #define GSB_FWD_CTAS 8    // minimum resident CTAs per SM handed to the register allocator: 55 registers, nine CTAs resident -- 0.292 ms against
                           // 0.294 (no bound: 45 registers, ten CTAs), 0.299 (12), 0.301 (9), 0.309 (10: 44 registers); same-box A/B
@@ -79,9 +82,9 @@ __global__ void __launch_bounds__(RENDER_THREADS, GSB_FWD_CTAS) render_fwd_kerne
         if (next_id != 0xFFFFFFFFu) {
             const SplatRec* g = a.recs + next_id;
             SplatRec* d = &s_rec[warp][buf][lane];
-            cp_async16(&d->a, &g->a);
-            cp_async16(&d->b, &g->b);
-            cp_async16(&d->c, &g->c);
+            cp_async16<GSB_FWD_CA != 0>(&d->a, &g->a);
+            cp_async16<GSB_FWD_CA != 0>(&d->b, &g->b);
+            cp_async16<GSB_FWD_CA != 0>(&d->c, &g->c);
         }
         cp_async_commit();
     };

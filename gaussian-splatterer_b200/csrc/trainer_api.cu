@@ -382,6 +382,10 @@ int gsb_trainer_create(gsb_trainer** out, int width, int height, void* stream) {
     // an SM frees while the (low-priority, register-heavy) backward kernel drains.
     int prio_lo = 0, prio_hi = 0;
     GSB_CUDA_OK(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+    if (const char* e = getenv("GSB_STREAM_PRIO")) {      // developer A/B: 0 = equal priorities, -1 = backward high / forward low
+        if (atoi(e) == 0) prio_hi = prio_lo;
+        else if (atoi(e) < 0) std::swap(prio_lo, prio_hi);
+    }
     GSB_CUDA_OK(cudaStreamCreateWithPriority(&t->sF, cudaStreamNonBlocking, prio_hi));
     GSB_CUDA_OK(cudaStreamCreateWithPriority(&t->sF2, cudaStreamNonBlocking, prio_hi));
     GSB_CUDA_OK(cudaStreamCreateWithPriority(&t->sB, cudaStreamNonBlocking, prio_lo));
