@@ -458,9 +458,16 @@ def run_gsb(args):
         dset = [([dev_all[w][i] for i in range(len(tw))], [dev_all[w][len(tw) + i] for i in range(len(tb))]) for w in (0, 1)]
         copy_stream = torch.cuda.Stream()
         up_ev = [torch.cuda.Event(), torch.cuda.Event()]
+        done_ev = [torch.cuda.Event(), torch.cuda.Event()]
         losses = []
 
-        def upload(which):
+        def upload(which, after=None):
+            # `after`: the end of the step that read the set about to be overwritten.  Without it the copy starts while
+            # that step's last backward pass still reads its truth frames (a write-after-read race, harmless here only
+            # because every step uploads the same frames) and runs underneath that step's exchange, which it slows down:
+            # tools/e2e_bisect.py on 2 B200, 8 cameras per rank: 8.38 ms HBM-resident, 8.67 end to end unordered, 8.50 ordered
+            if after is not None:
+                copy_stream.wait_event(after)
             with torch.cuda.stream(copy_stream):
                 dev_all[which].copy_(host_all, non_blocking=True)
                 up_ev[which].record(copy_stream)
@@ -468,9 +475,10 @@ def run_gsb(args):
         def step(k, last=False):
             cur = k & 1
             torch.cuda.current_stream().wait_event(up_ev[cur])    # this step's inputs have landed
-            upload(cur ^ 1)                                       # next step's inputs, overlapped
+            upload(cur ^ 1, done_ev[cur ^ 1])                     # next step's inputs, overlapped with this step
             tr.truthFrameBuffersW, tr.truthFrameBuffersB = dset[cur]
             tr.train(project, False)
+            done_ev[cur].record()     # legacy stream: behind everything the step enqueued (joined backward chains, exchange, apply)
             # device -> host read of a step's result, every step: the scalar of step k-1 is read while step k runs (the
             # library copies it to pinned memory at the end of each iteration), the last step's own before the clock stops
             losses.append(tr.loss(1 if not last else 0) if (len(losses) or last) else tr.loss(0))
@@ -481,10 +489,11 @@ def run_gsb(args):
         ms_e = timed_steps(torch, dist, lambda k: step(k, last=(k == args.steps - 1)), args.steps)
         h2d = n_local * 2 * W * Hh * 4 + n_local * 148
         e2e = {"value": views_per_step * args.steps / (ms_e / 1000.0), "unit": UNIT, "h2d_bytes_per_step": h2d,
-               "d2h_bytes_per_step": 8 + 4 * 2 * n_local, "ms_per_step": ms_e / args.steps,
+               "d2h_bytes_per_step": 8 * 128 + 4 * 2 * n_local,   # GSB_LOSS_SLOTS partial sums + R of every view pass "ms_per_step": ms_e / args.steps,
                "result": "sum of squared residuals", "last_loss": losses[-1],
                "how": "Trainer.train with RGBA8 truth frames in pinned host memory (allocated on the GPU's NUMA node); one "
-                      "cudaMemcpyAsync of the next step's frames on a copy stream overlaps the current step; the loss scalar of "
+                      "cudaMemcpyAsync of the next step's frames on a copy stream overlaps the current step (it starts when the step that "
+                      "last read that device set has finished); the loss scalar of "
                       "step k-1 is read from pinned memory while step k runs, the last step's before the clock stops; per rank",
                "host_placement": placement.info}
         tr.close()

@@ -233,6 +233,11 @@ struct RenderFwdArgs {
 void launch_render_fwd(const RenderFwdArgs& a, cudaStream_t s);
 
 // render_bwd.cu
+// The fused loss is one double atomic per warp.  Into a single address they serialise in one L2 slice: 32 640 of them per
+// launch at 1080p cost 14 us per launch (0.9 ms of a 65 ms step, tools/e2e_bisect.py); spread by tile over this many
+// addresses (the host adds the slots up after the copy) they disappear under the kernel.
+constexpr int GSB_LOSS_SLOTS = 128;
+
 struct RenderBwdArgs {
     int W, H, grid_x, grid_y;
     const uint2* ranges;
@@ -250,7 +255,7 @@ struct RenderBwdArgs {
     // `rendered` the black-background image; both passes accumulate into grads2 (grads is not touched)
     const uint32_t* truth2;
     GradRec2* grads2;
-    double* loss_out;               // optional: += sum of squared residuals (fused-loss modes only)
+    double* loss_out;               // optional: [GSB_LOSS_SLOTS] partial sums of squared residuals, += (fused-loss modes only)
     const uint32_t* tile_order;     // [GSB_LPT_BUCKETS][tiles] + ctrl: CTA -> tile, longest lists first (null: raster order)
     const GsbCtrl* ctrl;
     float expf_k1, expf_k252;       // set by the launcher (see RenderFwdArgs)

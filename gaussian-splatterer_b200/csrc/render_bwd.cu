@@ -207,7 +207,7 @@ __global__ void __launch_bounds__(RENDER_THREADS, GSB_BWD_CTAS) render_bwd_kerne
         double acc = (double)sq;
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
-        if (lane == 0) atomicAdd(a.loss_out, acc);
+        if (lane == 0) atomicAdd(a.loss_out + (tile & (GSB_LOSS_SLOTS - 1)), acc);
         if (start == 0) return;
     }
     asm volatile("" : "+f"(pyf[0]), "+f"(pyf[1]));   // keep the pixel rows in registers (not re-derived per entry)

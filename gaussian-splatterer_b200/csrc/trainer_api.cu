@@ -187,6 +187,13 @@ int ensure_avg(gsb_trainer* t) {
     return GSB_OK;
 }
 
+// loss of the iteration whose partial sums (GSB_LOSS_SLOTS doubles, common.cuh) were copied into host slot `slot`
+double loss_of_slot(const gsb_trainer* t, unsigned slot) {
+    double v = 0.0;
+    for (int k = 0; k < GSB_LOSS_SLOTS; k++) v += t->h_loss[(size_t)slot * GSB_LOSS_SLOTS + k];
+    return v;
+}
+
 // Look-back status words carry a 30-bit epoch tag (binning.cu lb_pack) so the status arrays never need clearing
 // between launches.  Before the tag would wrap, every stream is drained, all look-back arrays are cleared and the
 // counter restarts (one view pass consumes 1 epoch, a densify 1).
@@ -399,10 +406,10 @@ int gsb_trainer_create(gsb_trainer** out, int width, int height, void* stream) {
         GSB_CUDA_OK(cudaEventCreateWithFlags(&t->ev_fdone[k], cudaEventDisableTiming));
         GSB_CUDA_OK(cudaEventCreateWithFlags(&t->ev_bdone[k], cudaEventDisableTiming));
     }
-    GSB_CUDA_OK(cudaMalloc(&t->d_loss, sizeof(double)));
-    GSB_CUDA_OK(cudaMemset(t->d_loss, 0, sizeof(double)));
-    GSB_CUDA_OK(cudaHostAlloc(&t->h_loss, 2 * sizeof(double), cudaHostAllocDefault));
-    t->h_loss[0] = t->h_loss[1] = 0.0;
+    GSB_CUDA_OK(cudaMalloc(&t->d_loss, GSB_LOSS_SLOTS * sizeof(double)));
+    GSB_CUDA_OK(cudaMemset(t->d_loss, 0, GSB_LOSS_SLOTS * sizeof(double)));
+    GSB_CUDA_OK(cudaHostAlloc(&t->h_loss, 2 * GSB_LOSS_SLOTS * sizeof(double), cudaHostAllocDefault));
+    memset(t->h_loss, 0, 2 * GSB_LOSS_SLOTS * sizeof(double));
     for (int k = 0; k < 2; k++) GSB_CUDA_OK(cudaEventCreateWithFlags(&t->ev_loss[k], cudaEventDisableTiming));
     GSB_CUDA_OK(cudaMalloc(&t->totals, 4 * sizeof(uint32_t)));
     GSB_CUDA_OK(cudaMalloc(&t->dens_ticket, sizeof(uint32_t)));
@@ -526,7 +533,7 @@ int gsb_trainer_get_stats(gsb_trainer* t, gsb_trainer_stats* out) {
     if (!t || !out) return gsb_fail_msg("gsb_trainer_get_stats: invalid argument");
     if (t->loss_pending) {
         GSB_CUDA_OK(cudaEventSynchronize(t->ev_loss[t->loss_iter & 1]));
-        t->stats.sum_sq_residual = t->h_loss[t->loss_iter & 1];
+        t->stats.sum_sq_residual = loss_of_slot(t, t->loss_iter & 1);
         t->loss_pending = false;
     }
     *out = t->stats;
@@ -538,7 +545,7 @@ int gsb_trainer_get_loss(gsb_trainer* t, int iterations_back, double* out) {
     if (!t->loss_on || t->loss_iter < (unsigned)iterations_back + 1u) { gsb_fail_msg("gsb_trainer_get_loss: no such iteration (enable the loss first)"); return GSB_ERR_STATE; }
     const unsigned slot = (t->loss_iter - (unsigned)iterations_back) & 1u;
     GSB_CUDA_OK(cudaEventSynchronize(t->ev_loss[slot]));
-    *out = t->h_loss[slot];
+    *out = loss_of_slot(t, slot);
     return GSB_OK;
 }
 
@@ -597,7 +604,7 @@ int gsb_trainer_accumulate(gsb_trainer* t) {
         // underneath the first forward chain instead of in front of it
         cudaStream_t sz = pipe ? t->sB : s;
         GSB_CUDA_OK(cudaMemsetAsync(avg, 0, grad_floats(t) * sizeof(float), sz));
-        if (t->loss_on) GSB_CUDA_OK(cudaMemsetAsync(t->d_loss, 0, sizeof(double), sz));
+        if (t->loss_on) GSB_CUDA_OK(cudaMemsetAsync(t->d_loss, 0, GSB_LOSS_SLOTS * sizeof(double), sz));
         int err = GSB_OK;
         for (int i = 0; i < passes && !err; i++) {
             if (pipe) {
@@ -647,7 +654,7 @@ int gsb_trainer_accumulate(gsb_trainer* t) {
             }
             if (t->loss_on) {   // read back lazily: gsb_trainer_get_stats waits for this copy, train() does not
                 t->loss_iter++;
-                GSB_CUDA_OK(cudaMemcpyAsync(t->h_loss + (t->loss_iter & 1), t->d_loss, sizeof(double), cudaMemcpyDeviceToHost, s));
+                GSB_CUDA_OK(cudaMemcpyAsync(t->h_loss + (size_t)(t->loss_iter & 1) * GSB_LOSS_SLOTS, t->d_loss, GSB_LOSS_SLOTS * sizeof(double), cudaMemcpyDeviceToHost, s));
                 GSB_CUDA_OK(cudaEventRecord(t->ev_loss[t->loss_iter & 1], s));
                 t->loss_pending = true;
             }

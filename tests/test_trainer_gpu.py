@@ -245,3 +245,17 @@ def test_overlapped_pipeline_equals_serial_execution():
         assert sa["rendered_total"] == sb["rendered_total"]
         assert abs(sa["sum_sq_residual"] - sb["sum_sq_residual"]) <= 1e-9 * sa["sum_sq_residual"]
         assert H.rel_l2(b, a) <= 1e-5
+    # the fused loss (one double atomic per warp, spread over GSB_LOSS_SLOTS addresses and added up by the host) against an
+    # independent value: imageIntToLoss's residuals (src/Trainer.cu:38-42) of every (camera, background) pass, squared
+    # and summed in double by torch from Rasterizer::forward's image
+    sc = H.scene_tensors(cloud, DEV)
+    want = 0.0
+    for cam, fw, fb in zip(cams, tw, tb):
+        c = cam.view_constants(W, Hh, square_fov=False)
+        for bg, truth in (((1.0, 1.0, 1.0), fw), ((0.0, 0.0, 0.0), fb)):
+            _, out, _ = H.run_forward_gsb(sc, H.view_tensors(c, bg, DEV), P, 1, 4, W, Hh)
+            t = truth.view(torch.int32)
+            chan = torch.stack([(t >> s) & 0xFF for s in (0, 8, 16)]).to(torch.float32) / 255.0
+            want += float(((chan.reshape(3, -1) - out.reshape(3, -1)).double() ** 2).sum())
+    for key, (_, st) in res.items():
+        assert abs(st["sum_sq_residual"] - want) <= 1e-5 * want, (key, st["sum_sq_residual"], want)
