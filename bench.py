@@ -489,7 +489,8 @@ def run_gsb(args):
         ms_e = timed_steps(torch, dist, lambda k: step(k, last=(k == args.steps - 1)), args.steps)
         h2d = n_local * 2 * W * Hh * 4 + n_local * 148
         e2e = {"value": views_per_step * args.steps / (ms_e / 1000.0), "unit": UNIT, "h2d_bytes_per_step": h2d,
-               "d2h_bytes_per_step": 8 * 128 + 4 * 2 * n_local,   # GSB_LOSS_SLOTS partial sums + R of every view pass "ms_per_step": ms_e / args.steps,
+               "d2h_bytes_per_step": 8 * 128 + 4 * 2 * n_local,   # GSB_LOSS_SLOTS partial sums + R of every view pass
+               "ms_per_step": ms_e / args.steps,
                "result": "sum of squared residuals", "last_loss": losses[-1],
                "how": "Trainer.train with RGBA8 truth frames in pinned host memory (allocated on the GPU's NUMA node); one "
                       "cudaMemcpyAsync of the next step's frames on a copy stream overlaps the current step (it starts when the step that "

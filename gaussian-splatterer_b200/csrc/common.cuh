@@ -236,7 +236,10 @@ void launch_render_fwd(const RenderFwdArgs& a, cudaStream_t s);
 // The fused loss is one double atomic per warp.  Into a single address they serialise in one L2 slice: 32 640 of them per
 // launch at 1080p cost 14 us per launch (0.9 ms of a 65 ms step, tools/e2e_bisect.py); spread by tile over this many
 // addresses (the host adds the slots up after the copy) they disappear under the kernel.
-constexpr int GSB_LOSS_SLOTS = 128;
+#ifndef GSB_LOSS_SLOTS_N
+#define GSB_LOSS_SLOTS_N 128
+#endif
+constexpr int GSB_LOSS_SLOTS = GSB_LOSS_SLOTS_N;   // a power of two
 
 struct RenderBwdArgs {
     int W, H, grid_x, grid_y;

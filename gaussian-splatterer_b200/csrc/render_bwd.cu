@@ -204,10 +204,11 @@ __global__ void __launch_bounds__(RENDER_THREADS, GSB_BWD_CTAS) render_bwd_kerne
 #pragma unroll
             for (int s = 0; s < NS; s++)
                 sq += dLr[s][k] * dLr[s][k] + dLg[s][k] * dLg[s][k] + dLb[s][k] * dLb[s][k];
-        double acc = (double)sq;
+        // the warp's 64 pixels in float (384 squares: 1e-6 relative at worst, the value is for monitoring), one double
+        // atomic per warp into the tile's slot
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
-        if (lane == 0) atomicAdd(a.loss_out + (tile & (GSB_LOSS_SLOTS - 1)), acc);
+        for (int o = 16; o > 0; o >>= 1) sq += __shfl_xor_sync(0xffffffffu, sq, o);
+        if (lane == 0) atomicAdd(a.loss_out + (tile & (GSB_LOSS_SLOTS - 1)), (double)sq);
         if (start == 0) return;
     }
     asm volatile("" : "+f"(pyf[0]), "+f"(pyf[1]));   // keep the pixel rows in registers (not re-derived per entry)
