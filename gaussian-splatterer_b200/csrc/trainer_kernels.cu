@@ -225,20 +225,6 @@ __global__ void __launch_bounds__(256) densify_scatter_kernel(DensifyArgs a, Den
     }
 }
 
-__global__ void __launch_bounds__(256) sum_sq_residual_kernel(const uint32_t* __restrict__ truth,
-                                                              const float* __restrict__ rendered, int n, double* out) {
-    double acc = 0.0;
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-        const uint32_t t = truth[i];
-        const float r = (float)(t & 0xFF) / 255.0f - rendered[i];
-        const float g = (float)((t >> 8) & 0xFF) / 255.0f - rendered[i + n];
-        const float b = (float)((t >> 16) & 0xFF) / 255.0f - rendered[i + 2 * (size_t)n];
-        acc += (double)(r * r + g * g + b * b);
-    }
-    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
-    if ((threadIdx.x & 31) == 0) atomicAdd(out, acc);
-}
-
 }  // namespace
 
 void launch_image_float_to_int(const float* src, uint32_t* fb, int w, int h, cudaStream_t s) {
@@ -251,12 +237,6 @@ void launch_image_int_to_loss(const uint32_t* truth, const float* rasterized, fl
     const int n = w * h;
     if (n <= 0) return;
     image_int_to_loss_kernel<<<min(gsb_div_up(n, 256), 148 * 8), 256, 0, s>>>(truth, rasterized, loss, n);
-}
-
-void launch_sum_sq_residual(const uint32_t* truth, const float* rendered, int w, int h, double* out, cudaStream_t s) {
-    const int n = w * h;
-    if (n <= 0) return;
-    sum_sq_residual_kernel<<<min(gsb_div_up(n, 256), 148 * 4), 256, 0, s>>>(truth, rendered, n, out);
 }
 
 void launch_apply_gradients(const ApplyArgs& a, cudaStream_t s) {

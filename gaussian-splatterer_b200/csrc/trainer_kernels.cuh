@@ -32,7 +32,6 @@ struct DensifyOut {
 
 void launch_image_float_to_int(const float* src, uint32_t* fb, int w, int h, cudaStream_t s);
 void launch_image_int_to_loss(const uint32_t* truth, const float* rasterized, float* loss, int w, int h, cudaStream_t s);
-void launch_sum_sq_residual(const uint32_t* truth, const float* rendered, int w, int h, double* out, cudaStream_t s);
 void launch_apply_gradients(const ApplyArgs& a, cudaStream_t s);
 void launch_densify_classify_scan(const DensifyArgs& a, cudaStream_t s);
 void launch_densify_scatter(const DensifyArgs& a, const DensifyOut& o, cudaStream_t s);
